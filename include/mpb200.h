@@ -1,0 +1,164 @@
+/*
+ * mpb200.h -- C ABI of the B200-native kNN + edge-collision path for sampling-based
+ * motion planners (drop-in for the hot path of caelan/motion-planners).
+ *
+ * The reference has no FFI layer: its operator API is four Python callables
+ * (README.md:52-59).  This ABI is what a binding for the BATCHED forms of those
+ * callables binds; each entry point cites the reference code it replaces
+ * (paths relative to the reference checkout, motion_planners/...).
+ *
+ * Conventions
+ *  - Plain C: pointers and sizes only.  `stream` is a cudaStream_t passed as void*
+ *    (NULL = the legacy default stream).  Every call is asynchronous and ordered on
+ *    `stream`; nothing synchronises the device unless stated.
+ *  - "dev" pointers are device pointers on the CURRENT device, "host" pointers are
+ *    host pointers.  The caller owns every buffer; the library allocates nothing
+ *    except inside mpb_world_create.
+ *  - Configurations are row-major [n, D] IEEE binary64, contiguous, D <= MPB_MAX_DIM.
+ *  - Return value: 0 on success, a negative MPB_E* code otherwise; mpb_last_error()
+ *    returns a thread-local message.  Nothing throws, nothing aborts.
+ *  - All results are bit-exact to the reference's fp64 arithmetic.
+ */
+#ifndef MPB200_H
+#define MPB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MPB_VERSION 1
+#define MPB_MAX_DIM 16
+#define MPB_MAX_K 32
+
+#define MPB_OK 0
+#define MPB_EINVAL (-22)   /* bad argument (size, dim, k, null pointer, misalignment) */
+#define MPB_ENOMEM (-12)   /* workspace too small / allocation failed                */
+#define MPB_ECUDA (-5)     /* a CUDA runtime call failed; see mpb_last_error()        */
+
+typedef struct mpb_world mpb_world;
+
+int mpb_version(void);
+const char *mpb_last_error(void);
+
+/* ---- obstacle set --------------------------------------------------------------------
+ * Replaces the closure built by tkinter/samplers.py:88-98 get_collision_fn(environment,
+ * obstacles) over tkinter/viewer.py:16-17 Box / Circle.  All array arguments are HOST
+ * pointers and are copied to the current device (this is the one call that allocates).
+ * box_lo/box_hi: [n_box, dim] raw bounds; sph_c: [n_sph, dim]; sph_r: [n_sph];
+ * env_lo/env_hi: [dim]; buffer: obstacle inflation (viewer.py:70 MIN_PROXIMITY = 1e-3).
+ * The inflated bounds lower-buffer, upper+buffer and radius+buffer are rounded once in
+ * fp64, exactly as viewer.py:72-82 does on every call. */
+int mpb_world_create(const double *box_lo, const double *box_hi, int n_box, const double *sph_c,
+                     const double *sph_r, int n_sph, int dim, const double *env_lo,
+                     const double *env_hi, double buffer, mpb_world **out);
+int mpb_world_destroy(mpb_world *world);
+
+/* ---- collision_fn over a batch of configurations ---------------------------------------
+ * out[i] = collision_fn(q[i]) (tkinter/samplers.py:90-96): 1 if q is outside the closed
+ * environment box or inside any inflated obstacle, else 0.  Replaces the per-vertex
+ * calls at lazy_prm.py:173-178, rrt_connect.py:47, meta.py:24.
+ * q: dev [n, dim] f64; out: dev [n] u8. */
+int mpb_points_check(const mpb_world *world, const double *q, int64_t n, uint8_t *out, void *stream);
+
+/* ---- extend_fn + collision_fn fused over a batch of directed edges ----------------------
+ * For each edge q1 -> q2: discretise with tkinter/samplers.py:113-127 get_extend_fn
+ * (circular = {}, norm = inf): n = int(max_d |(q2-q1)/step|) + 1 waypoints from the serial
+ * recurrence q <- (1/(n-i))*(q2-q) + q, each operation rounded separately; test every
+ * waypoint i < n - skip_last with collision_fn.
+ *   mode MPB_EDGE_ANY   out_hit = index of SOME colliding waypoint, -1 if none
+ *                       (lazy_prm.py:189-195 check_edge; prm.py:250-251 with skip_last=1)
+ *   mode MPB_EDGE_FIRST out_hit = smallest colliding index (primitives.py:23 takewhile,
+ *                       rrt_star.py:76-82 safe_path)
+ *   mode MPB_EDGE_LAST  out_hit = largest colliding index (backward extension,
+ *                       primitives.py:13-16: the prefix of the reversed list)
+ * out_n (may be NULL) receives n.  Both outputs are dev [E] i32. */
+#define MPB_EDGE_ANY 0
+#define MPB_EDGE_FIRST 1
+#define MPB_EDGE_LAST 2
+/* edges as index pairs into a sample table: samples dev [N, dim] f64, src/dst dev [E] i64 */
+int mpb_edges_check(const mpb_world *world, const double *samples, int64_t n_samples,
+                    const int64_t *src, const int64_t *dst, int64_t n_edges, double step, int mode,
+                    int skip_last, int32_t *out_hit, int32_t *out_n, void *stream);
+/* edges as explicit endpoint arrays: q1, q2 dev [E, dim] f64 */
+int mpb_edges_check_pairs(const mpb_world *world, const double *q1, const double *q2,
+                          int64_t n_edges, double step, int mode, int skip_last, int32_t *out_hit,
+                          int32_t *out_n, void *stream);
+/* The waypoints themselves (extend_fn output) for one edge batch, for callers that need
+ * the path (lazy_prm.py:223-230 get_path, prm.py:51-58 Edge.path): offsets dev [E+1] i64 is
+ * the exclusive prefix sum of the counts from out_n; out dev [offsets[E], dim] f64. */
+int mpb_edges_waypoints(const double *q1, const double *q2, int64_t n_edges, int dim, double step,
+                        const int64_t *offsets, double *out, void *stream);
+
+/* ---- k nearest neighbours ---------------------------------------------------------------
+ * Replaces nearest.py:36-85 KDNeighbors.query_neighbors (scipy cKDTree, p = 2, eps = 0,
+ * no circular dimensions) as called per sample by lazy_prm.py:148-160, and the full
+ * distance sort of prm.py:244-246.  Points are embedded as e = fl(weights * x)
+ * (primitives.py:55-57); the ranking key is cKDTree's squared distance (4-way unrolled
+ * fp64 sum, no FMA), ties broken by the smaller index; out_dist = sqrt(key).  Only
+ * neighbours with key < fl(max_dist*max_dist) are returned (scipy's distance_upper_bound);
+ * missing slots hold idx = -1, dist = +inf.  Rows are sorted ascending.
+ * samples dev [N, dim], queries dev [M, dim] f64; weights HOST [dim] (NULL = ones);
+ * out_idx dev [M, k] i64; out_dist dev [M, k] f64 (may be NULL); 1 <= k <= MPB_MAX_K. */
+
+/* Exact fp64 brute force: one warp per query, no scratch memory. */
+int mpb_knn_f64(const double *samples, int64_t n_samples, const double *queries, int64_t n_queries,
+                int dim, const double *weights, int k, double max_dist, int64_t *out_idx,
+                double *out_dist, void *stream);
+
+/* Tiled fp32 filter + fp64 re-rank, same results bit for bit: an fp32 pass over
+ * shared-memory tiles keeps 32 candidates per query, the exact fp64 keys of those
+ * candidates are ranked, and a rigorous rounding-error bound proves that no excluded
+ * sample can belong to the answer; queries for which the proof fails are redone by the
+ * exact kernel inside the same call.
+ * workspace: dev, 256-byte aligned, at least mpb_knn_workspace_bytes(N, M, dim) bytes.
+ * stats (dev [2] i64, may be NULL): [0] = queries re-done exactly, [1] = reserved. */
+size_t mpb_knn_workspace_bytes(int64_t n_samples, int64_t n_queries, int dim);
+int mpb_knn_prepare(const double *samples, int64_t n_samples, int dim, const double *weights,
+                    void *workspace, size_t workspace_bytes, void *stream);
+int mpb_knn_search(const double *samples, int64_t n_samples, const double *queries,
+                   int64_t n_queries, int dim, const double *weights, int k, double max_dist,
+                   void *workspace, size_t workspace_bytes, int64_t *out_idx, double *out_dist,
+                   int64_t *stats, void *stream);
+/* prepare + search in one call */
+int mpb_knn_f32filter(const double *samples, int64_t n_samples, const double *queries,
+                      int64_t n_queries, int dim, const double *weights, int k, double max_dist,
+                      void *workspace, size_t workspace_bytes, int64_t *out_idx, double *out_dist,
+                      int64_t *stats, void *stream);
+
+/* ---- tree queries (RRT family) ----------------------------------------------------------
+ * metric selects the reference's rounding procedure for the weighted Euclidean distance:
+ *   MPB_METRIC_KDTREE     the kNN key above
+ *   MPB_METRIC_PRIMITIVES primitives.py:60-62 get_distance_fn (sequential-FMA dot)
+ *   MPB_METRIC_SAMPLERS   tkinter/samplers.py:11-16 get_distance_fn (sequential-FMA dot) */
+#define MPB_METRIC_KDTREE 0
+#define MPB_METRIC_PRIMITIVES 1
+#define MPB_METRIC_SAMPLERS 2
+/* For T independent trees stored as nodes dev [T, cap, dim] with sizes dev [T] i32 and one
+ * target per tree (targets dev [T, dim]): out_idx[t] = first arg-min of distance_fn(node,
+ * target) over the tree's nodes (utils.py:61-65 argmin as used by primitives.py:21 and
+ * rrt_star.py:117), out_dist[t] its distance (may be NULL).  `active` (dev [T] u8, may be
+ * NULL) skips trees whose flag is 0. */
+int mpb_trees_nearest(const double *nodes, const int32_t *sizes, int64_t n_trees, int64_t cap,
+                      int dim, const double *targets, const double *weights, int metric,
+                      const uint8_t *active, int32_t *out_idx, double *out_dist, void *stream);
+/* One tree: nearest node to q and every node with distance_fn(node, q) < radius
+ * (rrt_star.py:117,128).  out_nearest dev [1] i32; out_dist dev [n] f64 receives all
+ * distances; out_count dev [1] i32; out_list dev [n] i32 the qualifying indices ascending. */
+int mpb_scan_nearest_radius(const double *nodes, int64_t n, int dim, const double *q,
+                            const double *weights, int metric, double radius, int32_t *out_nearest,
+                            double *out_dist, int32_t *out_count, int32_t *out_list, void *stream);
+
+/* ---- measurement helpers (not part of the planner path) ---------------------------------
+ * Issue-rate micro-benchmarks used by bench.py for the roofline denominators: each thread
+ * runs `iters` rounds of 8 independent dependent-FMA chains.  flops = 2 * 8 * iters *
+ * blocks * threads.  sink: dev, at least blocks*threads elements. */
+int mpb_peak_fma_f32(int blocks, int threads, int iters, float *sink, void *stream);
+int mpb_peak_fma_f64(int blocks, int threads, int iters, double *sink, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MPB200_H */

@@ -1,0 +1,616 @@
+// k nearest neighbours: exact fp64 brute force, and the tiled fp32 filter + fp64 re-rank.
+//
+// Replaces motion_planners/nearest.py:36-85 (KDNeighbors over scipy's cKDTree, p = 2,
+// eps = 0) as driven by motion_planners/lazy_prm.py:148-160, and the distance sort of
+// motion_planners/prm.py:244-246.  Ranking key = cKDTree's squared distance between the
+// embedded points e = fl(w*x) (motion_planners/primitives.py:55-57): four fp64 accumulators
+// over blocks of four dimensions, no FMA, ties to the smaller index.
+//
+// fp32 filter: samples are packed once into fp32 tiles (centred on the bounding-box
+// midpoint, plus the squared norm), streamed through shared memory with 1-D bulk async
+// copies (TMA engine) in a multi-stage mbarrier ring, and each warp scores 32 candidates per
+// step for Q register-resident queries with the expansion key = |x|^2 - 2 q.x (D FFMA per
+// pair).  Each query keeps its 32 best candidates in a warp-distributed sorted list (one
+// entry per lane, shuffle insert).  At the end the exact fp64 keys of those 32 are ranked
+// and a rounding-error bound certifies that nothing outside the list can enter the top k;
+// uncertified queries are queued for the exact kernel.
+#include <math.h>
+
+#include "mpb_common.cuh"
+
+#define FULL_MASK 0xffffffffu
+
+namespace {
+
+constexpr int kWarps = 8;          // consumer warps per block
+constexpr int kStages = 4;         // shared-memory ring depth
+constexpr int kListLen = 32;       // candidates kept per query (one per lane)
+constexpr int kHeaderBytes = 512;
+
+struct Weights {
+    double w[MPB_MAX_DIM];
+};
+
+struct KnnHeader {
+    unsigned long long mm[2 * MPB_MAX_DIM];   // order-encoded min [0,16) and max [16,32)
+    double center[MPB_MAX_DIM];
+    double R;                                 // >= ||e - c|| and >= ||fl32(e - c)|| for every sample
+    int fb_count;                             // queries queued for the exact kernel
+    int pad;
+};
+static_assert(sizeof(KnnHeader) <= kHeaderBytes, "header overflows its slot");
+
+__host__ __device__ constexpr int planes_for(int D) { return (D + 1 + 3) / 4; }
+__host__ __device__ constexpr int tile_for(int D) { return planes_for(D) == 1 ? 1024 : (planes_for(D) == 2 ? 512 : 256); }
+
+__device__ __forceinline__ unsigned long long enc_f64(double v)
+{
+    unsigned long long u = (unsigned long long)__double_as_longlong(v);
+    return (u >> 63) ? ~u : (u | 0x8000000000000000ull);
+}
+__device__ __forceinline__ double dec_f64(unsigned long long u)
+{
+    u = (u >> 63) ? (u & 0x7fffffffffffffffull) : ~u;
+    return __longlong_as_double((long long)u);
+}
+
+// ------------------------------------------------------------------------------------------
+// prepare: bounding box -> centre and radius -> packed fp32 tiles
+// ------------------------------------------------------------------------------------------
+__global__ void knn_init_kernel(KnnHeader *h)
+{
+    const int i = threadIdx.x;
+    if (i < MPB_MAX_DIM) {
+        h->mm[i] = enc_f64(INFINITY);
+        h->mm[MPB_MAX_DIM + i] = enc_f64(-INFINITY);
+        h->center[i] = 0.;
+    }
+    if (i == 0) {
+        h->R = 0.;
+        h->fb_count = 0;
+    }
+}
+
+template <int D>
+__global__ void __launch_bounds__(256) knn_minmax_kernel(const double *__restrict__ x, int64_t N, Weights wt, KnnHeader *h)
+{
+    double lo[D], hi[D];
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        lo[d] = INFINITY;
+        hi[d] = -INFINITY;
+    }
+    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < N; j += (int64_t)gridDim.x * blockDim.x) {
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            const double e = d_mul(wt.w[d], x[j * D + d]);
+            lo[d] = fmin(lo[d], e);
+            hi[d] = fmax(hi[d], e);
+        }
+    }
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            lo[d] = fmin(lo[d], __shfl_xor_sync(FULL_MASK, lo[d], o));
+            hi[d] = fmax(hi[d], __shfl_xor_sync(FULL_MASK, hi[d], o));
+        }
+        if ((threadIdx.x & 31) == 0) {
+            atomicMin(&h->mm[d], enc_f64(lo[d]));
+            atomicMax(&h->mm[MPB_MAX_DIM + d], enc_f64(hi[d]));
+        }
+    }
+}
+
+__global__ void knn_finalize_kernel(KnnHeader *h, int D)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    double r2 = 0.;
+    for (int d = 0; d < D; ++d) {
+        const double lo = dec_f64(h->mm[d]), hi = dec_f64(h->mm[MPB_MAX_DIM + d]);
+        double c = 0.5 * lo + 0.5 * hi;
+        if (!isfinite(c)) c = 0.;
+        h->center[d] = c;
+        const double ext = fmax(fabs(hi - c), fabs(c - lo));
+        r2 += ext * ext;
+    }
+    // 1e-6 covers the rounding of c, ext, the sum, and of fl32(e - c) (2^-24)
+    h->R = sqrt(r2) * (1.0 + 1e-6) + 1e-300;
+}
+
+// Tile-planar layout: tile t holds TILE candidates as P planes of TILE float4 each;
+// component index D of a candidate's P*4 floats is its squared norm, the rest of the
+// padding is zero.  Slots past N carry an infinite norm so that they never qualify.
+template <int D>
+__global__ void __launch_bounds__(256)
+    knn_pack_kernel(const double *__restrict__ x, int64_t N, int64_t Npad, Weights wt, const KnnHeader *__restrict__ h,
+                    float4 *__restrict__ packed)
+{
+    constexpr int P = planes_for(D), TILE = tile_for(D);
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= Npad) return;
+    float v[4 * P];
+#pragma unroll
+    for (int i = 0; i < 4 * P; ++i) v[i] = 0.f;
+    if (j < N) {
+        double n2 = 0.;
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            const double e = d_mul(wt.w[d], x[j * D + d]);
+            const float f = (float)d_sub(e, h->center[d]);
+            v[d] = f;
+            n2 += (double)f * (double)f;
+        }
+        v[D] = (float)n2;
+    } else {
+        v[D] = INFINITY;
+    }
+    const int64_t t = j / TILE;
+    const int c = (int)(j - t * TILE);
+#pragma unroll
+    for (int p = 0; p < P; ++p)
+        packed[(t * P + p) * TILE + c] = make_float4(v[4 * p], v[4 * p + 1], v[4 * p + 2], v[4 * p + 3]);
+}
+
+// ------------------------------------------------------------------------------------------
+// exact kernel: one warp per query, sorted (key, index) list distributed over the lanes
+// ------------------------------------------------------------------------------------------
+template <int D>
+__global__ void __launch_bounds__(256)
+    knn_exact_kernel(const double *__restrict__ x, int64_t N, const double *__restrict__ qs, int64_t M, Weights wt,
+                     int k, double r2, const int *__restrict__ list, const int *__restrict__ list_count,
+                     int64_t *__restrict__ out_idx, double *__restrict__ out_dist, int64_t *__restrict__ stats)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int64_t total = list ? (int64_t)*list_count : M;
+    if (stats && warp0 == 0 && lane == 0) stats[0] = list ? total : 0;
+
+    for (int64_t it = warp0; it < total; it += nwarps) {
+        const int64_t q = list ? (int64_t)list[it] : it;
+        double eq[D];
+#pragma unroll
+        for (int d = 0; d < D; ++d) eq[d] = d_mul(wt.w[d], qs[q * D + d]);
+        double lk = INFINITY, thr = INFINITY;
+        int li = -1;
+        for (int64_t j0 = 0; j0 < N; j0 += 32) {
+            const int64_t j = j0 + lane;
+            double S = INFINITY;
+            if (j < N) {
+                double ex[D];
+#pragma unroll
+                for (int d = 0; d < D; ++d) ex[d] = d_mul(wt.w[d], x[j * D + d]);
+                S = sqdist_kdtree<D>(eq, ex);
+            }
+            unsigned m = __ballot_sync(FULL_MASK, S < thr);
+            while (m) {
+                const int src = __ffs(m) - 1;
+                m &= m - 1;
+                const double key = __shfl_sync(FULL_MASK, S, src);
+                if (key < thr) {
+                    // equal keys: the newcomer (larger index) goes after the incumbents
+                    const int pos = __popc(__ballot_sync(FULL_MASK, lk <= key));
+                    const double upk = __shfl_up_sync(FULL_MASK, lk, 1);
+                    const int upi = __shfl_up_sync(FULL_MASK, li, 1);
+                    if (lane > pos) {
+                        lk = upk;
+                        li = upi;
+                    } else if (lane == pos) {
+                        lk = key;
+                        li = (int)(j0 + src);
+                    }
+                    thr = __shfl_sync(FULL_MASK, lk, 31);
+                }
+            }
+        }
+        if (lane < k) {
+            const bool keep = (li >= 0) && (lk < r2);
+            out_idx[q * k + lane] = keep ? (int64_t)li : -1;
+            if (out_dist) out_dist[q * k + lane] = keep ? __dsqrt_rn(lk) : INFINITY;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// fp32 filter kernel
+// ------------------------------------------------------------------------------------------
+template <int D, int Q>
+struct FilterSmem {
+    static constexpr int P = planes_for(D);
+    static constexpr int TILE = tile_for(D);
+    static constexpr int STAGE_BYTES = TILE * P * 16;
+    static constexpr int BYTES = kStages * STAGE_BYTES + 2 * kStages * 8 + 64;
+};
+
+template <int D, int Q>
+__global__ void __launch_bounds__(kWarps * 32, 2)
+    knn_filter_kernel(const double *__restrict__ x, int64_t N, const double *__restrict__ qs, int64_t M, Weights wt,
+                      int k, double r2, const float4 *__restrict__ packed, int n_tiles, KnnHeader *__restrict__ h,
+                      int *__restrict__ fb_list, int64_t *__restrict__ out_idx, double *__restrict__ out_dist)
+{
+    using SM = FilterSmem<D, Q>;
+    constexpr int P = SM::P, TILE = SM::TILE;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    float4 *stage_base = reinterpret_cast<float4 *>(smem_raw);
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw + kStages * SM::STAGE_BYTES);
+    uint64_t *empty = full + kStages;
+
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const bool producer = (threadIdx.x == 0);
+
+    if (producer) {
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], kWarps);
+        }
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (producer) {
+        for (int s = 0; s < kStages && s < n_tiles; ++s) {
+            mbar_arrive_expect_tx(&full[s], SM::STAGE_BYTES);
+            bulk_copy_g2s(stage_base + (size_t)s * TILE * P, packed + (size_t)s * TILE * P, SM::STAGE_BYTES, &full[s]);
+        }
+    }
+
+    // ---- this warp's Q queries, as -2*fl32(e_q - c), uniform across the lanes
+    const int64_t q0 = ((int64_t)blockIdx.x * kWarps + warp) * Q;
+    float qm[Q][D];
+#pragma unroll
+    for (int qi = 0; qi < Q; ++qi) {
+        int64_t q = q0 + qi;
+        if (q >= M) q = M - 1;
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            const double e = d_mul(wt.w[d], qs[q * D + d]);
+            qm[qi][d] = -2.f * (float)d_sub(e, h->center[d]);
+        }
+    }
+    float thr[Q], lk[Q];
+    int li[Q];
+#pragma unroll
+    for (int qi = 0; qi < Q; ++qi) {
+        thr[qi] = INFINITY;
+        lk[qi] = INFINITY;
+        li[qi] = -1;
+    }
+
+    // ---- stream every tile through the ring
+    for (int t = 0; t < n_tiles; ++t) {
+        const int s = t % kStages;
+        const uint32_t ph = (uint32_t)(t / kStages) & 1u;
+        // refill the slot released one tile ago
+        if (producer && t >= 1 && (t - 1 + kStages) < n_tiles) {
+            const int sp = (t - 1) % kStages;
+            const uint32_t php = (uint32_t)((t - 1) / kStages) & 1u;
+            mbar_wait(&empty[sp], php);
+            mbar_arrive_expect_tx(&full[sp], SM::STAGE_BYTES);
+            bulk_copy_g2s(stage_base + (size_t)sp * TILE * P, packed + (size_t)(t - 1 + kStages) * TILE * P,
+                          SM::STAGE_BYTES, &full[sp]);
+        }
+        __syncwarp();
+        mbar_wait(&full[s], ph);
+
+        const float4 *tile = stage_base + (size_t)s * TILE * P;
+        const int cbase0 = t * TILE;
+#pragma unroll 2
+        for (int c0 = 0; c0 < TILE; c0 += 32) {
+            float xv[4 * P];
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                const float4 f = tile[p * TILE + c0 + lane];
+                xv[4 * p + 0] = f.x;
+                xv[4 * p + 1] = f.y;
+                xv[4 * p + 2] = f.z;
+                xv[4 * p + 3] = f.w;
+            }
+            float acc[Q];
+            bool pass = false;
+#pragma unroll
+            for (int qi = 0; qi < Q; ++qi) {
+                float a = xv[D];
+#pragma unroll
+                for (int d = 0; d < D; ++d) a = __fmaf_rn(qm[qi][d], xv[d], a);
+                acc[qi] = a;
+                pass = pass || (a < thr[qi]);
+            }
+            if (__any_sync(FULL_MASK, pass)) {
+                const int cbase = cbase0 + c0;
+#pragma unroll
+                for (int qi = 0; qi < Q; ++qi) {
+                    unsigned m = __ballot_sync(FULL_MASK, acc[qi] < thr[qi]);
+                    while (m) {
+                        const int src = __ffs(m) - 1;
+                        m &= m - 1;
+                        const float key = __shfl_sync(FULL_MASK, acc[qi], src);
+                        if (key < thr[qi]) {
+                            const int pos = __popc(__ballot_sync(FULL_MASK, lk[qi] <= key));
+                            const float upk = __shfl_up_sync(FULL_MASK, lk[qi], 1);
+                            const int upi = __shfl_up_sync(FULL_MASK, li[qi], 1);
+                            if (lane > pos) {
+                                lk[qi] = upk;
+                                li[qi] = upi;
+                            } else if (lane == pos) {
+                                lk[qi] = key;
+                                li[qi] = cbase + src;
+                            }
+                            thr[qi] = __shfl_sync(FULL_MASK, lk[qi], 31);
+                        }
+                    }
+                }
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[s]);
+    }
+
+    // ---- exact re-rank of the 32 survivors and the certificate
+    const double R = h->R;
+    constexpr double U32 = 5.9604644775390625e-08;   // 2^-24
+#pragma unroll
+    for (int qi = 0; qi < Q; ++qi) {
+        const int64_t q = q0 + qi;
+        if (q >= M) continue;   // warp-uniform
+        double eq[D];
+        double nq2 = 0.;
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            eq[d] = d_mul(wt.w[d], qs[q * D + d]);
+            const double qh = -0.5 * (double)qm[qi][d];
+            nq2 += qh * qh;
+        }
+        const int ci = li[qi];
+        double S = INFINITY;
+        if (ci >= 0) {
+            double ex[D];
+#pragma unroll
+            for (int d = 0; d < D; ++d) ex[d] = d_mul(wt.w[d], x[(int64_t)ci * D + d]);
+            S = sqdist_kdtree<D>(eq, ex);
+        }
+        int rank = 0;
+#pragma unroll 4
+        for (int o = 0; o < 32; ++o) {
+            const double So = __shfl_sync(FULL_MASK, S, o);
+            const int io = __shfl_sync(FULL_MASK, ci, o);
+            rank += ((So < S) || (So == S && io < ci)) ? 1 : 0;
+        }
+        // k-th smallest exact key among the survivors (inf when fewer than k exist)
+        const unsigned mk = __ballot_sync(FULL_MASK, ci >= 0 && rank == k - 1);
+        const double Sk = mk ? __shfl_sync(FULL_MASK, S, __ffs(mk) - 1) : INFINITY;
+        const double T = (double)thr[qi];
+        bool ok = isinf(T) && T > 0;   // list never filled: every sample is a survivor
+        if (!ok) {
+            // every sample outside the list has computed key >= T, hence exact squared
+            // distance >= (sqrt(T - eta + |q|^2) - delta)^2  ("kNN certificate")
+            const double nq = sqrt(nq2);
+            const double delta = U32 * (R + nq) * 1.0001 + 1e-30;
+            const double eta = (double)(D + 2) * U32 * 1.001 * (R * R + 2.0 * nq * R) + 1e-37;
+            double slow = T - eta + nq2;
+            slow -= 1e-12 * (fabs(T) + eta + nq2);
+            double bound = 0.;
+            if (slow > 0.) {
+                const double rho = sqrt(slow) * (1.0 - 1e-15) - delta;
+                if (rho > 0.) bound = rho * rho * (1.0 - 1e-12);
+            }
+            ok = (Sk < bound) || (r2 <= bound);
+        }
+        if (ok) {
+            if (ci >= 0 && rank < k) {
+                const bool keep = S < r2;
+                out_idx[q * k + rank] = keep ? (int64_t)ci : -1;
+                if (out_dist) out_dist[q * k + rank] = keep ? __dsqrt_rn(S) : INFINITY;
+            }
+            const int nvalid = __popc(__ballot_sync(FULL_MASK, ci >= 0));
+            if (lane < k && lane >= nvalid) {
+                out_idx[q * k + lane] = -1;
+                if (out_dist) out_dist[q * k + lane] = INFINITY;
+            }
+        } else if (lane == 0) {
+            const int pos = atomicAdd(&h->fb_count, 1);
+            fb_list[pos] = (int)q;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------
+struct WsLayout {
+    size_t packed_off, packed_bytes, fb_off, fb_bytes, total;
+    int64_t n_tiles, n_pad;
+};
+
+WsLayout ws_layout(int64_t N, int64_t M, int D)
+{
+    WsLayout L;
+    const int P = planes_for(D), TILE = tile_for(D);
+    L.n_tiles = (N + TILE - 1) / TILE;
+    L.n_pad = L.n_tiles * TILE;
+    L.packed_off = kHeaderBytes;
+    L.packed_bytes = (size_t)L.n_pad * P * 16;
+    L.fb_off = (L.packed_off + L.packed_bytes + 255) & ~(size_t)255;
+    L.fb_bytes = ((size_t)(M > 0 ? M : 1) * sizeof(int) + 255) & ~(size_t)255;
+    L.total = L.fb_off + L.fb_bytes;
+    return L;
+}
+
+Weights make_weights(const double *weights, int D)
+{
+    Weights w;
+    for (int d = 0; d < MPB_MAX_DIM; ++d) w.w[d] = (weights && d < D) ? weights[d] : 1.0;
+    return w;
+}
+
+int check_common(const char *who, const double *samples, int64_t N, const double *queries, int64_t M, int D, int k,
+                 const int64_t *out_idx)
+{
+    MPB_REQUIRE(D >= 1 && D <= MPB_MAX_DIM, "%s: dim %d outside [1, %d]", who, D, MPB_MAX_DIM);
+    MPB_REQUIRE(k >= 1 && k <= MPB_MAX_K, "%s: k %d outside [1, %d]", who, k, MPB_MAX_K);
+    MPB_REQUIRE(N >= 0 && M >= 0, "%s: negative size", who);
+    MPB_REQUIRE(N < 2147483647LL && M < 2147483647LL, "%s: more than 2^31-1 samples or queries", who);
+    MPB_REQUIRE(M == 0 || (queries && out_idx), "%s: NULL query or output buffer", who);
+    MPB_REQUIRE(N == 0 || samples, "%s: NULL sample buffer", who);
+    return MPB_OK;
+}
+
+int sm_count()
+{
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    return sms;
+}
+
+template <int D>
+int launch_exact(const double *x, int64_t N, const double *qs, int64_t M, const Weights &wt, int k, double r2,
+                 const int *list, const int *list_count, int64_t *out_idx, double *out_dist, int64_t *stats,
+                 cudaStream_t st)
+{
+    const int threads = 256;
+    int64_t blocks = list ? (int64_t)sm_count() * 4 : (M * 32 + threads - 1) / threads;
+    if (blocks > (int64_t)sm_count() * 32) blocks = (int64_t)sm_count() * 32;
+    if (blocks < 1) blocks = 1;
+    knn_exact_kernel<D><<<(unsigned)blocks, threads, 0, st>>>(x, N, qs, M, wt, k, r2, list, list_count, out_idx,
+                                                              out_dist, stats);
+    MPB_LAUNCH_CHECK();
+    return MPB_OK;
+}
+
+template <int D>
+int launch_prepare(const double *x, int64_t N, const Weights &wt, void *ws, cudaStream_t st)
+{
+    const WsLayout L = ws_layout(N, 0, D);
+    KnnHeader *h = reinterpret_cast<KnnHeader *>(ws);
+    float4 *packed = reinterpret_cast<float4 *>(reinterpret_cast<char *>(ws) + L.packed_off);
+    knn_init_kernel<<<1, 32, 0, st>>>(h);
+    MPB_LAUNCH_CHECK();
+    if (N > 0) {
+        int64_t blocks = (N + 255) / 256;
+        if (blocks > (int64_t)sm_count() * 8) blocks = (int64_t)sm_count() * 8;
+        knn_minmax_kernel<D><<<(unsigned)blocks, 256, 0, st>>>(x, N, wt, h);
+        MPB_LAUNCH_CHECK();
+    }
+    knn_finalize_kernel<<<1, 32, 0, st>>>(h, D);
+    MPB_LAUNCH_CHECK();
+    if (L.n_pad > 0) {
+        knn_pack_kernel<D><<<(unsigned)((L.n_pad + 255) / 256), 256, 0, st>>>(x, N, L.n_pad, wt, h, packed);
+        MPB_LAUNCH_CHECK();
+    }
+    return MPB_OK;
+}
+
+template <int D>
+int launch_search(const double *x, int64_t N, const double *qs, int64_t M, const Weights &wt, int k, double r2,
+                  void *ws, int64_t *out_idx, double *out_dist, int64_t *stats, cudaStream_t st)
+{
+    constexpr int Q = (D <= 8) ? 8 : 4;
+    using SM = FilterSmem<D, Q>;
+    const WsLayout L = ws_layout(N, M, D);
+    KnnHeader *h = reinterpret_cast<KnnHeader *>(ws);
+    const float4 *packed = reinterpret_cast<const float4 *>(reinterpret_cast<char *>(ws) + L.packed_off);
+    int *fb = reinterpret_cast<int *>(reinterpret_cast<char *>(ws) + L.fb_off);
+    MPB_CUDA_CHECK(cudaMemsetAsync(&h->fb_count, 0, sizeof(int), st));
+    MPB_CUDA_CHECK(cudaFuncSetAttribute(knn_filter_kernel<D, Q>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)SM::BYTES));
+    const int64_t blocks = (M + (int64_t)kWarps * Q - 1) / ((int64_t)kWarps * Q);
+    knn_filter_kernel<D, Q><<<(unsigned)blocks, kWarps * 32, SM::BYTES, st>>>(
+        x, N, qs, M, wt, k, r2, packed, (int)L.n_tiles, h, fb, out_idx, out_dist);
+    MPB_LAUNCH_CHECK();
+    return launch_exact<D>(x, N, qs, M, wt, k, r2, fb, &h->fb_count, out_idx, out_dist, stats, st);
+}
+
+int dispatch_exact(int D, const double *x, int64_t N, const double *qs, int64_t M, const Weights &wt, int k, double r2,
+                   int64_t *out_idx, double *out_dist, cudaStream_t st)
+{
+#define CALL(DD) launch_exact<DD>(x, N, qs, M, wt, k, r2, nullptr, nullptr, out_idx, out_dist, nullptr, st)
+    MPB_DISPATCH_DIM(D, CALL)
+#undef CALL
+    return MPB_EINVAL;
+}
+int dispatch_prepare(int D, const double *x, int64_t N, const Weights &wt, void *ws, cudaStream_t st)
+{
+#define CALL(DD) launch_prepare<DD>(x, N, wt, ws, st)
+    MPB_DISPATCH_DIM(D, CALL)
+#undef CALL
+    return MPB_EINVAL;
+}
+int dispatch_search(int D, const double *x, int64_t N, const double *qs, int64_t M, const Weights &wt, int k, double r2,
+                    void *ws, int64_t *out_idx, double *out_dist, int64_t *stats, cudaStream_t st)
+{
+#define CALL(DD) launch_search<DD>(x, N, qs, M, wt, k, r2, ws, out_idx, out_dist, stats, st)
+    MPB_DISPATCH_DIM(D, CALL)
+#undef CALL
+    return MPB_EINVAL;
+}
+
+}   // namespace
+
+MPB_API int mpb_knn_f64(const double *samples, int64_t n_samples, const double *queries, int64_t n_queries, int dim,
+                        const double *weights, int k, double max_dist, int64_t *out_idx, double *out_dist,
+                        void *stream)
+{
+    int rc = check_common("mpb_knn_f64", samples, n_samples, queries, n_queries, dim, k, out_idx);
+    if (rc != MPB_OK) return rc;
+    MPB_REQUIRE(max_dist >= 0., "mpb_knn_f64: max_dist must be >= 0");
+    if (n_queries == 0) return MPB_OK;
+    return dispatch_exact(dim, samples, n_samples, queries, n_queries, make_weights(weights, dim), k,
+                          max_dist * max_dist, out_idx, out_dist, (cudaStream_t)stream);
+}
+
+MPB_API size_t mpb_knn_workspace_bytes(int64_t n_samples, int64_t n_queries, int dim)
+{
+    if (dim < 1 || dim > MPB_MAX_DIM || n_samples < 0 || n_queries < 0) return 0;
+    return ws_layout(n_samples, n_queries, dim).total;
+}
+
+static int check_ws(const char *who, void *ws, size_t ws_bytes, int64_t N, int64_t M, int D)
+{
+    MPB_REQUIRE(ws != nullptr, "%s: workspace is NULL", who);
+    MPB_REQUIRE(((uintptr_t)ws & 255) == 0, "%s: workspace must be 256-byte aligned", who);
+    const size_t need = ws_layout(N, M, D).total;
+    if (ws_bytes < need) {
+        mpb_set_error("%s: workspace of %zu bytes is smaller than the %zu required", who, ws_bytes, need);
+        return MPB_ENOMEM;
+    }
+    return MPB_OK;
+}
+
+MPB_API int mpb_knn_prepare(const double *samples, int64_t n_samples, int dim, const double *weights, void *workspace,
+                            size_t workspace_bytes, void *stream)
+{
+    MPB_REQUIRE(dim >= 1 && dim <= MPB_MAX_DIM, "mpb_knn_prepare: dim %d outside [1, %d]", dim, MPB_MAX_DIM);
+    MPB_REQUIRE(n_samples >= 0 && n_samples < 2147483647LL, "mpb_knn_prepare: bad sample count");
+    MPB_REQUIRE(n_samples == 0 || samples, "mpb_knn_prepare: NULL sample buffer");
+    int rc = check_ws("mpb_knn_prepare", workspace, workspace_bytes, n_samples, 0, dim);
+    if (rc != MPB_OK) return rc;
+    return dispatch_prepare(dim, samples, n_samples, make_weights(weights, dim), workspace, (cudaStream_t)stream);
+}
+
+MPB_API int mpb_knn_search(const double *samples, int64_t n_samples, const double *queries, int64_t n_queries, int dim,
+                           const double *weights, int k, double max_dist, void *workspace, size_t workspace_bytes,
+                           int64_t *out_idx, double *out_dist, int64_t *stats, void *stream)
+{
+    int rc = check_common("mpb_knn_search", samples, n_samples, queries, n_queries, dim, k, out_idx);
+    if (rc != MPB_OK) return rc;
+    MPB_REQUIRE(max_dist >= 0., "mpb_knn_search: max_dist must be >= 0");
+    rc = check_ws("mpb_knn_search", workspace, workspace_bytes, n_samples, n_queries, dim);
+    if (rc != MPB_OK) return rc;
+    if (n_queries == 0) return MPB_OK;
+    return dispatch_search(dim, samples, n_samples, queries, n_queries, make_weights(weights, dim), k,
+                           max_dist * max_dist, workspace, out_idx, out_dist, stats, (cudaStream_t)stream);
+}
+
+MPB_API int mpb_knn_f32filter(const double *samples, int64_t n_samples, const double *queries, int64_t n_queries,
+                              int dim, const double *weights, int k, double max_dist, void *workspace,
+                              size_t workspace_bytes, int64_t *out_idx, double *out_dist, int64_t *stats, void *stream)
+{
+    int rc = check_common("mpb_knn_f32filter", samples, n_samples, queries, n_queries, dim, k, out_idx);
+    if (rc != MPB_OK) return rc;
+    rc = check_ws("mpb_knn_f32filter", workspace, workspace_bytes, n_samples, n_queries, dim);
+    if (rc != MPB_OK) return rc;
+    rc = mpb_knn_prepare(samples, n_samples, dim, weights, workspace, workspace_bytes, stream);
+    if (rc != MPB_OK) return rc;
+    return mpb_knn_search(samples, n_samples, queries, n_queries, dim, weights, k, max_dist, workspace, workspace_bytes,
+                          out_idx, out_dist, stats, stream);
+}

@@ -1,0 +1,160 @@
+// Shared helpers for the mpb200 kernels: error reporting, exact-rounding fp64 primitives,
+// mbarrier / bulk-copy PTX wrappers (sm_100a).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/mpb200.h"
+
+#define MPB_API extern "C" __attribute__((visibility("default")))
+
+void mpb_set_error(const char *fmt, ...);
+
+#define MPB_CUDA_CHECK(expr)                                                                   \
+    do {                                                                                       \
+        cudaError_t _e = (expr);                                                               \
+        if (_e != cudaSuccess) {                                                               \
+            mpb_set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__,    \
+                          __LINE__);                                                           \
+            return MPB_ECUDA;                                                                  \
+        }                                                                                      \
+    } while (0)
+
+#define MPB_REQUIRE(cond, ...)                                                                 \
+    do {                                                                                       \
+        if (!(cond)) {                                                                         \
+            mpb_set_error(__VA_ARGS__);                                                        \
+            return MPB_EINVAL;                                                                 \
+        }                                                                                      \
+    } while (0)
+
+#define MPB_LAUNCH_CHECK()                                                                     \
+    do {                                                                                       \
+        cudaError_t _e = cudaGetLastError();                                                   \
+        if (_e != cudaSuccess) {                                                               \
+            mpb_set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e),         \
+                          __FILE__, __LINE__);                                                 \
+            return MPB_ECUDA;                                                                  \
+        }                                                                                      \
+    } while (0)
+
+// Device-side view of an obstacle set.  Bounds are already inflated.
+struct WorldDev {
+    int dim, n_box, n_sph;
+    const double *box_lo;   // [n_box, dim]  lower - buffer
+    const double *box_hi;   // [n_box, dim]  upper + buffer
+    const double *sph_c;    // [n_sph, dim]
+    const double *sph_rb;   // [n_sph]       radius + buffer
+    const double *env_lo;   // [dim]
+    const double *env_hi;   // [dim]
+};
+
+struct mpb_world {
+    WorldDev dev;
+    void *blob;    // single device allocation backing every array above
+    int device;
+};
+
+// ---- exactly rounded fp64 steps (never contracted into FMA) -------------------------------
+__device__ __forceinline__ double d_sub(double a, double b) { return __dsub_rn(a, b); }
+__device__ __forceinline__ double d_add(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ double d_mul(double a, double b) { return __dmul_rn(a, b); }
+
+// cKDTree's squared distance between embedded points held in registers.
+template <int D>
+__device__ __forceinline__ double sqdist_kdtree(const double (&u)[D], const double (&v)[D])
+{
+    double a0 = 0., a1 = 0., a2 = 0., a3 = 0.;
+    constexpr int NB = D / 4;
+#pragma unroll
+    for (int b = 0; b < NB; ++b) {
+        double d0 = d_sub(u[4 * b + 0], v[4 * b + 0]);
+        double d1 = d_sub(u[4 * b + 1], v[4 * b + 1]);
+        double d2 = d_sub(u[4 * b + 2], v[4 * b + 2]);
+        double d3 = d_sub(u[4 * b + 3], v[4 * b + 3]);
+        a0 = d_add(a0, d_mul(d0, d0));
+        a1 = d_add(a1, d_mul(d1, d1));
+        a2 = d_add(a2, d_mul(d2, d2));
+        a3 = d_add(a3, d_mul(d3, d3));
+    }
+    double s = d_add(d_add(d_add(a0, a1), a2), a3);
+#pragma unroll
+    for (int i = 4 * NB; i < D; ++i) {
+        double d = d_sub(u[i], v[i]);
+        s = d_add(s, d_mul(d, d));
+    }
+    return s;
+}
+
+// ---- mbarrier + 1-D bulk async copy (TMA engine, no tensor map) ---------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p)
+{
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init()
+{
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity)
+{
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+// Bounded wait: a barrier that never completes traps instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
+{
+    for (uint32_t spins = 0; !mbar_try_wait(bar, parity); ++spins) {
+        if (spins > (1u << 26)) __trap();
+    }
+}
+__device__ __forceinline__ void bulk_copy_g2s(void *smem_dst, const void *gmem_src, uint32_t bytes, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+// Runtime dimension -> template instantiation.  CALL(D) must be an int-returning expression.
+#define MPB_DISPATCH_DIM(dim, CALL)                                                            \
+    switch (dim) {                                                                             \
+        case 1: return CALL(1);                                                                \
+        case 2: return CALL(2);                                                                \
+        case 3: return CALL(3);                                                                \
+        case 4: return CALL(4);                                                                \
+        case 5: return CALL(5);                                                                \
+        case 6: return CALL(6);                                                                \
+        case 7: return CALL(7);                                                                \
+        case 8: return CALL(8);                                                                \
+        case 9: return CALL(9);                                                                \
+        case 10: return CALL(10);                                                              \
+        case 11: return CALL(11);                                                              \
+        case 12: return CALL(12);                                                              \
+        case 13: return CALL(13);                                                              \
+        case 14: return CALL(14);                                                              \
+        case 15: return CALL(15);                                                              \
+        case 16: return CALL(16);                                                              \
+        default: break;                                                                        \
+    }

@@ -1,0 +1,59 @@
+"""CPU-side checks of the C-ABI library: it loads and exports every symbol include/mpb200.h declares.
+No compute call is made here (no GPU in this tier)."""
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    text = open(os.path.join(ROOT, "include", "mpb200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(mpb_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_declares_entry_points():
+    names = _declared()
+    for must in ("mpb_world_create", "mpb_points_check", "mpb_edges_check", "mpb_edges_check_pairs",
+                 "mpb_knn_f64", "mpb_knn_f32filter", "mpb_trees_nearest", "mpb_scan_nearest_radius"):
+        assert must in names
+
+
+def test_library_exports_every_declared_symbol():
+    from motion_planners_b200 import _lib
+    if not os.path.exists(_lib.LIB_PATH):
+        import __graft_entry__
+        __graft_entry__.build()
+    lib = _lib.lib()
+    for name in _declared():
+        assert hasattr(lib, name), name
+    # the binding table mirrors the header one to one
+    assert sorted(_lib.SIGNATURES) == _declared()
+    assert lib.mpb_version() == 1
+
+
+def test_bad_arguments_are_rejected_without_a_gpu():
+    from motion_planners_b200 import _lib
+    lib = _lib.lib()
+    # sizes/dims are validated before any CUDA call
+    assert lib.mpb_knn_workspace_bytes(1000, 10, 0) == 0
+    assert lib.mpb_knn_workspace_bytes(1000, 10, 17) == 0
+    assert lib.mpb_knn_workspace_bytes(1000, 10, 7) > 1000 * 32
+    rc = lib.mpb_knn_f64(None, 10, None, 10, 99, None, 3, 1.0, None, None, None)
+    assert rc == -22 and b"dim" in lib.mpb_last_error()
+    rc = lib.mpb_knn_f64(None, 10, None, 10, 3, None, 33, 1.0, None, None, None)
+    assert rc == -22 and b"k" in lib.mpb_last_error()
+    rc = lib.mpb_points_check(None, None, 5, None, None)
+    assert rc == -22
+
+
+def test_product_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "motion_planners_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), f
+                assert "mp_oracle" not in src, f
