@@ -1,0 +1,371 @@
+#!/usr/bin/env python
+"""bench.py -- one JSON line for the kNN + edge-collision hot path (BASELINE.json's metric).
+
+    python bench.py --gpus 1 --steps K --warmup W                       (single GPU)
+    python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N --steps K --warmup W
+    python bench.py --impl reference ...                                (CPU arm: the oracle port)
+
+A step = one pass of the hot path over one synthetic roadmap: [all-gather of the sample shards when
+N > 1] -> kNN (k+1 = 11) of every sample of this rank's shard against the global set -> collision_fn
+on the shard's vertices -> extend_fn + collision_fn on every directed sample->neighbour edge.
+`value` = directed edges collision-checked per second over the whole step, all ranks, inputs resident
+in HBM; `knn_queries_per_s` is the same step's query rate.  `e2e` times the same pass through the
+host-buffer API (pinned host samples in, neighbour matrix and flags back on the host).
+"""
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+METRIC = "PRM edges collision-checked/sec (kNN k=10 + vertex + edge checks per roadmap build step)"
+UNIT = "edges/s"
+
+WORKLOADS = {
+    # name -> (world factory name, dim, n_samples, k, description)
+    "c2": ("c2_world", 6, 100000, 10, "configs[1]: lazy-PRM roadmap, 100k samples, 6-DoF unit cube, 64 random boxes, k=10"),
+    "c4lite": ("c4lite_world", 7, 1000000, 10, "configs[3] with reference primitives: 1M samples, 7-DoF, 256 C-space boxes, k=10"),
+    "c1": ("c1", 2, 2000, 10, "configs[0]: 2-D demo fixture, 2k samples, k=10"),
+}
+
+
+def make_workload(name):
+    from motion_planners_b200 import workloads
+    fac, dim, n, k, desc = WORKLOADS[name]
+    world = workloads.problem1_world()[0] if name == "c1" else getattr(workloads, fac)()
+    X = workloads.uniform_samples(n, dim, seed=0)
+    return world, X, k, desc
+
+
+# ------------------------------------------------------------------------------------------ clocks
+class ClockSampler(object):
+    """Samples SM clock and throttle reasons of one GPU every 100 ms while the timed region runs."""
+
+    def __init__(self, index):
+        self.index = index
+        self.samples, self.reasons = [], set()
+        self.max_mhz = None
+        self._stop = threading.Event()
+        self._thread = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        names = {
+            "hw_slowdown": getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8),
+            "hw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
+            "sw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20),
+            "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4),
+        }
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for n, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(n)
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+
+    def start(self):
+        if self.nv is not None:
+            self._thread = threading.Thread(target=self._run, daemon=True)
+            self._thread.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._thread is not None:
+            self._thread.join(timeout=2)
+        return {"sm_mhz": statistics.median(self.samples) if self.samples else None,
+                "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# --------------------------------------------------------------------------------------- CPU arms
+def cpu_sample_rate(world, X, k, budget_s=12.0, first=4000):
+    """The oracle port on a bounded sample: the first `first` queries (grown until ~budget_s of CPU work)."""
+    from oracle import cpu_baseline
+    from scipy.spatial import KDTree
+    n = X.shape[0]
+    t0 = time.perf_counter()
+    tree = KDTree(X)
+    build_s = time.perf_counter() - t0
+    hi = min(first, n)
+    r = cpu_baseline.native_port_step(world, X, 0, hi, k, tree=tree)
+    while r["seconds"] < budget_s / 4 and hi < n:
+        hi = min(n, hi * 4)
+        r = cpu_baseline.native_port_step(world, X, 0, hi, k, tree=tree)
+    r["tree_build_s"] = build_s
+    r["hi"] = hi
+    return r
+
+
+def run_reference_arm(args, rank):
+    """`--impl reference`: the reference's CPU path (oracle port: scipy cKDTree on all cores + the C oracle
+    under OpenMP) on the same workload; each step is a bounded sample of it."""
+    if rank != 0:
+        return 0
+    from oracle import cpu_baseline
+    from scipy.spatial import KDTree
+    world, X, k, desc = make_workload(args.workload)
+    n = X.shape[0]
+    tree = KDTree(X)
+    sample = min(n, args.ref_sample)
+    for _ in range(args.warmup):
+        cpu_baseline.native_port_step(world, X, 0, min(sample, 2000), k, tree=tree)
+    secs, edges, queries = 0.0, 0, 0
+    for s in range(args.steps):
+        lo = (s * sample) % max(1, n - sample + 1)
+        r = cpu_baseline.native_port_step(world, X, lo, lo + sample, k, tree=tree)
+        secs += r["seconds"]
+        edges += r["n_edges"]
+        queries += r["n_queries"]
+    value = edges / secs
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "knn_queries_per_s": queries / secs,
+        "config": {"workload": args.workload, "description": desc, "n_samples": n, "dim": X.shape[1], "k": k,
+                   "n_box": world.n_box, "n_sph": world.n_sph},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cpu_baseline.cores(), "kind": "port",
+                         "sample": "%d of %d queries and their %d directed edges per step; kd-tree built once, "
+                                   "untimed" % (sample, n, sample * k)},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------------------------------- main
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default=os.environ.get("MPB_BENCH_WORKLOAD", "c2"), choices=sorted(WORKLOADS))
+    ap.add_argument("--ref-sample", type=int, default=100000)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the extra 1M-sample measurement")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world_size = int(os.environ.get("WORLD_SIZE", "1"))
+
+    if args.impl == "reference":
+        return run_reference_arm(args, rank)
+
+    import torch
+    import torch.distributed as dist
+    from motion_planners_b200 import ops
+    from motion_planners_b200.roadmap import DeviceRoadmap, shard_bounds
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU path); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local_rank)
+    if world_size > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    assert world_size == args.gpus or world_size == 1, "launch with torchrun for --gpus > 1"
+
+    def barrier():
+        if world_size > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def measure(workload, steps, warmup, with_e2e):
+        world, X, k, desc = make_workload(workload)
+        n, D = X.shape
+        lo, hi = shard_bounds(n, world_size, rank)
+        equal = (n % world_size == 0)
+        local = torch.from_numpy(X[lo:hi]).cuda()
+        gathered_buf = torch.empty((n, D), dtype=torch.float64, device="cuda") if world_size > 1 else None
+        rm = DeviceRoadmap(world, k=k)
+        flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")   # > 126 MB of L2
+
+        def step():
+            if world_size > 1 and equal:
+                rm.build(local, gathered=rm.gather_samples_equal(local, gathered_buf))
+            else:
+                rm.build(local)
+
+        for _ in range(max(warmup, 3)):
+            step()
+        barrier()
+        sampler = ClockSampler(local_rank)
+        sampler.start()
+        rm.profile = True
+        total_ms, phase = 0.0, {}
+        barrier()
+        wall0 = time.perf_counter()
+        for _ in range(steps):
+            flush.zero_()                                           # evict the inputs from L2 (untimed)
+            e0 = torch.cuda.Event(enable_timing=True)
+            e1 = torch.cuda.Event(enable_timing=True)
+            if world_size > 1:
+                dist.barrier()
+            e0.record()
+            step()
+            e1.record()
+            e1.synchronize()
+            total_ms += e0.elapsed_time(e1)
+            for name, ms in rm.phase_ms().items():
+                phase[name] = phase.get(name, 0.0) + ms
+        barrier()
+        wall_s = time.perf_counter() - wall0
+        clocks = sampler.stop()
+        rm.profile = False
+        t = torch.tensor([total_ms], device="cuda", dtype=torch.float64)
+        if world_size > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)                # max over ranks
+        total_ms = float(t.item())
+        edges_local = torch.tensor([rm.n_edges_checked()], device="cuda", dtype=torch.int64)
+        fb = rm.stats[:1].clone()
+        if world_size > 1:
+            dist.all_reduce(edges_local)
+            dist.all_reduce(fb)
+        edges_total = int(edges_local.item())
+        ms_step = total_ms / steps
+        out = {"world": world, "X": X, "k": k, "desc": desc, "n": n, "D": D, "ms_step": ms_step,
+               "edges": edges_total, "value": edges_total / (ms_step * 1e-3), "qps": n / (ms_step * 1e-3),
+               "phase_ms": {a: b / steps for a, b in phase.items()}, "clocks": clocks, "launches": rm.launches,
+               "fallback_queries": int(fb.item()), "n_local": hi - lo, "wall_s": wall_s}
+
+        if with_e2e:
+            pinned = torch.from_numpy(np.ascontiguousarray(X[lo:hi])).pin_memory()
+            rm2 = DeviceRoadmap(world, k=k)
+            if world_size == 1:
+                for _ in range(2):
+                    rm2.build_from_host(pinned)
+                barrier()
+                t0 = time.perf_counter()
+                for _ in range(steps):
+                    res = rm2.build_from_host(pinned)
+                torch.cuda.synchronize()
+                e2e_s = (time.perf_counter() - t0) / steps
+            else:
+                def e2e_step():
+                    dev = pinned.cuda(non_blocking=True)
+                    rm2.build(dev, gathered=rm2.gather_samples_equal(dev, gathered_buf) if equal else None)
+                    return rm2.nbr_idx.cpu(), rm2.vertex_hit.cpu(), rm2.edge_hit.cpu()
+                for _ in range(2):
+                    e2e_step()
+                barrier()
+                t0 = time.perf_counter()
+                for _ in range(steps):
+                    res = e2e_step()
+                barrier()
+                e2e_s = (time.perf_counter() - t0) / steps
+                ts = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
+                dist.all_reduce(ts, op=dist.ReduceOp.MAX)
+                e2e_s = float(ts.item())
+            out["e2e"] = {"value": edges_total / e2e_s, "unit": UNIT, "ms_per_step": 1e3 * e2e_s,
+                          "h2d_bytes_per_step": int(pinned.numel() * 8) * world_size,
+                          "d2h_bytes_per_step": int(sum(r.numel() * r.element_size() for r in res)) * world_size,
+                          "knn_queries_per_s": n / e2e_s}
+        del flush
+        return out
+
+    m = measure(args.workload, args.steps, args.warmup, with_e2e=True)
+
+    # ---- roofline of the dominant kernel (the fp32 filter pass of the kNN)
+    peaks_file = {}
+    try:
+        peaks_file = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    fp32_peak = ops.peak_fma(torch.float32)
+    fp64_peak = ops.peak_fma(torch.float64)
+    n, D, k = m["n"], m["D"], m["k"]
+    knn_ms = m["phase_ms"].get("knn", float("nan"))
+    fma_flops = 2.0 * D * float(m["n_local"]) * n            # one FFMA per dimension per (query, sample) pair
+    achieved = fma_flops / (knn_ms * 1e-3)
+    hbm_peak = peaks_file.get("hbm_gbs")
+    # algorithmic HBM bytes of the step: samples in (fp64), packed tiles out+in once, neighbour matrix
+    # (idx + dist) out and idx back in for the edge pass, flags out
+    step_bytes = m["n_local"] * (D * 8 + (k + 1) * (8 + 8 + 8 + 4) + 1) + n * (D * 8 + 2 * 32)
+    roofline = {
+        "kernel": "knn_filter_kernel", "bound": "fp32", "achieved": achieved / 1e12, "peak": fp32_peak / 1e12,
+        "unit": "TFLOP/s", "frac": achieved / fp32_peak,
+        "peak_source": "measured live: mpb_peak_fma_f32 micro-benchmark on this GPU (MEASURED_PEAKS.json carries "
+                       "only HBM and bf16 tensor peaks; nominal fp32 = 148 SM x 128 lanes x 2 x 1.965 GHz = 74.4)",
+        "flops_per_pair": 2 * D, "survey_flops_per_pair": 3 * D,
+        "frac_on_survey_count": (3.0 * D * m["n_local"] * n / (knn_ms * 1e-3)) / fp32_peak,
+        "traffic": None,
+        "kernel_ms": knn_ms,
+        "hbm": {"achieved_gbs": step_bytes / (m["ms_step"] * 1e-3) / 1e9, "peak_gbs": hbm_peak,
+                "frac": (step_bytes / (m["ms_step"] * 1e-3) / 1e9 / hbm_peak) if hbm_peak else None,
+                "note": "whole step, algorithmic bytes; the path is FMA-pipe bound, not HBM bound"},
+        "fp64_fma_peak_tflops": fp64_peak / 1e12,
+    }
+
+    line = {
+        "metric": METRIC, "value": m["value"], "unit": UNIT, "n_gpus": world_size, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": m["ms_step"], "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f64 (fp32 filter pass inside the kNN, results bit-exact to the fp64 reference)",
+        "data": "synthetic", "knn_queries_per_s": m["qps"],
+        "config": {"workload": args.workload, "description": m["desc"], "n_samples": n, "dim": D, "k": k,
+                   "n_box": m["world"].n_box, "n_sph": m["world"].n_sph, "edges_per_step": m["edges"],
+                   "sharding": "samples sharded over ranks, one NCCL all-gather per step, edges stay sharded",
+                   "l2": "flushed between timed steps (256 MiB write, untimed); inputs are smaller than L2"},
+        "phases_ms": m["phase_ms"],
+        "kernel_rates": {"knn_queries_per_s": m["n_local"] * world_size / (knn_ms * 1e-3),
+                         "edges_per_s": m["edges"] / (m["phase_ms"].get("edges", float("nan")) * 1e-3)},
+        "fallback_queries": m["fallback_queries"],
+        "roofline": roofline, "clocks": m["clocks"], "e2e": m["e2e"], "gpu_launches": m["launches"] * args.steps,
+        "wall_s_timed_region": m["wall_s"],
+    }
+
+    if rank == 0 and world_size == 1 and not args.no_cpu_baseline:
+        from oracle import cpu_baseline
+        r = cpu_sample_rate(m["world"], m["X"], k)
+        line["cpu_baseline"] = {
+            "value": r["n_edges"] / r["seconds"], "unit": UNIT, "cores": cpu_baseline.cores(), "kind": "port",
+            "knn_queries_per_s": r["n_queries"] / r["seconds"],
+            "sample": "first %d of %d queries and their %d directed edges (scipy cKDTree batched on all cores + "
+                      "C oracle under OpenMP); kd-tree build %.2f s untimed" % (r["hi"], n, r["n_edges"],
+                                                                                r["tree_build_s"]),
+        }
+        p = cpu_baseline.python_port_step(m["world"], m["X"], 0, 40, k)
+        line["cpu_baseline"]["python_port"] = {
+            "value": p["n_edges"] / p["seconds"], "unit": UNIT, "cores": 1,
+            "sample": "first 40 queries, %d edges, per-call Python structure of the reference" % p["n_edges"]}
+
+    if not args.no_extra and args.workload == "c2":
+        x = measure("c4lite", max(2, min(args.steps, 3)), 3, with_e2e=False)
+        x_knn = x["phase_ms"].get("knn", float("nan"))
+        line["extra_c4lite"] = {
+            "description": x["desc"], "ms_per_step": x["ms_step"], "edges_per_s": x["value"],
+            "knn_queries_per_s": x["qps"], "edges_per_step": x["edges"], "phases_ms": x["phase_ms"],
+            "knn_fp32_frac": (2.0 * x["D"] * x["n_local"] * x["n"] / (x_knn * 1e-3)) / fp32_peak,
+            "fallback_queries": x["fallback_queries"], "clocks": x["clocks"]}
+
+    if rank == 0:
+        print(json.dumps(line))
+    if world_size > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

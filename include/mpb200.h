@@ -78,7 +78,9 @@ int mpb_points_check(const mpb_world *world, const double *q, int64_t n, uint8_t
 #define MPB_EDGE_ANY 0
 #define MPB_EDGE_FIRST 1
 #define MPB_EDGE_LAST 2
-/* edges as index pairs into a sample table: samples dev [N, dim] f64, src/dst dev [E] i64 */
+/* edges as index pairs into a sample table: samples dev [N, dim] f64, src/dst dev [E] i64.
+ * A pair with a negative index (the "no neighbour" slot of a kNN row) is skipped:
+ * out_hit = -1, out_n = 0. */
 int mpb_edges_check(const mpb_world *world, const double *samples, int64_t n_samples,
                     const int64_t *src, const int64_t *dst, int64_t n_edges, double step, int mode,
                     int skip_last, int32_t *out_hit, int32_t *out_n, void *stream);
@@ -86,6 +88,9 @@ int mpb_edges_check(const mpb_world *world, const double *samples, int64_t n_sam
 int mpb_edges_check_pairs(const mpb_world *world, const double *q1, const double *q2,
                           int64_t n_edges, double step, int mode, int skip_last, int32_t *out_hit,
                           int32_t *out_n, void *stream);
+/* Waypoint counts only: out_n[e] = int(max_d |(q2-q1)/step|) + 1 (tkinter/samplers.py:119-120). */
+int mpb_edges_count(const double *q1, const double *q2, int64_t n_edges, int dim, double step,
+                    int32_t *out_n, void *stream);
 /* The waypoints themselves (extend_fn output) for one edge batch, for callers that need
  * the path (lazy_prm.py:223-230 get_path, prm.py:51-58 Edge.path): offsets dev [E+1] i64 is
  * the exclusive prefix sum of the counts from out_n; out dev [offsets[E], dim] f64. */
@@ -107,6 +112,15 @@ int mpb_edges_waypoints(const double *q1, const double *q2, int64_t n_edges, int
 int mpb_knn_f64(const double *samples, int64_t n_samples, const double *queries, int64_t n_queries,
                 int dim, const double *weights, int k, double max_dist, int64_t *out_idx,
                 double *out_dist, void *stream);
+
+/* The same exact scan under any of the reference's distance procedures (MPB_METRIC_* below).  For
+ * the non-kd-tree metrics the ranking key is the ROUNDED distance distance_fn returns (the reference
+ * sorts on that value: prm.py:244-246 sorted(...), nearest.py:102-109 BruteForceNeighbors), ties to the
+ * smaller index (Python's sort is stable), and a neighbour is kept iff distance <= max_dist
+ * (prm.py:244 connect_distance filter).  metric = MPB_METRIC_KDTREE is mpb_knn_f64. */
+int mpb_knn_f64_metric(const double *samples, int64_t n_samples, const double *queries,
+                       int64_t n_queries, int dim, const double *weights, int metric, int k,
+                       double max_dist, int64_t *out_idx, double *out_dist, void *stream);
 
 /* Tiled fp32 filter + fp64 re-rank, same results bit for bit: an fp32 pass over
  * shared-memory tiles keeps 32 candidates per query, the exact fp64 keys of those

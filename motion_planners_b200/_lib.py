@@ -30,8 +30,10 @@ SIGNATURES = {
     "mpb_points_check": (c_int, [c_vp, c_vp, c_i64, c_vp, c_vp]),
     "mpb_edges_check": (c_int, [c_vp, c_vp, c_i64, c_vp, c_vp, c_i64, c_dbl, c_int, c_int, c_vp, c_vp, c_vp]),
     "mpb_edges_check_pairs": (c_int, [c_vp, c_vp, c_vp, c_i64, c_dbl, c_int, c_int, c_vp, c_vp, c_vp]),
+    "mpb_edges_count": (c_int, [c_vp, c_vp, c_i64, c_int, c_dbl, c_vp, c_vp]),
     "mpb_edges_waypoints": (c_int, [c_vp, c_vp, c_i64, c_int, c_dbl, c_vp, c_vp, c_vp]),
     "mpb_knn_f64": (c_int, [c_vp, c_i64, c_vp, c_i64, c_int, c_hostf64, c_int, c_dbl, c_vp, c_vp, c_vp]),
+    "mpb_knn_f64_metric": (c_int, [c_vp, c_i64, c_vp, c_i64, c_int, c_hostf64, c_int, c_int, c_dbl, c_vp, c_vp, c_vp]),
     "mpb_knn_workspace_bytes": (c_sz, [c_i64, c_i64, c_int]),
     "mpb_knn_prepare": (c_int, [c_vp, c_i64, c_int, c_hostf64, c_vp, c_sz, c_vp]),
     "mpb_knn_search": (c_int, [c_vp, c_i64, c_vp, c_i64, c_int, c_hostf64, c_int, c_dbl, c_vp, c_sz, c_vp, c_vp,

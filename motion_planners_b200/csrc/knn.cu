@@ -27,10 +27,6 @@ constexpr int kStages = 4;         // shared-memory ring depth
 constexpr int kListLen = 32;       // candidates kept per query (one per lane)
 constexpr int kHeaderBytes = 512;
 
-struct Weights {
-    double w[MPB_MAX_DIM];
-};
-
 struct KnnHeader {
     unsigned long long mm[2 * MPB_MAX_DIM];   // order-encoded min [0,16) and max [16,32)
     double center[MPB_MAX_DIM];
@@ -158,7 +154,7 @@ __global__ void __launch_bounds__(256)
 template <int D>
 __global__ void __launch_bounds__(256)
     knn_exact_kernel(const double *__restrict__ x, int64_t N, const double *__restrict__ qs, int64_t M, Weights wt,
-                     int k, double r2, const int *__restrict__ list, const int *__restrict__ list_count,
+                     int metric, int k, double lim, const int *__restrict__ list, const int *__restrict__ list_count,
                      int64_t *__restrict__ out_idx, double *__restrict__ out_dist, int64_t *__restrict__ stats)
 {
     const int lane = threadIdx.x & 31;
@@ -169,9 +165,14 @@ __global__ void __launch_bounds__(256)
 
     for (int64_t it = warp0; it < total; it += nwarps) {
         const int64_t q = list ? (int64_t)list[it] : it;
-        double eq[D];
+        // ranking key: the kd-tree's squared distance, or (other metrics) the rounded distance itself,
+        // because the reference sorts / arg-mins on distance_fn's return value
+        double eq[D], qr[D];
 #pragma unroll
-        for (int d = 0; d < D; ++d) eq[d] = d_mul(wt.w[d], qs[q * D + d]);
+        for (int d = 0; d < D; ++d) {
+            qr[d] = qs[q * D + d];
+            eq[d] = d_mul(wt.w[d], qr[d]);
+        }
         double lk = INFINITY, thr = INFINITY;
         int li = -1;
         for (int64_t j0 = 0; j0 < N; j0 += 32) {
@@ -179,9 +180,15 @@ __global__ void __launch_bounds__(256)
             double S = INFINITY;
             if (j < N) {
                 double ex[D];
+                if (metric == MPB_METRIC_KDTREE) {
 #pragma unroll
-                for (int d = 0; d < D; ++d) ex[d] = d_mul(wt.w[d], x[j * D + d]);
-                S = sqdist_kdtree<D>(eq, ex);
+                    for (int d = 0; d < D; ++d) ex[d] = d_mul(wt.w[d], x[j * D + d]);
+                    S = sqdist_kdtree<D>(eq, ex);
+                } else {
+#pragma unroll
+                    for (int d = 0; d < D; ++d) ex[d] = x[j * D + d];
+                    S = metric_dist<D>(qr, ex, wt, metric);
+                }
             }
             unsigned m = __ballot_sync(FULL_MASK, S < thr);
             while (m) {
@@ -205,9 +212,10 @@ __global__ void __launch_bounds__(256)
             }
         }
         if (lane < k) {
-            const bool keep = (li >= 0) && (lk < r2);
+            const bool kd = (metric == MPB_METRIC_KDTREE);
+            const bool keep = (li >= 0) && (kd ? (lk < lim) : (lk <= lim));
             out_idx[q * k + lane] = keep ? (int64_t)li : -1;
-            if (out_dist) out_dist[q * k + lane] = keep ? __dsqrt_rn(lk) : INFINITY;
+            if (out_dist) out_dist[q * k + lane] = keep ? (kd ? __dsqrt_rn(lk) : lk) : INFINITY;
         }
     }
 }
@@ -436,13 +444,6 @@ WsLayout ws_layout(int64_t N, int64_t M, int D)
     return L;
 }
 
-Weights make_weights(const double *weights, int D)
-{
-    Weights w;
-    for (int d = 0; d < MPB_MAX_DIM; ++d) w.w[d] = (weights && d < D) ? weights[d] : 1.0;
-    return w;
-}
-
 int check_common(const char *who, const double *samples, int64_t N, const double *queries, int64_t M, int D, int k,
                  const int64_t *out_idx)
 {
@@ -463,16 +464,16 @@ int sm_count()
 }
 
 template <int D>
-int launch_exact(const double *x, int64_t N, const double *qs, int64_t M, const Weights &wt, int k, double r2,
-                 const int *list, const int *list_count, int64_t *out_idx, double *out_dist, int64_t *stats,
-                 cudaStream_t st)
+int launch_exact(const double *x, int64_t N, const double *qs, int64_t M, const Weights &wt, int metric, int k,
+                 double lim, const int *list, const int *list_count, int64_t *out_idx, double *out_dist,
+                 int64_t *stats, cudaStream_t st)
 {
     const int threads = 256;
     int64_t blocks = list ? (int64_t)sm_count() * 4 : (M * 32 + threads - 1) / threads;
     if (blocks > (int64_t)sm_count() * 32) blocks = (int64_t)sm_count() * 32;
     if (blocks < 1) blocks = 1;
-    knn_exact_kernel<D><<<(unsigned)blocks, threads, 0, st>>>(x, N, qs, M, wt, k, r2, list, list_count, out_idx,
-                                                              out_dist, stats);
+    knn_exact_kernel<D><<<(unsigned)blocks, threads, 0, st>>>(x, N, qs, M, wt, metric, k, lim, list, list_count,
+                                                              out_idx, out_dist, stats);
     MPB_LAUNCH_CHECK();
     return MPB_OK;
 }
@@ -517,13 +518,13 @@ int launch_search(const double *x, int64_t N, const double *qs, int64_t M, const
     knn_filter_kernel<D, Q><<<(unsigned)blocks, kWarps * 32, SM::BYTES, st>>>(
         x, N, qs, M, wt, k, r2, packed, (int)L.n_tiles, h, fb, out_idx, out_dist);
     MPB_LAUNCH_CHECK();
-    return launch_exact<D>(x, N, qs, M, wt, k, r2, fb, &h->fb_count, out_idx, out_dist, stats, st);
+    return launch_exact<D>(x, N, qs, M, wt, MPB_METRIC_KDTREE, k, r2, fb, &h->fb_count, out_idx, out_dist, stats, st);
 }
 
-int dispatch_exact(int D, const double *x, int64_t N, const double *qs, int64_t M, const Weights &wt, int k, double r2,
-                   int64_t *out_idx, double *out_dist, cudaStream_t st)
+int dispatch_exact(int D, const double *x, int64_t N, const double *qs, int64_t M, const Weights &wt, int metric, int k,
+                   double lim, int64_t *out_idx, double *out_dist, cudaStream_t st)
 {
-#define CALL(DD) launch_exact<DD>(x, N, qs, M, wt, k, r2, nullptr, nullptr, out_idx, out_dist, nullptr, st)
+#define CALL(DD) launch_exact<DD>(x, N, qs, M, wt, metric, k, lim, nullptr, nullptr, out_idx, out_dist, nullptr, st)
     MPB_DISPATCH_DIM(D, CALL)
 #undef CALL
     return MPB_EINVAL;
@@ -554,8 +555,22 @@ MPB_API int mpb_knn_f64(const double *samples, int64_t n_samples, const double *
     if (rc != MPB_OK) return rc;
     MPB_REQUIRE(max_dist >= 0., "mpb_knn_f64: max_dist must be >= 0");
     if (n_queries == 0) return MPB_OK;
-    return dispatch_exact(dim, samples, n_samples, queries, n_queries, make_weights(weights, dim), k,
-                          max_dist * max_dist, out_idx, out_dist, (cudaStream_t)stream);
+    return dispatch_exact(dim, samples, n_samples, queries, n_queries, make_weights(weights, dim), MPB_METRIC_KDTREE,
+                          k, max_dist * max_dist, out_idx, out_dist, (cudaStream_t)stream);
+}
+
+MPB_API int mpb_knn_f64_metric(const double *samples, int64_t n_samples, const double *queries, int64_t n_queries,
+                               int dim, const double *weights, int metric, int k, double max_dist, int64_t *out_idx,
+                               double *out_dist, void *stream)
+{
+    int rc = check_common("mpb_knn_f64_metric", samples, n_samples, queries, n_queries, dim, k, out_idx);
+    if (rc != MPB_OK) return rc;
+    MPB_REQUIRE(metric >= 0 && metric <= 2, "mpb_knn_f64_metric: bad metric %d", metric);
+    MPB_REQUIRE(max_dist >= 0., "mpb_knn_f64_metric: max_dist must be >= 0");
+    if (n_queries == 0) return MPB_OK;
+    const double lim = (metric == MPB_METRIC_KDTREE) ? max_dist * max_dist : max_dist;
+    return dispatch_exact(dim, samples, n_samples, queries, n_queries, make_weights(weights, dim), metric, k, lim,
+                          out_idx, out_dist, (cudaStream_t)stream);
 }
 
 MPB_API size_t mpb_knn_workspace_bytes(int64_t n_samples, int64_t n_queries, int dim)

@@ -88,6 +88,51 @@ __device__ __forceinline__ double sqdist_kdtree(const double (&u)[D], const doub
     return s;
 }
 
+// ---- weights and the reference's three distance roundings --------------------------------
+struct Weights {
+    double w[MPB_MAX_DIM];
+};
+
+inline Weights make_weights(const double *weights, int D)
+{
+    Weights w;
+    for (int d = 0; d < MPB_MAX_DIM; ++d) w.w[d] = (weights && d < D) ? weights[d] : 1.0;
+    return w;
+}
+
+// The reference's three roundings of the weighted Euclidean distance.
+template <int D>
+__device__ __forceinline__ double metric_dist(const double (&a)[D], const double (&b)[D], const Weights &wt, int metric)
+{
+    if (metric == MPB_METRIC_KDTREE) {
+        double ea[D], eb[D];
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            ea[d] = d_mul(wt.w[d], a[d]);
+            eb[d] = d_mul(wt.w[d], b[d]);
+        }
+        return __dsqrt_rn(sqdist_kdtree<D>(ea, eb));
+    }
+    double s = 0.;
+    if (metric == MPB_METRIC_PRIMITIVES) {
+        // primitives.py:60-62: norm(w*q2 - w*q1), norm = sqrt(dot) with a fused sequential dot
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            const double e = d_sub(d_mul(wt.w[d], b[d]), d_mul(wt.w[d], a[d]));
+            s = __fma_rn(e, e, s);
+        }
+    } else {
+        // tkinter/samplers.py:13-15: diff = q2 - q1; sqrt(dot(weights, diff*diff))
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            const double df = d_sub(b[d], a[d]);
+            s = __fma_rn(wt.w[d], d_mul(df, df), s);
+        }
+    }
+    return __dsqrt_rn(s);
+}
+
+
 // ---- mbarrier + 1-D bulk async copy (TMA engine, no tensor map) ---------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void *p)
 {

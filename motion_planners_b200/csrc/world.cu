@@ -293,6 +293,11 @@ __global__ void __launch_bounds__(128)
     extern __shared__ __align__(16) double sm[];
     const WorldSmem s = stage_world(w, sm);
     for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < E; e += (int64_t)gridDim.x * blockDim.x) {
+    if (INDEXED && (src[e] < 0 || dst[e] < 0)) {   // "no neighbour" slots of a kNN matrix
+        out_hit[e] = -1;
+        if (out_n) out_n[e] = 0;
+        continue;
+    }
     double a[D], b[D];
     {
         const double *pa = INDEXED ? A + src[e] * D : A + e * D;
@@ -463,6 +468,45 @@ __global__ void __launch_bounds__(128)
 #pragma unroll
         for (int d = 0; d < D; ++d) out[(o + i) * D + d] = q[d];
     }
+}
+
+template <int D>
+__global__ void __launch_bounds__(256)
+    edges_count_kernel(const double *__restrict__ A, const double *__restrict__ B, int64_t E, double step,
+                       int32_t *__restrict__ out_n)
+{
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= E) return;
+    double a[D], b[D];
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        a[d] = A[e * D + d];
+        b[d] = B[e * D + d];
+    }
+    out_n[e] = waypoint_count<D>(a, b, step);
+}
+
+template <int D>
+static int launch_count(const double *q1, const double *q2, int64_t E, double step, int32_t *out_n, cudaStream_t st)
+{
+    edges_count_kernel<D><<<(unsigned)((E + 255) / 256), 256, 0, st>>>(q1, q2, E, step, out_n);
+    MPB_LAUNCH_CHECK();
+    return MPB_OK;
+}
+
+MPB_API int mpb_edges_count(const double *q1, const double *q2, int64_t n_edges, int dim, double step, int32_t *out_n,
+                            void *stream)
+{
+    MPB_REQUIRE(n_edges >= 0, "mpb_edges_count: negative edge count");
+    MPB_REQUIRE(dim >= 1 && dim <= MPB_MAX_DIM, "mpb_edges_count: dim %d outside [1, %d]", dim, MPB_MAX_DIM);
+    MPB_REQUIRE(step > 0., "mpb_edges_count: step must be positive");
+    if (n_edges == 0) return MPB_OK;
+    MPB_REQUIRE(q1 && q2 && out_n, "mpb_edges_count: NULL buffer");
+    cudaStream_t st = (cudaStream_t)stream;
+#define CALL(DD) launch_count<DD>(q1, q2, n_edges, step, out_n, st)
+    MPB_DISPATCH_DIM(dim, CALL)
+#undef CALL
+    return MPB_EINVAL;
 }
 
 template <int D>

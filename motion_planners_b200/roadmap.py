@@ -1,0 +1,172 @@
+"""Device-resident kNN roadmap: the batched form of lazy_prm.Roadmap.add_samples + check_roadmap.
+
+What the reference builds one sample and one edge at a time in Python
+(motion_planners/lazy_prm.py:148-160 add_samples -> nearest.py:74-85; lazy_prm.py:211-215
+check_roadmap -> :173-178 check_vertex, :189-195 check_edge) is built here in three kernel
+passes over tensors that stay in HBM:
+
+    nbr_idx  [n_local, k+1] int64   neighbour matrix (global indices, self included, -1 = none)
+    nbr_dist [n_local, k+1] float64
+    vertex_hit [n_local] bool       collision_fn(sample)
+    edge_hit [n_local, k+1] int32   >= 0: a colliding waypoint index of sample -> neighbour,
+                                    -1: free (or no edge: self / missing neighbour)
+
+Samples are sharded across ranks; one all-gather (NCCL over NVLink) builds the global sample
+set, every rank answers the queries of its own shard against it and checks the directed
+edges that leave its shard.  Results are identical for every world size.
+"""
+import math
+
+import numpy as np
+import torch
+
+from . import ops
+from .geometry import STEP_SIZE
+
+
+def shard_bounds(n, world_size, rank):
+    """Contiguous, balanced shard [lo, hi) of n items for `rank`."""
+    base, rem = divmod(n, world_size)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+class DeviceRoadmap(object):
+    def __init__(self, world, k=10, weights=None, max_distance=math.inf, step=STEP_SIZE, group=None):
+        self.world = world
+        self.k = int(k)
+        self.kk = self.k + 1                      # the reference asks for max_degree + 1 and drops self
+        self.weights = weights
+        self.max_distance = float(max_distance)
+        self.step = float(step)
+        self.group = group
+        self.obstacles = ops.ObstacleSet(world)
+        self.launches = 0                          # kernels of this library launched by the last build()
+        self.profile = False                       # record CUDA events around each phase of build()
+        self.events = {}
+        self._index = None
+        self._src = None
+
+    # -- distributed plumbing (torch.distributed only; no collective inside the library)
+    def _dist(self):
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized():
+            return dist, dist.get_world_size(self.group), dist.get_rank(self.group)
+        return None, 1, 0
+
+    def gather_samples(self, local):
+        """All-gather the per-rank sample shards into the global [N, D] table (equal shard sizes use
+        all_gather_into_tensor; ragged shards fall back to all_gather with padding)."""
+        dist, ws, rank = self._dist()
+        if ws == 1:
+            return local, 0
+        counts = torch.tensor([local.shape[0]], device=local.device, dtype=torch.int64)
+        all_counts = [torch.zeros_like(counts) for _ in range(ws)]
+        dist.all_gather(all_counts, counts, group=self.group)
+        sizes = [int(c.item()) for c in all_counts]
+        D = local.shape[1]
+        if len(set(sizes)) == 1:
+            out = torch.empty((sum(sizes), D), dtype=local.dtype, device=local.device)
+            dist.all_gather_into_tensor(out, local.contiguous(), group=self.group)
+        else:
+            m = max(sizes)
+            pad = torch.zeros((m, D), dtype=local.dtype, device=local.device)
+            pad[:local.shape[0]] = local
+            parts = [torch.empty_like(pad) for _ in range(ws)]
+            dist.all_gather(parts, pad, group=self.group)
+            out = torch.cat([p[:s] for p, s in zip(parts, sizes)], 0)
+        return out, sum(sizes[:rank])
+
+    def gather_samples_equal(self, local, out):
+        """Fast path used by the bench: equal shards, preallocated output, one collective."""
+        dist, ws, rank = self._dist()
+        if ws == 1:
+            return local, 0
+        dist.all_gather_into_tensor(out, local, group=self.group)
+        return out, rank * local.shape[0]
+
+    # -- the build
+    def build(self, local_samples, check=True, gathered=None):
+        """local_samples: this rank's shard, CUDA float64 [n_local, D].  Returns self."""
+        if gathered is None:
+            samples, offset = self.gather_samples(local_samples)
+        else:
+            samples, offset = gathered
+        n_local = local_samples.shape[0]
+        self.samples, self.offset, self.n_local = samples, offset, n_local
+        queries = samples[offset:offset + n_local]
+        launches = 0
+        mark = self._mark
+        mark("start")
+
+        if self._index is None or self._index.samples.data_ptr() != samples.data_ptr() \
+                or self._index.n != samples.shape[0]:
+            self._index = ops.KnnIndex(samples, self.weights)
+        self._index._prepared = False
+        self._index.prepare(n_local)
+        launches += 4                               # init, minmax, finalize, pack
+        mark("packed")
+        if getattr(self, "nbr_idx", None) is None or self.nbr_idx.shape != (n_local, self.kk):
+            self.nbr_idx = torch.empty((n_local, self.kk), dtype=torch.int64, device=samples.device)
+            self.nbr_dist = torch.empty((n_local, self.kk), dtype=torch.float64, device=samples.device)
+            self.stats = torch.zeros(2, dtype=torch.int64, device=samples.device)
+        self._index.search(queries, self.kk, self.max_distance, stats=self.stats, out_idx=self.nbr_idx,
+                           out_dist=self.nbr_dist)
+        launches += 2                               # filter + exact re-do of uncertified queries
+        mark("knn")
+
+        if check:
+            self.vertex_hit = self.obstacles.points_check(queries)
+            launches += 1
+            mark("vertices")
+            if self._src is None or self._src.numel() != n_local * self.kk or self._src_offset != offset:
+                self._src = (torch.arange(n_local, device=samples.device, dtype=torch.int64) + offset) \
+                    .repeat_interleave(self.kk)
+                self._src_offset = offset
+            dst = self.nbr_idx.view(-1)
+            # self-edges (one waypoint) and missing neighbours (-1, skipped) ride along, so the neighbour
+            # matrix is consumed in place with no compaction pass
+            hit, _ = self.obstacles.edges_check(samples, self._src, dst, mode=ops.EDGE_ANY, step=self.step,
+                                                want_counts=False)
+            self.edge_hit = hit.view(n_local, self.kk)
+            launches += 1
+            mark("edges")
+        self.launches = launches
+        return self
+
+    def _mark(self, name):
+        if self.profile:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            self.events[name] = ev
+
+    def phase_ms(self):
+        """Milliseconds per phase of the last profiled build() (call after a synchronize)."""
+        order = ["start", "packed", "knn", "vertices", "edges"]
+        have = [n for n in order if n in self.events]
+        return {b: self.events[a].elapsed_time(self.events[b]) for a, b in zip(have[:-1], have[1:])}
+
+    def build_from_host(self, pinned_samples):
+        """End-to-end call with HOST buffers: a pinned float64 [N, D] CPU tensor in; neighbour matrix,
+        vertex flags and edge flags back on the host.  Host->device and device->host copies are part of
+        the call; this is what bench.py times as `e2e`."""
+        dev = pinned_samples.cuda(non_blocking=True)
+        self.build(dev)
+        return self.nbr_idx.cpu(), self.vertex_hit.cpu(), self.edge_hit.cpu()
+
+    # -- counts for the metric
+    def n_edges_checked(self):
+        """Directed sample->neighbour edges checked (self and missing slots excluded)."""
+        own = torch.arange(self.n_local, device=self.nbr_idx.device).unsqueeze(1) + self.offset
+        return int(((self.nbr_idx >= 0) & (self.nbr_idx != own)).sum().item())
+
+    # -- host views
+    def undirected_edges(self):
+        """Sorted unique (v1 < v2) pairs of this rank's directed edges, as a numpy int64 [E, 2]."""
+        idx = self.nbr_idx.cpu().numpy()
+        own = np.arange(self.n_local)[:, None] + self.offset
+        mask = (idx >= 0) & (idx != own)
+        a = np.broadcast_to(own, idx.shape)[mask]
+        b = idx[mask]
+        lo, hi = np.minimum(a, b), np.maximum(a, b)
+        return np.unique(np.stack([lo, hi], 1), axis=0)
