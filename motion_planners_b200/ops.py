@@ -118,11 +118,24 @@ class ObstacleSet(object):
         return hit, cnt
 
 
-def edges_waypoints(q1, q2, counts, step=STEP_SIZE):
+def edges_count(q1, q2, step=STEP_SIZE):
+    """Number of waypoints extend_fn(q1[e], q2[e]) yields (tkinter/samplers.py:119-120) -> int32 [E]."""
+    q1 = _f64(q1, "q1")
+    q2 = _f64(q2, "q2", q1.shape[1])
+    E, D = q1.shape
+    out = torch.empty(E, dtype=torch.int32, device=q1.device)
+    rc = _lib.lib().mpb_edges_count(_ptr(q1), _ptr(q2), E, D, float(step), _ptr(out), _stream())
+    _lib.check(rc, "mpb_edges_count")
+    return out
+
+
+def edges_waypoints(q1, q2, counts=None, step=STEP_SIZE):
     """extend_fn(q1[e], q2[e]) for a batch -> (offsets[E+1] int64, waypoints[sum(counts), D])."""
     q1 = _f64(q1, "q1")
     q2 = _f64(q2, "q2", q1.shape[1])
     E, D = q1.shape
+    if counts is None:
+        counts = edges_count(q1, q2, step)
     offsets = torch.zeros(E + 1, dtype=torch.int64, device=q1.device)
     if E:
         offsets[1:] = torch.cumsum(counts.to(torch.int64), 0)
@@ -179,11 +192,23 @@ class KnnIndex(object):
         return idx, dist
 
 
-def knn(samples, queries, k, weights=None, max_dist=math.inf, method="f32filter", stats=None):
+def knn(samples, queries, k, weights=None, max_dist=math.inf, method="f32filter", stats=None, metric=METRIC_KDTREE):
     """k nearest stored samples per query, bit-exact to nearest.py:74-85 (see include/mpb200.h).
-    method: "f32filter" (tiled fp32 filter + fp64 re-rank) or "f64" (exact brute force)."""
+    method: "f32filter" (tiled fp32 filter + fp64 re-rank) or "f64" (exact brute force).
+    metric: METRIC_KDTREE ranks like scipy's cKDTree; METRIC_PRIMITIVES / METRIC_SAMPLERS rank by the
+    value the corresponding distance_fn returns (exact kernel only)."""
     samples = _f64(samples, "samples")
     queries = _f64(queries, "queries", samples.shape[1])
+    if metric != METRIC_KDTREE:
+        N, D = samples.shape
+        M = queries.shape[0]
+        idx = torch.empty((M, k), dtype=torch.int64, device=queries.device)
+        dist = torch.empty((M, k), dtype=torch.float64, device=queries.device)
+        _, wp = _host_weights(weights, D)
+        rc = _lib.lib().mpb_knn_f64_metric(_ptr(samples), N, _ptr(queries), M, D, wp, int(metric), int(k),
+                                           float(max_dist), _ptr(idx), _ptr(dist), _stream())
+        _lib.check(rc, "mpb_knn_f64_metric")
+        return idx, dist
     if method == "f32filter":
         return KnnIndex(samples, weights).search(queries, k, max_dist, stats=stats)
     if method != "f64":

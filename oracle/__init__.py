@@ -41,6 +41,9 @@ def lib():
     return _lib
 
 
+METRIC_SCIPY, METRIC_PRIMITIVES, METRIC_SAMPLERS = 0, 1, 2
+
+
 def _p(a, t):
     return a.ctypes.data_as(t)
 
@@ -126,6 +129,25 @@ def knn(samples, queries, k, weights=None, max_dist=np.inf):
     return idx, dist
 
 
+def knn_metric(samples, queries, k, weights=None, mode=2, max_dist=np.inf):
+    """k smallest (distance_fn value, index) per query for the primitives / samplers metrics
+    (nearest.py:102-109, prm.py:244-246); mode 0 falls back to the kd-tree metric's knn()."""
+    if mode == METRIC_SCIPY:
+        return knn(samples, queries, k, weights, max_dist)
+    samples = _c(samples)
+    queries = _c(queries)
+    N, D = samples.shape
+    M = queries.shape[0]
+    w = np.ones(D) if weights is None else _c(weights)
+    idx = np.empty((M, k), np.int64)
+    dist = np.empty((M, k), np.float64)
+    rc = lib().orc_knn_metric(_p(samples, _f64p), ctypes.c_int64(N), _p(queries, _f64p), ctypes.c_int64(M),
+                              ctypes.c_int(D), _p(w, _f64p), ctypes.c_int(mode), ctypes.c_int(k),
+                              ctypes.c_double(max_dist), _p(idx, _i64p), _p(dist, _f64p))
+    assert rc == 0
+    return idx, dist
+
+
 def extend(q1, q2, step=1e-2):
     """Waypoints of get_extend_fn(circular={})(q1, q2) (tkinter/samplers.py:113-127)."""
     q1 = _c(q1)
@@ -154,9 +176,6 @@ def dist_scipy(q1, q2, w):
     e1 = np.ascontiguousarray(w * q1)
     e2 = np.ascontiguousarray(w * q2)
     return float(np.sqrt(lib().orc_sqdist_scipy(_p(e1, _f64p), _p(e2, _f64p), ctypes.c_int(q1.shape[0]))))
-
-
-METRIC_SCIPY, METRIC_PRIMITIVES, METRIC_SAMPLERS = 0, 1, 2
 
 
 def nearest(nodes, target, w=None, mode=METRIC_SAMPLERS):

@@ -72,6 +72,21 @@ def test_knn_matches_oracle(ops, D, N, M, k):
     assert (host(idx) == o_idx).all() and (host(dist) == o_dist).all()
 
 
+@pytest.mark.parametrize("metric", [1, 2])
+@pytest.mark.parametrize("D", [2, 7, 9])
+def test_knn_other_metrics_match_oracle(ops, D, metric):
+    """Ranking by the value distance_fn returns (primitives / samplers procedures), stable on index."""
+    rs = np.random.RandomState(77 + D)
+    X = rs.uniform(size=(4000, D))
+    X[100:140] = X[60:100]                                      # duplicates: exact distance ties
+    Q = np.concatenate([X[:300], rs.uniform(size=(200, D))])
+    w = rs.uniform(0.5, 2.0, size=D)
+    for md in (np.inf, 0.35):
+        o_idx, o_dist = oracle.knn_metric(X, Q, 12, w, metric, md)
+        idx, dist = ops.knn(dev(X), dev(Q), 12, weights=w, metric=metric, max_dist=md)
+        assert (host(idx) == o_idx).all() and (host(dist) == o_dist).all()
+
+
 def test_knn_certificate_falls_back_when_fp32_cannot_separate(ops):
     """Samples 1e-7 apart around an fp32-hostile spread: the filter cannot rank them, the
     certificate must fail and the exact kernel must still give the oracle's answer."""
@@ -238,7 +253,8 @@ def test_waypoints_golden(ops, golden, D):
     obs = ops.ObstacleSet(World(D, np.zeros(D), np.ones(D)))
     _, n = obs.edges_check_pairs(q1, q2)
     assert (host(n) == g["counts"]).all()
-    off, way = ops.edges_waypoints(q1, q2, n)
+    assert (host(ops.edges_count(q1, q2)) == g["counts"]).all()
+    off, way = ops.edges_waypoints(q1, q2)
     assert (host(way) == g["waypoints"]).all()              # the serial recurrence, bit for bit
     assert int(off[-1]) == g["waypoints"].shape[0]
 
