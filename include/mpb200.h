@@ -142,6 +142,27 @@ int mpb_knn_f32filter(const double *samples, int64_t n_samples, const double *qu
                       void *workspace, size_t workspace_bytes, int64_t *out_idx, double *out_dist,
                       int64_t *stats, void *stream);
 
+/* The same search for callers that cannot allocate device memory -- a planner thread in a control
+ * loop that must stay away from the driver's allocator (process-wide lock, possible device
+ * synchronisation, unbounded latency), a process whose device memory was handed out in full to
+ * another pool at start-up, or a thin foreign-language binding that owns no device allocator.  The
+ * scratch is a fixed array of MPB_KNN_STATIC_BYTES inside the library, resident on every GPU that
+ * loads it until the process exits; inputs and outputs are still the caller's.  No counterpart in
+ * the reference (it has no device memory to manage).
+ *  - Sizes whose scratch need (mpb_knn_workspace_bytes) exceeds MPB_KNN_STATIC_BYTES are refused
+ *    with MPB_ENOMEM and a message; 4 MiB covers e.g. 100k samples x 100k queries at dim <= 7.
+ *  - The first call on each device looks up the array's device address; make that call before
+ *    starting any stream capture on that device.
+ *  - The call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine).
+ *  - All calls share the one array and it keeps the previous call's bytes; each call rewrites what
+ *    it reads (header, counters, tile slots), so results do not depend on history -- but two calls
+ *    that overlap on the GPU (different streams, or threads) race on it.  Serialise them. */
+#define MPB_KNN_STATIC_BYTES (4u << 20)
+int mpb_knn_f32filter_static(const double *samples, int64_t n_samples, const double *queries,
+                             int64_t n_queries, int dim, const double *weights, int k,
+                             double max_dist, int64_t *out_idx, double *out_dist, int64_t *stats,
+                             void *stream);
+
 /* ---- tree queries (RRT family) ----------------------------------------------------------
  * metric selects the reference's rounding procedure for the weighted Euclidean distance:
  *   MPB_METRIC_KDTREE     the kNN key above

@@ -16,6 +16,8 @@
 // uncertified queries are queued for the exact kernel.
 #include <math.h>
 
+#include <mutex>
+
 #include "mpb_common.cuh"
 
 #define FULL_MASK 0xffffffffu
@@ -628,4 +630,56 @@ MPB_API int mpb_knn_f32filter(const double *samples, int64_t n_samples, const do
     if (rc != MPB_OK) return rc;
     return mpb_knn_search(samples, n_samples, queries, n_queries, dim, weights, k, max_dist, workspace, workspace_bytes,
                           out_idx, out_dist, stats, stream);
+}
+
+// ------------------------------------------------------------------------------------------
+// kNN on scratch memory that lives inside the library
+// ------------------------------------------------------------------------------------------
+// Some users of this ABI have no way to hand us a workspace: a planner thread inside a robot's
+// control loop must not touch the driver's allocator (cudaMalloc takes a process-wide lock, may
+// synchronise the device and has no latency bound); a process whose device memory was handed out
+// in full at start-up to another pool (a simulator, an inference runtime) has nothing left to ask
+// the driver for; and a thin foreign-language binding that wraps only the functions of this header
+// owns no device allocator at all.  For them the filter's scratch -- header, packed fp32 tiles,
+// fallback list -- sits in the fixed array below.  Every GPU that loads the library carries these
+// MPB_KNN_STATIC_BYTES until the process exits, which is why the array is kept small.
+static __device__ __align__(256) unsigned char g_knn_static_scratch[MPB_KNN_STATIC_BYTES];
+
+// In host code `g_knn_static_scratch` is only a handle for the runtime, not an address a kernel could
+// use; the device address is looked up once per device and remembered here.
+static void *g_knn_static_ptr[64];
+static std::mutex g_knn_static_mutex;
+
+MPB_API int mpb_knn_f32filter_static(const double *samples, int64_t n_samples, const double *queries,
+                                     int64_t n_queries, int dim, const double *weights, int k, double max_dist,
+                                     int64_t *out_idx, double *out_dist, int64_t *stats, void *stream)
+{
+    int rc = check_common("mpb_knn_f32filter_static", samples, n_samples, queries, n_queries, dim, k, out_idx);
+    if (rc != MPB_OK) return rc;
+    MPB_REQUIRE(max_dist >= 0., "mpb_knn_f32filter_static: max_dist must be >= 0");
+    const size_t need = ws_layout(n_samples, n_queries, dim).total;
+    if (need > (size_t)MPB_KNN_STATIC_BYTES) {
+        mpb_set_error("mpb_knn_f32filter_static: %lld samples x %lld queries at dim %d need %zu bytes of scratch, "
+                      "the built-in array holds %zu; use mpb_knn_f32filter with a caller-owned workspace",
+                      (long long)n_samples, (long long)n_queries, dim, need, (size_t)MPB_KNN_STATIC_BYTES);
+        return MPB_ENOMEM;
+    }
+    int dev = 0;
+    MPB_CUDA_CHECK(cudaGetDevice(&dev));
+    MPB_REQUIRE(dev >= 0 && dev < 64, "mpb_knn_f32filter_static: device ordinal %d not supported", dev);
+    void *scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_knn_static_mutex);
+        if (g_knn_static_ptr[dev] == nullptr) {
+            // first call on this device: resolve the array's device address (the device is current)
+            void *p = nullptr;
+            MPB_CUDA_CHECK(cudaGetSymbolAddress(&p, g_knn_static_scratch));
+            g_knn_static_ptr[dev] = p;
+        }
+        scratch = g_knn_static_ptr[dev];
+    }
+    // prepare re-initialises the header (bounding box, fallback counter) and rewrites every tile slot it
+    // will read, so nothing left behind by an earlier call is ever consumed
+    return mpb_knn_f32filter(samples, n_samples, queries, n_queries, dim, weights, k, max_dist, scratch,
+                             (size_t)MPB_KNN_STATIC_BYTES, out_idx, out_dist, stats, stream);
 }

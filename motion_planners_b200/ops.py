@@ -224,6 +224,23 @@ def knn(samples, queries, k, weights=None, max_dist=math.inf, method="f32filter"
     return idx, dist
 
 
+def knn_static(samples, queries, k, weights=None, max_dist=math.inf, stats=None):
+    """knn() on the library's built-in scratch array, for callers that must not allocate device memory
+    (see mpb_knn_f32filter_static in include/mpb200.h for who those are and for the size limit).
+    The output tensors are still allocated here by torch; pass through the C ABI directly to avoid that too."""
+    samples = _f64(samples, "samples")
+    queries = _f64(queries, "queries", samples.shape[1])
+    N, D = samples.shape
+    M = queries.shape[0]
+    idx = torch.empty((M, k), dtype=torch.int64, device=queries.device)
+    dist = torch.empty((M, k), dtype=torch.float64, device=queries.device)
+    _, wp = _host_weights(weights, D)
+    rc = _lib.lib().mpb_knn_f32filter_static(_ptr(samples), N, _ptr(queries), M, D, wp, int(k), float(max_dist),
+                                             _ptr(idx), _ptr(dist), _ptr(stats), _stream())
+    _lib.check(rc, "mpb_knn_f32filter_static")
+    return idx, dist
+
+
 def trees_nearest(nodes, sizes, targets, weights=None, metric=METRIC_SAMPLERS, active=None):
     """First arg-min nearest node per tree (primitives.py:21).  nodes [T, cap, D], sizes [T] int32,
     targets [T, D] -> (idx [T] int32, dist [T] float64)."""
