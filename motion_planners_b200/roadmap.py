@@ -31,6 +31,48 @@ def shard_bounds(n, world_size, rank):
     return lo, lo + base + (1 if rank < rem else 0)
 
 
+def dist_info(group=None):
+    """(torch.distributed or None, world size, rank) of the running job."""
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized():
+        return dist, dist.get_world_size(group), dist.get_rank(group)
+    return None, 1, 0
+
+
+def gather_samples(local, group=None):
+    """All-gather the per-rank sample shards [n_r, D] into the global [N, D] table, rank order.
+    -> (table, offset of this rank's first sample).  Equal shards take one all_gather_into_tensor;
+    ragged shards are padded to the longest one."""
+    dist, ws, rank = dist_info(group)
+    if ws == 1:
+        return local, 0
+    counts = torch.tensor([local.shape[0]], device=local.device, dtype=torch.int64)
+    all_counts = [torch.zeros_like(counts) for _ in range(ws)]
+    dist.all_gather(all_counts, counts, group=group)
+    sizes = [int(c.item()) for c in all_counts]
+    D = local.shape[1]
+    if len(set(sizes)) == 1:
+        out = torch.empty((sum(sizes), D), dtype=local.dtype, device=local.device)
+        dist.all_gather_into_tensor(out, local.contiguous(), group=group)
+    else:
+        m = max(sizes)
+        pad = torch.zeros((m, D), dtype=local.dtype, device=local.device)
+        pad[:local.shape[0]] = local
+        parts = [torch.empty_like(pad) for _ in range(ws)]
+        dist.all_gather(parts, pad, group=group)
+        out = torch.cat([p[:s] for p, s in zip(parts, sizes)], 0)
+    return out, sum(sizes[:rank])
+
+
+def gather_rows(local, group=None):
+    """Concatenate per-rank result rows (neighbour matrices, flags) in rank order on every rank."""
+    dist, ws, rank = dist_info(group)
+    if ws == 1:
+        return local
+    out, _ = gather_samples(local.reshape(local.shape[0], -1), group)
+    return out.reshape((-1,) + tuple(local.shape[1:]))
+
+
 class DeviceRoadmap(object):
     def __init__(self, world, k=10, weights=None, max_distance=math.inf, step=STEP_SIZE, group=None):
         self.world = world
@@ -49,33 +91,10 @@ class DeviceRoadmap(object):
 
     # -- distributed plumbing (torch.distributed only; no collective inside the library)
     def _dist(self):
-        import torch.distributed as dist
-        if dist.is_available() and dist.is_initialized():
-            return dist, dist.get_world_size(self.group), dist.get_rank(self.group)
-        return None, 1, 0
+        return dist_info(self.group)
 
     def gather_samples(self, local):
-        """All-gather the per-rank sample shards into the global [N, D] table (equal shard sizes use
-        all_gather_into_tensor; ragged shards fall back to all_gather with padding)."""
-        dist, ws, rank = self._dist()
-        if ws == 1:
-            return local, 0
-        counts = torch.tensor([local.shape[0]], device=local.device, dtype=torch.int64)
-        all_counts = [torch.zeros_like(counts) for _ in range(ws)]
-        dist.all_gather(all_counts, counts, group=self.group)
-        sizes = [int(c.item()) for c in all_counts]
-        D = local.shape[1]
-        if len(set(sizes)) == 1:
-            out = torch.empty((sum(sizes), D), dtype=local.dtype, device=local.device)
-            dist.all_gather_into_tensor(out, local.contiguous(), group=self.group)
-        else:
-            m = max(sizes)
-            pad = torch.zeros((m, D), dtype=local.dtype, device=local.device)
-            pad[:local.shape[0]] = local
-            parts = [torch.empty_like(pad) for _ in range(ws)]
-            dist.all_gather(parts, pad, group=self.group)
-            out = torch.cat([p[:s] for p, s in zip(parts, sizes)], 0)
-        return out, sum(sizes[:rank])
+        return gather_samples(local, self.group)
 
     def gather_samples_equal(self, local, out):
         """Fast path used by the bench: equal shards, preallocated output, one collective."""
