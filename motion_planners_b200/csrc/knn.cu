@@ -26,7 +26,7 @@ namespace {
 
 constexpr int kWarps = 8;          // consumer warps per block
 constexpr int kStages = 4;         // shared-memory ring depth
-constexpr int kListLen = 32;       // candidates kept per query (one per lane)
+constexpr int kSmallListMaxK = 12; // k up to which 16 survivors per query are kept (else 32)
 constexpr int kHeaderBytes = 512;
 
 struct KnnHeader {
@@ -230,10 +230,25 @@ struct FilterSmem {
     static constexpr int P = planes_for(D);
     static constexpr int TILE = tile_for(D);
     static constexpr int STAGE_BYTES = TILE * P * 16;
-    static constexpr int BYTES = kStages * STAGE_BYTES + 2 * kStages * 8 + 64;
+    static constexpr int RING_BYTES = kStages * STAGE_BYTES;
+    static constexpr int BYTES = RING_BYTES + 128;   // + full barriers and release counters
 };
+static_assert(kStages * 8 + kStages * 4 <= 128, "sync area too small");
 
-template <int D, int Q>
+// 128-bit shared-memory load by 32-bit shared-space address (no generic->shared conversion in the loop).
+// volatile: keeps its order relative to the mbarrier waits (also volatile asm).
+__device__ __forceinline__ float4 lds128(uint32_t addr)
+{
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+
+// SEG = candidates kept per query (16 or 32).  A 32-lane register holds 32/SEG query lists side by side:
+// query q of the warp lives in register q / (32/SEG), lanes [SEG*(q % (32/SEG)), +SEG), sorted ascending.
+// (Measured alternatives that lost, see profiles/r1_summary.md: a shared-memory append buffer with periodic
+// compaction; a fixed producer warp; staggered tile order between blocks.)
+template <int D, int Q, int SEG>
 __global__ void __launch_bounds__(kWarps * 32, 2)
     knn_filter_kernel(const double *__restrict__ x, int64_t N, const double *__restrict__ qs, int64_t M, Weights wt,
                       int k, double r2, const float4 *__restrict__ packed, int n_tiles, KnnHeader *__restrict__ h,
@@ -241,28 +256,36 @@ __global__ void __launch_bounds__(kWarps * 32, 2)
 {
     using SM = FilterSmem<D, Q>;
     constexpr int P = SM::P, TILE = SM::TILE;
+    constexpr int PER = 32 / SEG;          // query lists per register
+    constexpr int NREG = Q / PER;          // list registers per warp
+    constexpr unsigned SEGMASK = (SEG == 32) ? 0xffffffffu : ((1u << (SEG & 31)) - 1u);
+    static_assert(Q % PER == 0, "Q must be a multiple of the lists per register");
     extern __shared__ __align__(128) unsigned char smem_raw[];
     float4 *stage_base = reinterpret_cast<float4 *>(smem_raw);
-    uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw + kStages * SM::STAGE_BYTES);
-    uint64_t *empty = full + kStages;
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw + SM::RING_BYTES);
+    int *released = reinterpret_cast<int *>(full + kStages);      // warps done with each ring slot
 
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
-    const bool producer = (threadIdx.x == 0);
+    const int seg = lane / SEG;            // which list of a register this lane belongs to
+    const int sl = lane % SEG;             // position inside that list
 
-    if (producer) {
+    auto request_tile = [&](int i) {   // one lane: arm the slot's barrier and start the bulk copy of tile i
+        const int slot = i % kStages;
+        mbar_arrive_expect_tx(&full[slot], SM::STAGE_BYTES);
+        bulk_copy_g2s(stage_base + (size_t)slot * TILE * P, packed + (size_t)i * TILE * P, SM::STAGE_BYTES,
+                      &full[slot]);
+    };
+    if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; ++s) {
             mbar_init(&full[s], 1);
-            mbar_init(&empty[s], kWarps);
+            released[s] = 0;
         }
         mbar_fence_init();
     }
     __syncthreads();
-    if (producer) {
-        for (int s = 0; s < kStages && s < n_tiles; ++s) {
-            mbar_arrive_expect_tx(&full[s], SM::STAGE_BYTES);
-            bulk_copy_g2s(stage_base + (size_t)s * TILE * P, packed + (size_t)s * TILE * P, SM::STAGE_BYTES, &full[s]);
-        }
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < kStages && i < n_tiles; ++i) request_tile(i);
     }
 
     // ---- this warp's Q queries, as -2*fl32(e_q - c), uniform across the lanes
@@ -278,43 +301,42 @@ __global__ void __launch_bounds__(kWarps * 32, 2)
             qm[qi][d] = -2.f * (float)d_sub(e, h->center[d]);
         }
     }
-    float thr[Q], lk[Q];
-    int li[Q];
+    float thr[Q], lk[NREG];
+    int li[NREG];
 #pragma unroll
-    for (int qi = 0; qi < Q; ++qi) {
-        thr[qi] = INFINITY;
-        lk[qi] = INFINITY;
-        li[qi] = -1;
+    for (int qi = 0; qi < Q; ++qi) thr[qi] = INFINITY;
+#pragma unroll
+    for (int r = 0; r < NREG; ++r) {
+        lk[r] = INFINITY;
+        li[r] = -1;
     }
+
+    const uint32_t smem0 = smem_u32(stage_base) + (uint32_t)lane * 16u;
 
     // ---- stream every tile through the ring
     for (int t = 0; t < n_tiles; ++t) {
         const int s = t % kStages;
         const uint32_t ph = (uint32_t)(t / kStages) & 1u;
-        // refill the slot released one tile ago
-        if (producer && t >= 1 && (t - 1 + kStages) < n_tiles) {
-            const int sp = (t - 1) % kStages;
-            const uint32_t php = (uint32_t)((t - 1) / kStages) & 1u;
-            mbar_wait(&empty[sp], php);
-            mbar_arrive_expect_tx(&full[sp], SM::STAGE_BYTES);
-            bulk_copy_g2s(stage_base + (size_t)sp * TILE * P, packed + (size_t)(t - 1 + kStages) * TILE * P,
-                          SM::STAGE_BYTES, &full[sp]);
-        }
-        __syncwarp();
         mbar_wait(&full[s], ph);
 
-        const float4 *tile = stage_base + (size_t)s * TILE * P;
+        const uint32_t tbase = smem0 + (uint32_t)s * (uint32_t)SM::STAGE_BYTES;
         const int cbase0 = t * TILE;
-#pragma unroll 2
+        float4 nxt[P];
+#pragma unroll
+        for (int p = 0; p < P; ++p) nxt[p] = lds128(tbase + (uint32_t)(p * TILE) * 16u);
+#pragma unroll 4
         for (int c0 = 0; c0 < TILE; c0 += 32) {
             float xv[4 * P];
 #pragma unroll
             for (int p = 0; p < P; ++p) {
-                const float4 f = tile[p * TILE + c0 + lane];
-                xv[4 * p + 0] = f.x;
-                xv[4 * p + 1] = f.y;
-                xv[4 * p + 2] = f.z;
-                xv[4 * p + 3] = f.w;
+                xv[4 * p + 0] = nxt[p].x;
+                xv[4 * p + 1] = nxt[p].y;
+                xv[4 * p + 2] = nxt[p].z;
+                xv[4 * p + 3] = nxt[p].w;
+            }
+            if (c0 + 32 < TILE) {   // next group's candidates are in flight while this one is scored
+#pragma unroll
+                for (int p = 0; p < P; ++p) nxt[p] = lds128(tbase + (uint32_t)(p * TILE + c0 + 32) * 16u);
             }
             float acc[Q];
             bool pass = false;
@@ -327,51 +349,89 @@ __global__ void __launch_bounds__(kWarps * 32, 2)
                 pass = pass || (a < thr[qi]);
             }
             if (__any_sync(FULL_MASK, pass)) {
+                // Insertion rounds.  Every round gives each query at most one of its passing candidates;
+                // the rounds are branch-free so that the shuffle chains of all list registers overlap.
+                // A candidate that no longer beats its list (or "no candidate": key = +inf) lands at
+                // position SEG, i.e. nowhere.
                 const int cbase = cbase0 + c0;
+                unsigned m[Q];
 #pragma unroll
-                for (int qi = 0; qi < Q; ++qi) {
-                    unsigned m = __ballot_sync(FULL_MASK, acc[qi] < thr[qi]);
-                    while (m) {
-                        const int src = __ffs(m) - 1;
-                        m &= m - 1;
-                        const float key = __shfl_sync(FULL_MASK, acc[qi], src);
-                        if (key < thr[qi]) {
-                            const int pos = __popc(__ballot_sync(FULL_MASK, lk[qi] <= key));
-                            const float upk = __shfl_up_sync(FULL_MASK, lk[qi], 1);
-                            const int upi = __shfl_up_sync(FULL_MASK, li[qi], 1);
-                            if (lane > pos) {
-                                lk[qi] = upk;
-                                li[qi] = upi;
-                            } else if (lane == pos) {
-                                lk[qi] = key;
-                                li[qi] = cbase + src;
+                for (int qi = 0; qi < Q; ++qi) m[qi] = __ballot_sync(FULL_MASK, acc[qi] < thr[qi]);
+                bool more = true;
+                while (more) {
+                    more = false;
+#pragma unroll
+                    for (int r = 0; r < NREG; ++r) {
+                        float key = INFINITY;
+                        int cidx = -1;
+#pragma unroll
+                        for (int hs = 0; hs < PER; ++hs) {
+                            const int qi = r * PER + hs;
+                            const int src = (__ffs(m[qi]) - 1) & 31;
+                            const float kq = __shfl_sync(FULL_MASK, acc[qi], src);
+                            if (seg == hs) {
+                                key = m[qi] ? kq : INFINITY;
+                                cidx = cbase + src;
                             }
-                            thr[qi] = __shfl_sync(FULL_MASK, lk[qi], 31);
+                            m[qi] &= m[qi] - 1;
+                            more = more || (m[qi] != 0);
                         }
+                        const unsigned le = __ballot_sync(FULL_MASK, lk[r] <= key);
+                        const int pos = __popc((le >> ((SEG * seg) & 31)) & SEGMASK);
+                        const float upk = __shfl_up_sync(FULL_MASK, lk[r], 1, SEG);
+                        const int upi = __shfl_up_sync(FULL_MASK, li[r], 1, SEG);
+                        if (sl > pos) {
+                            lk[r] = upk;
+                            li[r] = upi;
+                        } else if (sl == pos) {
+                            lk[r] = key;
+                            li[r] = cidx;
+                        }
+#pragma unroll
+                        for (int hs = 0; hs < PER; ++hs)
+                            thr[r * PER + hs] = __shfl_sync(FULL_MASK, lk[r], SEG * hs + SEG - 1);
                     }
                 }
             }
         }
+        // The last warp to release a slot requests its next tenant: nobody waits for anybody.
         __syncwarp();
-        if (lane == 0) mbar_arrive(&empty[s]);
+        if (lane == 0) {
+            __threadfence_block();
+            const int done = atomicAdd(&released[s], 1);
+            if (done == kWarps - 1) {
+                released[s] = 0;
+                __threadfence_block();
+                if (t + kStages < n_tiles) request_tile(t + kStages);
+            }
+        }
+        __syncwarp();
     }
 
-    // ---- exact re-rank of the 32 survivors and the certificate
+    // ---- exact re-rank of the survivors and the certificate; the PER lists of a register are handled
+    //      side by side, each lane working for the query its segment belongs to
     const double R = h->R;
     constexpr double U32 = 5.9604644775390625e-08;   // 2^-24
 #pragma unroll
-    for (int qi = 0; qi < Q; ++qi) {
-        const int64_t q = q0 + qi;
-        if (q >= M) continue;   // warp-uniform
+    for (int r = 0; r < NREG; ++r) {
+        const int64_t q = q0 + r * PER + seg;
+        const bool qvalid = q < M;
+        const int64_t qc = qvalid ? q : (M - 1);
         double eq[D];
         double nq2 = 0.;
+        float T32 = thr[r * PER];
+#pragma unroll
+        for (int hs = 1; hs < PER; ++hs) T32 = (seg == hs) ? thr[r * PER + hs] : T32;
 #pragma unroll
         for (int d = 0; d < D; ++d) {
-            eq[d] = d_mul(wt.w[d], qs[q * D + d]);
-            const double qh = -0.5 * (double)qm[qi][d];
+            eq[d] = d_mul(wt.w[d], qs[qc * D + d]);
+            float qmd = qm[r * PER][d];
+#pragma unroll
+            for (int hs = 1; hs < PER; ++hs) qmd = (seg == hs) ? qm[r * PER + hs][d] : qmd;
+            const double qh = -0.5 * (double)qmd;
             nq2 += qh * qh;
         }
-        const int ci = li[qi];
+        const int ci = li[r];
         double S = INFINITY;
         if (ci >= 0) {
             double ex[D];
@@ -381,15 +441,19 @@ __global__ void __launch_bounds__(kWarps * 32, 2)
         }
         int rank = 0;
 #pragma unroll 4
-        for (int o = 0; o < 32; ++o) {
-            const double So = __shfl_sync(FULL_MASK, S, o);
-            const int io = __shfl_sync(FULL_MASK, ci, o);
+        for (int o = 0; o < SEG; ++o) {
+            const double So = __shfl_sync(FULL_MASK, S, o, SEG);
+            const int io = __shfl_sync(FULL_MASK, ci, o, SEG);
             rank += ((So < S) || (So == S && io < ci)) ? 1 : 0;
         }
-        // k-th smallest exact key among the survivors (inf when fewer than k exist)
-        const unsigned mk = __ballot_sync(FULL_MASK, ci >= 0 && rank == k - 1);
-        const double Sk = mk ? __shfl_sync(FULL_MASK, S, __ffs(mk) - 1) : INFINITY;
-        const double T = (double)thr[qi];
+        // k-th smallest exact key among this segment's survivors (inf when fewer than k exist)
+        const unsigned mk_all = __ballot_sync(FULL_MASK, ci >= 0 && rank == k - 1);
+        const unsigned mk = (mk_all >> ((SEG * seg) & 31)) & SEGMASK;
+        const double Sk_src = __shfl_sync(FULL_MASK, S, mk ? (__ffs(mk) - 1) : 0, SEG);
+        const double Sk = mk ? Sk_src : INFINITY;
+        const unsigned valid_all = __ballot_sync(FULL_MASK, ci >= 0);
+        const int nvalid = __popc((valid_all >> ((SEG * seg) & 31)) & SEGMASK);
+        const double T = (double)T32;
         bool ok = isinf(T) && T > 0;   // list never filled: every sample is a survivor
         if (!ok) {
             // every sample outside the list has computed key >= T, hence exact squared
@@ -406,20 +470,21 @@ __global__ void __launch_bounds__(kWarps * 32, 2)
             }
             ok = (Sk < bound) || (r2 <= bound);
         }
-        if (ok) {
-            if (ci >= 0 && rank < k) {
-                const bool keep = S < r2;
-                out_idx[q * k + rank] = keep ? (int64_t)ci : -1;
-                if (out_dist) out_dist[q * k + rank] = keep ? __dsqrt_rn(S) : INFINITY;
+        if (qvalid) {
+            if (ok) {
+                if (ci >= 0 && rank < k) {
+                    const bool keep = S < r2;
+                    out_idx[q * k + rank] = keep ? (int64_t)ci : -1;
+                    if (out_dist) out_dist[q * k + rank] = keep ? __dsqrt_rn(S) : INFINITY;
+                }
+                if (sl < k && sl >= nvalid) {
+                    out_idx[q * k + sl] = -1;
+                    if (out_dist) out_dist[q * k + sl] = INFINITY;
+                }
+            } else if (sl == 0) {
+                const int pos = atomicAdd(&h->fb_count, 1);
+                fb_list[pos] = (int)q;
             }
-            const int nvalid = __popc(__ballot_sync(FULL_MASK, ci >= 0));
-            if (lane < k && lane >= nvalid) {
-                out_idx[q * k + lane] = -1;
-                if (out_dist) out_dist[q * k + lane] = INFINITY;
-            }
-        } else if (lane == 0) {
-            const int pos = atomicAdd(&h->fb_count, 1);
-            fb_list[pos] = (int)q;
         }
     }
 }
@@ -503,23 +568,37 @@ int launch_prepare(const double *x, int64_t N, const Weights &wt, void *ws, cuda
     return MPB_OK;
 }
 
+template <int D, int Q, int SEG>
+int launch_filter(const double *x, int64_t N, const double *qs, int64_t M, const Weights &wt, int k, double r2,
+                  const float4 *packed, int n_tiles, KnnHeader *h, int *fb, int64_t *out_idx, double *out_dist,
+                  cudaStream_t st)
+{
+    using SM = FilterSmem<D, Q>;
+    MPB_CUDA_CHECK(cudaFuncSetAttribute(knn_filter_kernel<D, Q, SEG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)SM::BYTES));
+    const int64_t blocks = (M + (int64_t)kWarps * Q - 1) / ((int64_t)kWarps * Q);
+    knn_filter_kernel<D, Q, SEG><<<(unsigned)blocks, kWarps * 32, SM::BYTES, st>>>(x, N, qs, M, wt, k, r2, packed,
+                                                                                  n_tiles, h, fb, out_idx, out_dist);
+    MPB_LAUNCH_CHECK();
+    return MPB_OK;
+}
+
 template <int D>
 int launch_search(const double *x, int64_t N, const double *qs, int64_t M, const Weights &wt, int k, double r2,
                   void *ws, int64_t *out_idx, double *out_dist, int64_t *stats, cudaStream_t st)
 {
     constexpr int Q = (D <= 8) ? 8 : 4;
-    using SM = FilterSmem<D, Q>;
     const WsLayout L = ws_layout(N, M, D);
     KnnHeader *h = reinterpret_cast<KnnHeader *>(ws);
     const float4 *packed = reinterpret_cast<const float4 *>(reinterpret_cast<char *>(ws) + L.packed_off);
     int *fb = reinterpret_cast<int *>(reinterpret_cast<char *>(ws) + L.fb_off);
     MPB_CUDA_CHECK(cudaMemsetAsync(&h->fb_count, 0, sizeof(int), st));
-    MPB_CUDA_CHECK(cudaFuncSetAttribute(knn_filter_kernel<D, Q>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        (int)SM::BYTES));
-    const int64_t blocks = (M + (int64_t)kWarps * Q - 1) / ((int64_t)kWarps * Q);
-    knn_filter_kernel<D, Q><<<(unsigned)blocks, kWarps * 32, SM::BYTES, st>>>(
-        x, N, qs, M, wt, k, r2, packed, (int)L.n_tiles, h, fb, out_idx, out_dist);
-    MPB_LAUNCH_CHECK();
+    // 16 survivors per query leave a comfortable certificate margin up to k = 12 (a PRM's k + 1 = 11) and
+    // halve the insertion work; larger k keeps 32
+    int rc = (k <= kSmallListMaxK)
+                 ? launch_filter<D, Q, 16>(x, N, qs, M, wt, k, r2, packed, (int)L.n_tiles, h, fb, out_idx, out_dist, st)
+                 : launch_filter<D, Q, 32>(x, N, qs, M, wt, k, r2, packed, (int)L.n_tiles, h, fb, out_idx, out_dist, st);
+    if (rc != MPB_OK) return rc;
     return launch_exact<D>(x, N, qs, M, wt, MPB_METRIC_KDTREE, k, r2, fb, &h->fb_count, out_idx, out_dist, stats, st);
 }
 
