@@ -179,6 +179,17 @@ int mpb_knn_f32filter_static(const double *samples, int64_t n_samples, const dou
 int mpb_trees_nearest(const double *nodes, const int32_t *sizes, int64_t n_trees, int64_t cap,
                       int dim, const double *targets, const double *weights, int metric,
                       const uint8_t *active, int32_t *out_idx, double *out_dist, void *stream);
+/* Append the kept part of one extension per entry to resident trees (primitives.py:24-27: one TreeNode per
+ * safe waypoint, each the child of the previous one, the first the child of parent0).  Entry b extends tree
+ * tree_ids[b] (negative = skip; at most one entry per tree per call): the waypoints of extend_fn(from[b],
+ * to[b]) with generation index in [lo[b], hi[b]) are stored at the end of the tree, in generation order, or
+ * reversed when reverse[b] != 0 (the backward extension of primitives.py:13-16).  nodes dev [T, cap, dim] f64,
+ * parents dev [T, cap] i32, sizes dev [T] i32 (updated); out_last[b] = index of the last node stored (parent0[b]
+ * when nothing was kept); *out_overflow is incremented for every entry that did not fit in cap (left unstored). */
+int mpb_trees_append(double *nodes, int32_t *parents, int32_t *sizes, int64_t n_trees, int64_t cap, int dim,
+                     const int32_t *tree_ids, const double *from, const double *to, const int32_t *lo,
+                     const int32_t *hi, const uint8_t *reverse, const int32_t *parent0, int64_t n_ext,
+                     double step, int32_t *out_last, int32_t *out_overflow, void *stream);
 /* One tree: nearest node to q and every node with distance_fn(node, q) < radius
  * (rrt_star.py:117,128).  out_nearest dev [1] i32; out_dist dev [n] f64 receives all
  * distances; out_count dev [1] i32; out_list dev [n] i32 the qualifying indices ascending. */

@@ -41,7 +41,13 @@ __global__ void __launch_bounds__(256)
     const int lane = threadIdx.x & 31;
     const int64_t t = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (t >= T) return;
-    if (active && !active[t]) return;
+    if (active && !active[t]) {   // skipped trees report "no node"
+        if (lane == 0) {
+            out_idx[t] = -1;
+            if (out_dist) out_dist[t] = INFINITY;
+        }
+        return;
+    }
     double tg[D];
 #pragma unroll
     for (int d = 0; d < D; ++d) tg[d] = targets[t * D + d];
@@ -135,6 +141,79 @@ __global__ void __launch_bounds__(1024)
     }
 }
 
+// Append the kept part of an extension to a tree (primitives.py:24-27: one TreeNode per safe waypoint,
+// chained parent -> child).  One thread per extension: the waypoints from `from` to `to` are regenerated
+// with the reference recurrence (tkinter/samplers.py:121-126) and those with generation index in [lo, hi)
+// are stored, in generation order (forward extension) or reversed (backward extension, primitives.py:13-16).
+template <int D>
+__global__ void __launch_bounds__(128)
+    trees_append_kernel(double *__restrict__ nodes, int32_t *__restrict__ parents, int32_t *__restrict__ sizes,
+                        int64_t cap, const int32_t *__restrict__ tree_ids, const double *__restrict__ from,
+                        const double *__restrict__ to, const int32_t *__restrict__ lo, const int32_t *__restrict__ hi,
+                        const uint8_t *__restrict__ reverse, const int32_t *__restrict__ parent0, int64_t B,
+                        double step, int32_t *__restrict__ out_last, int32_t *__restrict__ out_overflow)
+{
+    const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    const int t = tree_ids[b];
+    if (t < 0) {
+        out_last[b] = -1;
+        return;
+    }
+    double a[D], q2[D], q[D];
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        a[d] = from[b * D + d];
+        q2[d] = to[b * D + d];
+        q[d] = a[d];
+    }
+    double m = 0.;
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        const double v = fabs(__ddiv_rn(d_sub(q2[d], a[d]), step));
+        m = (v > m) ? v : m;
+    }
+    if (!(m < 2147483000.)) m = 2147483000.;
+    const int n = (int)m + 1;
+    const int l = lo[b], h = min(hi[b], n);
+    const int keep = max(h - l, 0);
+    const int size = sizes[t];
+    if ((int64_t)size + keep > cap) {
+        atomicAdd(out_overflow, 1);
+        out_last[b] = parent0[b];
+        return;
+    }
+    double *base = nodes + (int64_t)t * cap * D;
+    int32_t *par = parents + (int64_t)t * cap;
+    const bool rev = reverse[b] != 0;
+    for (int i = 0; i < h; ++i) {
+        const double c = __ddiv_rn(1.0, (double)(n - i));
+#pragma unroll
+        for (int d = 0; d < D; ++d) q[d] = d_add(d_mul(c, d_sub(q2[d], q[d])), q[d]);
+        if (i >= l) {
+            const int pos = size + (rev ? (h - 1 - i) : (i - l));
+#pragma unroll
+            for (int d = 0; d < D; ++d) base[(int64_t)pos * D + d] = q[d];
+            par[pos] = (pos == size) ? parent0[b] : pos - 1;
+        }
+    }
+    sizes[t] = size + keep;
+    out_last[b] = keep > 0 ? size + keep - 1 : parent0[b];
+}
+
+template <int D>
+int launch_append(double *nodes, int32_t *parents, int32_t *sizes, int64_t cap, const int32_t *tree_ids,
+                  const double *from, const double *to, const int32_t *lo, const int32_t *hi, const uint8_t *reverse,
+                  const int32_t *parent0, int64_t B, double step, int32_t *out_last, int32_t *out_overflow,
+                  cudaStream_t st)
+{
+    trees_append_kernel<D><<<(unsigned)((B + 127) / 128), 128, 0, st>>>(nodes, parents, sizes, cap, tree_ids, from, to,
+                                                                        lo, hi, reverse, parent0, B, step, out_last,
+                                                                        out_overflow);
+    MPB_LAUNCH_CHECK();
+    return MPB_OK;
+}
+
 template <int D>
 int launch_trees(const double *nodes, const int32_t *sizes, int64_t T, int64_t cap, const double *targets,
                  const Weights &wt, int metric, const uint8_t *active, int32_t *out_idx, double *out_dist,
@@ -193,6 +272,25 @@ MPB_API int mpb_scan_nearest_radius(const double *nodes, int64_t n, int dim, con
     const Weights wt = make_weights(weights, dim);
     cudaStream_t st = (cudaStream_t)stream;
 #define CALL(DD) launch_scan<DD>(nodes, n, q, wt, metric, radius, out_nearest, out_dist, out_count, out_list, st)
+    MPB_DISPATCH_DIM(dim, CALL)
+#undef CALL
+    return MPB_EINVAL;
+}
+
+MPB_API int mpb_trees_append(double *nodes, int32_t *parents, int32_t *sizes, int64_t n_trees, int64_t cap, int dim,
+                             const int32_t *tree_ids, const double *from, const double *to, const int32_t *lo,
+                             const int32_t *hi, const uint8_t *reverse, const int32_t *parent0, int64_t n_ext,
+                             double step, int32_t *out_last, int32_t *out_overflow, void *stream)
+{
+    MPB_REQUIRE(dim >= 1 && dim <= MPB_MAX_DIM, "mpb_trees_append: dim %d outside [1, %d]", dim, MPB_MAX_DIM);
+    MPB_REQUIRE(n_trees >= 0 && cap >= 0 && n_ext >= 0, "mpb_trees_append: negative size");
+    MPB_REQUIRE(step > 0., "mpb_trees_append: step must be positive");
+    if (n_ext == 0) return MPB_OK;
+    MPB_REQUIRE(nodes && parents && sizes && tree_ids && from && to && lo && hi && reverse && parent0 && out_last &&
+                    out_overflow,
+                "mpb_trees_append: NULL buffer");
+    cudaStream_t st = (cudaStream_t)stream;
+#define CALL(DD) launch_append<DD>(nodes, parents, sizes, cap, tree_ids, from, to, lo, hi, reverse, parent0, n_ext, step, out_last, out_overflow, st)
     MPB_DISPATCH_DIM(dim, CALL)
 #undef CALL
     return MPB_EINVAL;

@@ -261,6 +261,19 @@ def trees_nearest(nodes, sizes, targets, weights=None, metric=METRIC_SAMPLERS, a
     return idx, dist
 
 
+def trees_append(nodes, parents, sizes, tree_ids, frm, to, lo, hi, reverse, parent0, overflow, step=STEP_SIZE):
+    """Store the kept waypoints of one extension per entry at the end of resident trees (see
+    mpb_trees_append).  -> out_last [B] int32; `overflow` (int32 [1]) counts entries that did not fit."""
+    T, cap, D = nodes.shape
+    B = tree_ids.shape[0]
+    out_last = torch.empty(B, dtype=torch.int32, device=nodes.device)
+    rc = _lib.lib().mpb_trees_append(_ptr(nodes), _ptr(parents), _ptr(sizes), T, cap, D, _ptr(tree_ids), _ptr(frm),
+                                     _ptr(to), _ptr(lo), _ptr(hi), _ptr(reverse), _ptr(parent0), B, float(step),
+                                     _ptr(out_last), _ptr(overflow), _stream())
+    _lib.check(rc, "mpb_trees_append")
+    return out_last
+
+
 def scan_nearest_radius(nodes, q, radius, weights=None, metric=METRIC_SAMPLERS):
     """Nearest node and every node closer than `radius` (rrt_star.py:117,128).
     -> (nearest [1] int32, dist [n] float64, count [1] int32, list [n] int32)."""

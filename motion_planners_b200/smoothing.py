@@ -1,0 +1,127 @@
+"""Shortcut smoothing of a path (the step right after every planner).
+
+Same contract as the reference's motion_planners/smoothing.py:51-144 smooth_path: per iteration two
+segments are drawn with probability proportional to their length (np.random.choice), one point on each
+(random.choice over the segment's waypoints), and the bridge between the two points replaces the part of
+the path between them when it is shorter and collision free.  The random draws are made by the same
+library calls in the same order as the reference, so a seeded run consumes the same streams.
+The two point checks and the bridge's edge check of an iteration go to the device in one launch each
+when the accelerated primitives are in use.
+"""
+import time
+from random import choice
+
+import numpy as np
+
+from . import ops
+from .primitives import GpuCollisionFn, GpuExtendFn
+from .utils import INF, bisect_order, compute_path_cost, elapsed_time, get_pairs
+
+
+def _unit(vec):
+    norm = np.linalg.norm(vec)
+    return vec if norm == 0 else np.array(vec) / norm
+
+
+def remove_redundant(path, tolerance=1e-3):
+    """Drop configurations closer than `tolerance` (per coordinate) to the last kept one (utils.py:205-212)."""
+    assert path
+    kept = [path[0]]
+    for conf in path[1:]:
+        diff = np.array(kept[-1]) - np.array(conf)
+        if not np.allclose(np.zeros(len(diff)), diff, atol=tolerance, rtol=0):
+            kept.append(conf)
+    return kept
+
+
+def waypoints_from_path(path, tolerance=1e-3):
+    """Corner points of a densely sampled path: a configuration is kept where the unit direction from the
+    last kept corner changes by more than `tolerance` (utils.py:215-232)."""
+    path = remove_redundant(path, tolerance=tolerance)
+    if len(path) < 2:
+        return path
+    corners = [path[0]]
+    last_conf = path[1]
+    last_dir = _unit(np.array(last_conf) - np.array(corners[-1]))
+    for conf in path[2:]:
+        direction = _unit(np.array(conf) - np.array(corners[-1]))
+        if not np.allclose(last_dir, direction, atol=tolerance, rtol=0):
+            corners.append(last_conf)
+            direction = _unit(np.array(conf) - np.array(corners[-1]))
+        last_conf = conf
+        last_dir = direction
+    corners.append(last_conf)
+    return corners
+
+
+def refine_waypoints(waypoints, extend_fn):
+    """Concatenated extend_fn output over consecutive corners (utils.py:235-238)."""
+    out = []
+    for q1, q2 in get_pairs(waypoints):
+        out.extend(extend_fn(q1, q2))
+    return out
+
+
+def _bridge_collides(shortcut, extend_fn, collision_fn):
+    """any(map(collision_fn, shortcut)) or any collision along refine_waypoints(shortcut)[:-1]."""
+    if isinstance(collision_fn, GpuCollisionFn) and isinstance(extend_fn, GpuExtendFn):
+        pts = np.ascontiguousarray(np.array([np.asarray(p, dtype=np.float64) for p in shortcut]))
+        if bool(collision_fn.batch(pts).any().item()):
+            return True
+        import torch
+        hit, _ = collision_fn.obstacles.edges_check_pairs(torch.from_numpy(pts[:1]).cuda(),
+                                                          torch.from_numpy(pts[1:2]).cuda(), mode=ops.EDGE_ANY,
+                                                          skip_last=True, step=extend_fn.step_size, want_counts=False)
+        return bool(hit[0].item() >= 0)
+    if any(collision_fn(q) for q in shortcut):
+        return True
+    dense = refine_waypoints(shortcut, extend_fn)[:-1]
+    return any(collision_fn(dense[i]) for i in bisect_order(len(dense)))
+
+
+def smooth_path(path, extend_fn, collision_fn, distance_fn=None, cost_fn=None, sample_fn=None, max_iterations=100,
+                max_time=INF, converge_fraction=0.0, converge_time=INF, print_frequency=1., verbose=False):
+    """:return: smoothed, re-discretised path (smoothing.py:51-144)."""
+    start_time = last_time = time.time()
+    if not path or not max_iterations:
+        return path
+    assert (max_iterations < INF) or (max_time < INF) or (converge_time < INF)
+    if distance_fn is None:
+        distance_fn = lambda q1, q2: len(list(extend_fn(q1, q2)))      # primitives.py:65-70
+    if cost_fn is None:
+        cost_fn = distance_fn
+    waypoints = waypoints_from_path(path)
+    cost = compute_path_cost(waypoints, cost_fn=cost_fn)
+    iteration = 0
+    while iteration < max_iterations:
+        iteration += 1
+        if (max_time - elapsed_time(start_time) <= 0.) or (converge_time - elapsed_time(last_time) <= 0.) or \
+                (len(waypoints) <= 2):
+            break
+        segments = get_pairs(range(len(waypoints)))
+        weights = [distance_fn(waypoints[i], waypoints[j]) for i, j in segments]
+        probabilities = np.array(weights) / sum(weights)
+        seg_indices = list(range(len(segments)))
+        seg_idx1, seg_idx2 = np.random.choice(seg_indices, size=2, replace=True, p=probabilities)
+        if seg_idx1 == seg_idx2:
+            continue
+        if seg_idx2 < seg_idx1:
+            seg_idx1, seg_idx2 = seg_idx2, seg_idx1
+        segment1, segment2 = segments[seg_idx1], segments[seg_idx2]
+        paths = [list(extend_fn(waypoints[i], waypoints[j]))[:-1] for i, j in [segment1, segment2]]
+        if not all(paths):
+            continue
+        point1, point2 = [choice(p) for p in paths]
+        i, _ = segment1
+        _, j = segment2
+        shortcut = [point1, point2]
+        new_waypoints = waypoints[:i + 1] + shortcut + waypoints[j:]
+        new_cost = compute_path_cost(new_waypoints, cost_fn=cost_fn)
+        improve_fraction = (cost - new_cost) / cost
+        if (new_cost >= cost) or (improve_fraction <= converge_fraction) or \
+                _bridge_collides(shortcut, extend_fn, collision_fn):
+            continue
+        waypoints = new_waypoints
+        cost = new_cost
+        last_time = time.time()
+    return [waypoints[0]] + refine_waypoints(waypoints, extend_fn)

@@ -361,8 +361,46 @@ def gen_rrt_star():
               **_world_arrays(world))
 
 
+# ------------------------------------------------------------------------- birrt
+def gen_birrt():
+    """birrt() = random_restarts(rrt_connect) + smooth_path (rrt_connect.py:76-93, meta.py:46-86,
+    smoothing.py:51-144) under fixed seeds; both global generators are consumed."""
+    from motion_planners.rrt_connect import birrt
+    from motion_planners.tkinter.samplers import get_collision_fn, get_distance_fn, get_extend_fn, get_sample_fn
+    ext = get_extend_fn()
+    for name, nq, iters, seed0 in [("problem1", 6, 80, 120), ("mixed3d", 5, 100, 140)]:
+        world = WORLDS[name]()
+        env, obs = _ref_world(world)
+        col = get_collision_fn(env, obs)
+        D = world.dim
+        dist = get_distance_fn(np.ones(D))
+        starts, goals, solved, lens, flat, seeds = [], [], [], [], [], []
+        for q in range(nq):
+            seed = seed0 + q
+            random.seed(seed)
+            np.random.seed(seed)
+            cfree = get_sample_fn(env, obstacles=obs, use_halton=False)
+            start, goal = cfree(), cfree()
+            random.seed(seed)
+            np.random.seed(seed)
+            sample_fn = get_sample_fn(env, obstacles=[], use_halton=False)
+            with redirect_stdout(io.StringIO()):
+                path = birrt(start, goal, dist, sample_fn, ext, col, max_iterations=iters, smooth=20, restarts=2)
+            starts.append(start)
+            goals.append(goal)
+            seeds.append(seed)
+            solved.append(path is not None)
+            p = np.array(path) if path is not None else np.zeros((0, D))
+            lens.append(len(p))
+            flat.append(p)
+        _save("birrt_%s" % name, starts=np.array(starts), goals=np.array(goals), seeds=np.array(seeds, np.int64),
+              max_iterations=np.int64(iters), solved=np.array(solved), path_len=np.array(lens, np.int64),
+              paths=np.concatenate(flat), **_world_arrays(world))
+
+
 GENERATORS = {"knn": gen_knn, "extend": gen_extend, "collide": gen_collide, "edges": gen_edges, "dist": gen_dist,
-              "lazy_prm": gen_lazy_prm, "prm": gen_prm, "rrt_connect": gen_rrt_connect, "rrt_star": gen_rrt_star}
+              "lazy_prm": gen_lazy_prm, "prm": gen_prm, "rrt_connect": gen_rrt_connect, "rrt_star": gen_rrt_star,
+              "birrt": gen_birrt}
 
 
 def main(argv):

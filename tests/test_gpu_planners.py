@@ -163,3 +163,128 @@ def test_prm_small_candidate_budget_takes_the_full_ranking_path(mp, golden):
                target_degree=int(g["target_degree"]))
     edges = np.array([(e.v1.index, e.v2.index) for e in rm.edges], np.int64).reshape(-1, 2)
     assert edges.shape == g["edges"].shape and (edges == g["edges"]).all()
+
+
+# ----------------------------------------------------------------------------- tree planners
+def _tree_primitives(mp, world):
+    D = world.dim
+    return (mp.primitives.get_distance_fn(np.ones(D)), mp.primitives.get_extend_fn(),
+            mp.primitives.GpuCollisionFn(world))
+
+
+def _paths_from(g):
+    off = np.concatenate([[0], np.cumsum(g["path_len"])])
+    return [g["paths"][off[i]:off[i + 1]] if g["solved"][i] else None for i in range(len(g["solved"]))]
+
+
+@pytest.mark.parametrize("name", ["problem1", "boxes7d", "mixed3d"])
+def test_rrt_connect_matches_reference_runs(mp, golden, name):
+    """rrt_connect() under the same seeds as the reference run (rrt_connect.py:31-72): identical paths,
+    both through the drop-in entry point (global generators) and through the batched form fed with the
+    pre-drawn per-query streams."""
+    import random
+    from motion_planners_b200.rrt_connect import rrt_connect, rrt_connect_batch
+    g = golden("rrt_connect_" + name)
+    world = _world(mp, g)
+    dist, ext, col = _tree_primitives(mp, world)
+    env, _ = world.shapes()
+    ref_paths = _paths_from(g)
+    iters = int(g["max_iterations"])
+    D = world.dim
+    # drop-in entry point: seeds the global generators exactly as the fixture generator did
+    for q in range(len(ref_paths)):
+        seed = int(g["seeds"][q])
+        random.seed(seed)
+        np.random.seed(seed)
+        sample_fn = mp.primitives.get_sample_fn(env, obstacles=[])
+        path = rrt_connect(g["starts"][q], g["goals"][q], dist, sample_fn, ext, col, max_iterations=iters)
+        assert (path is None) == (ref_paths[q] is None)
+        if path is not None:
+            arr = np.array(path)
+            assert arr.shape == ref_paths[q].shape and (arr == ref_paths[q]).all()
+    # batched form: all queries in lock step, each with its own streams
+    B = len(ref_paths)
+    u = np.empty((B, iters))
+    tg = np.empty((B, iters, D))
+    for q in range(B):
+        seed = int(g["seeds"][q])
+        r = random.Random(seed)
+        u[q] = [r.random() for _ in range(iters)]
+        tg[q] = np.random.RandomState(seed).uniform(size=(iters, D))
+    paths = rrt_connect_batch(g["starts"], g["goals"], dist, ext, col, u, tg)
+    for q in range(B):
+        assert (paths[q] is None) == (ref_paths[q] is None)
+        if paths[q] is not None:
+            arr = np.array(paths[q])
+            assert arr.shape == ref_paths[q].shape and (arr == ref_paths[q]).all()
+
+
+@pytest.mark.parametrize("name", ["problem1", "mixed3d"])
+def test_rrt_star_matches_reference_run(mp, golden, name):
+    """rrt_star() as executed on Python 3 (rrt_star.py:86-146): identical path, cost within 1e-9."""
+    import random
+    from motion_planners_b200.rrt_star import rrt_star
+    g = golden("rrt_star_" + name)
+    world = _world(mp, g)
+    dist, ext, col = _tree_primitives(mp, world)
+    env, _ = world.shapes()
+    seed = int(g["seed"])
+    random.seed(seed)
+    np.random.seed(seed)
+    sample_fn = mp.primitives.get_sample_fn(env, obstacles=[])
+    path = rrt_star(g["start"], g["goal"], dist, sample_fn, ext, col, radius=float(g["radius"]),
+                    max_iterations=int(g["max_iterations"]))
+    assert (path is not None) == bool(g["solved"])
+    arr = np.array(path)
+    assert arr.shape == g["path"].shape and (arr == g["path"]).all()
+    cost = sum(dist(a, b) for a, b in zip(arr[:-1], arr[1:]))
+    assert abs(cost - float(g["cost"])) <= 1e-9 * float(g["cost"])
+
+
+@pytest.mark.parametrize("name", ["problem1", "mixed3d"])
+def test_birrt_matches_reference_runs(mp, golden, name):
+    """birrt() = restarts of rrt_connect + shortcut smoothing (meta.py:46-86, smoothing.py:51-144)."""
+    import io
+    import random
+    from contextlib import redirect_stdout
+    from motion_planners_b200.rrt_connect import birrt
+    g = golden("birrt_" + name)
+    world = _world(mp, g)
+    dist, ext, col = _tree_primitives(mp, world)
+    env, _ = world.shapes()
+    ref_paths = _paths_from(g)
+    for q in range(len(ref_paths)):
+        seed = int(g["seeds"][q])
+        random.seed(seed)
+        np.random.seed(seed)
+        sample_fn = mp.primitives.get_sample_fn(env, obstacles=[])
+        with redirect_stdout(io.StringIO()):
+            path = birrt(g["starts"][q], g["goals"][q], dist, sample_fn, ext, col,
+                         max_iterations=int(g["max_iterations"]), smooth=20, restarts=2)
+        assert (path is None) == (ref_paths[q] is None)
+        if path is not None:
+            arr = np.array(path)
+            assert arr.shape == ref_paths[q].shape and (arr == ref_paths[q]).all()
+
+
+def test_solve_dispatch(mp, golden):
+    from motion_planners_b200.meta import solve
+    g = golden("collide_problem1")
+    world = _world(mp, g)
+    dist, ext, col = _tree_primitives(mp, world)
+    env, _ = world.shapes()
+    import random
+    random.seed(3)
+    np.random.seed(3)
+    sample_fn = mp.primitives.get_sample_fn(env, obstacles=[])
+    start, goal = np.array([0.1, 0.1]), np.array([0.8, 0.8])
+    for alg in ("rrt_connect", "birrt", "prm", "lazy_prm"):
+        path = solve(start, goal, dist, sample_fn, ext, col, algorithm=alg, max_iterations=200, num_samples=200,
+                     weights=np.ones(2) if alg == "lazy_prm" else None)
+        assert path is not None
+        arr = np.array([np.asarray(q) for q in path])
+        assert not col.batch(arr).any()
+        assert np.allclose(arr[0], start) and np.allclose(arr[-1], goal, atol=1e-9)
+    with pytest.raises(NotImplementedError):
+        solve(start, goal, dist, sample_fn, ext, col, algorithm="lattice")
+    assert solve(np.array([0.5, 0.5]), goal, dist, sample_fn, ext, col) is False   # start inside the centre box
