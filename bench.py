@@ -156,6 +156,57 @@ def run_reference_arm(args, rank):
     return 0
 
 
+# ------------------------------------------------------------------------------- batched RRT extra
+def measure_rrt_batch(world_size, rank, dist, total_queries=4096, iters=100):
+    """configs[2]: a batch of independent 7-DoF RRT-Connect queries split over the ranks with no
+    communication; every query consumes its own pre-drawn random streams."""
+    import random as pyrandom
+    import torch
+    from motion_planners_b200 import primitives, workloads
+    from motion_planners_b200.roadmap import shard_bounds
+    from motion_planners_b200.rrt_connect import rrt_connect_batch
+    world = workloads.c3_world()
+    D = world.dim
+    col = primitives.GpuCollisionFn(world)
+    ext = primitives.get_extend_fn()
+    dfn = primitives.get_distance_fn(np.ones(D))
+    lo, hi = shard_bounds(total_queries, world_size, rank)
+    B = hi - lo
+    rs = np.random.RandomState(12345)
+    pool = rs.uniform(size=(8 * total_queries, D))
+    free = pool[~col.batch(pool).cpu().numpy()]
+    starts, goals = free[lo:hi], free[total_queries + lo:total_queries + hi]
+    u = np.empty((B, iters))
+    tg = np.empty((B, iters, D))
+    for q in range(B):
+        r = pyrandom.Random(1000 + lo + q)
+        u[q] = [r.random() for _ in range(iters)]
+        tg[q] = np.random.RandomState(1000 + lo + q).uniform(size=(iters, D))
+    rrt_connect_batch(starts[:64], goals[:64], dfn, ext, col, u[:64, :8], tg[:64, :8], retrace=False)   # warm-up
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    e0 = torch.cuda.Event(enable_timing=True)
+    e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    _, state = rrt_connect_batch(starts, goals, dfn, ext, col, u, tg, return_state=True, retrace=False)
+    e1.record()
+    e1.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], device="cuda", dtype=torch.float64)
+    solved = torch.tensor([int(state.solved.sum().item())], device="cuda", dtype=torch.int64)
+    ext_count = torch.tensor([2 * B * state.iterations], device="cuda", dtype=torch.int64)
+    if dist is not None:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(solved)
+        dist.all_reduce(ext_count)
+    sec = float(ms.item()) * 1e-3
+    return {"description": "configs[2]: %d independent 7-DoF rrt_connect queries, 64 boxes, %d iterations max, "
+                           "split over ranks, no communication" % (total_queries, iters),
+            "seconds": sec, "queries_per_s": total_queries / sec, "solved": int(solved.item()),
+            "tree_extensions_per_s": int(ext_count.item()) / sec, "iterations_run": int(state.iterations),
+            "kernel_launches": int(state.launches)}
+
+
 # ------------------------------------------------------------------------------------------- main
 def main():
     ap = argparse.ArgumentParser()
@@ -267,7 +318,13 @@ def main():
                 def e2e_step():
                     dev = pinned.cuda(non_blocking=True)
                     rm2.build(dev, gathered=rm2.gather_samples_equal(dev, gathered_buf) if equal else None)
-                    return rm2.nbr_idx.cpu(), rm2.vertex_hit.cpu(), rm2.edge_hit.cpu()
+                    outs = (rm2.nbr_idx, rm2.vertex_hit, rm2.edge_hit)
+                    if not hasattr(rm2, "_host_out"):
+                        rm2._host_out = tuple(torch.empty(o.shape, dtype=o.dtype).pin_memory() for o in outs)
+                    for hbuf, o in zip(rm2._host_out, outs):
+                        hbuf.copy_(o, non_blocking=True)
+                    torch.cuda.current_stream().synchronize()
+                    return rm2._host_out
                 for _ in range(2):
                     e2e_step()
                 barrier()
@@ -359,6 +416,9 @@ def main():
             "knn_queries_per_s": x["qps"], "edges_per_step": x["edges"], "phases_ms": x["phase_ms"],
             "knn_fp32_frac": (2.0 * x["D"] * x["n_local"] * x["n"] / (x_knn * 1e-3)) / fp32_peak,
             "fallback_queries": x["fallback_queries"], "clocks": x["clocks"]}
+
+    if not args.no_extra and args.workload == "c2":
+        line["extra_c3_rrt_connect_batch"] = measure_rrt_batch(world_size, rank, dist if world_size > 1 else None)
 
     if rank == 0:
         print(json.dumps(line))

@@ -141,7 +141,8 @@ class TreeBatch(object):
         return path1[:-1] + path2[::-1]
 
 
-def rrt_connect_batch(starts, goals, distance_fn, extend_fn, collision_fn, swap_draws, targets, return_state=False):
+def rrt_connect_batch(starts, goals, distance_fn, extend_fn, collision_fn, swap_draws, targets, return_state=False,
+                      retrace=True):
     """B independent rrt_connect runs.  starts, goals: [B, D]; swap_draws: [B, iters] uniforms in [0, 1);
     targets: [B, iters, D] sampled configurations (query q consumes column i at its iteration i).
     -> list of B paths (lists of numpy configs) or None."""
@@ -162,7 +163,8 @@ def rrt_connect_batch(starts, goals, distance_fn, extend_fn, collision_fn, swap_
         if (i & 15) == 15 and not bool(state.active.any().item()):
             break
     state.check_overflow()
-    paths = [state.path(q) for q in range(B)]
+    state.iterations = i + 1 if iters else 0
+    paths = [state.path(q) for q in range(B)] if retrace else None
     return (paths, state) if return_state else paths
 
 
