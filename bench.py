@@ -5,6 +5,11 @@
     python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N --steps K --warmup W
     python bench.py --impl reference ...                                (CPU arm: the oracle port)
 
+Default workload: `c4lite` = configs[3], the samples-sharded + all-gathered PRM that BASELINE.json's
+"at 1/2/4/8 B200" metric and its target (1M samples, 7-DoF, k=10) are quoted on, with the reference's own
+box primitives (the sphere-approximated arm has no counterpart in the reference); it fits one GPU.
+`extra_c2` in the same line is configs[1] (100k x 6-DoF, 64 boxes).
+
 A step = one pass of the hot path over one synthetic roadmap: [all-gather of the sample shards when
 N > 1] -> kNN (k+1 = 11) of every sample of this rank's shard against the global set -> collision_fn
 on the shard's vertices -> extend_fn + collision_fn on every directed sample->neighbour edge.
@@ -26,13 +31,16 @@ if ROOT not in sys.path:
 
 import numpy as np  # noqa: E402
 
+NCU_DRAM_BYTES_PER_LAUNCH = {"c4lite": 1.012007e9 + 184.279808e6}
+
 METRIC = "PRM edges collision-checked/sec (kNN k=10 + vertex + edge checks per roadmap build step)"
 UNIT = "edges/s"
 
 WORKLOADS = {
     # name -> (world factory name, dim, n_samples, k, description)
     "c2": ("c2_world", 6, 100000, 10, "configs[1]: lazy-PRM roadmap, 100k samples, 6-DoF unit cube, 64 random boxes, k=10"),
-    "c4lite": ("c4lite_world", 7, 1000000, 10, "configs[3] with reference primitives: 1M samples, 7-DoF, 256 C-space boxes, k=10"),
+    "c4lite": ("c4lite_world", 7, 1000000, 10, "configs[3] (the sharded, all-gathered PRM the 1/2/4/8-GPU metric and the "
+               "north-star target are quoted on) with reference primitives: 1M samples, 7-DoF, 256 C-space boxes, k=10"),
     "c1": ("c1", 2, 2000, 10, "configs[0]: 2-D demo fixture, 2k samples, k=10"),
 }
 
@@ -100,7 +108,7 @@ class ClockSampler(object):
 
 
 # --------------------------------------------------------------------------------------- CPU arms
-def cpu_sample_rate(world, X, k, budget_s=12.0, first=4000):
+def cpu_sample_rate(world, X, k, budget_s=12.0, first=8000):
     """The oracle port on a bounded sample: the first `first` queries (grown until ~budget_s of CPU work)."""
     from oracle import cpu_baseline
     from scipy.spatial import KDTree
@@ -214,7 +222,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default=os.environ.get("MPB_BENCH_WORKLOAD", "c2"), choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default=os.environ.get("MPB_BENCH_WORKLOAD", "c4lite"), choices=sorted(WORKLOADS))
     ap.add_argument("--ref-sample", type=int, default=100000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra", action="store_true", help="skip the extra 1M-sample measurement")
@@ -368,7 +376,9 @@ def main():
                        "only HBM and bf16 tensor peaks; nominal fp32 = 148 SM x 128 lanes x 2 x 1.965 GHz = 74.4)",
         "flops_per_pair": 2 * D, "survey_flops_per_pair": 3 * D,
         "frac_on_survey_count": (3.0 * D * m["n_local"] * n / (knn_ms * 1e-3)) / fp32_peak,
-        "traffic": None,
+        # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the committed ncu --set full capture
+        # (profiles/r1_ncu_full_knn_filter_edges_check_raw.csv); measured for the default workload only
+        "traffic": NCU_DRAM_BYTES_PER_LAUNCH.get(args.workload) if world_size == 1 else None,
         "kernel_ms": knn_ms,
         "hbm": {"achieved_gbs": step_bytes / (m["ms_step"] * 1e-3) / 1e9, "peak_gbs": hbm_peak,
                 "frac": (step_bytes / (m["ms_step"] * 1e-3) / 1e9 / hbm_peak) if hbm_peak else None,
@@ -408,16 +418,17 @@ def main():
             "value": p["n_edges"] / p["seconds"], "unit": UNIT, "cores": 1,
             "sample": "first 40 queries, %d edges, per-call Python structure of the reference" % p["n_edges"]}
 
-    if not args.no_extra and args.workload == "c2":
-        x = measure("c4lite", max(2, min(args.steps, 3)), 3, with_e2e=False)
+    if not args.no_extra:
+        other = "c2" if args.workload != "c2" else "c4lite"
+        x = measure(other, max(2, min(args.steps, 10 if other == "c2" else 3)), 3, with_e2e=False)
         x_knn = x["phase_ms"].get("knn", float("nan"))
-        line["extra_c4lite"] = {
+        line["extra_" + other] = {
             "description": x["desc"], "ms_per_step": x["ms_step"], "edges_per_s": x["value"],
             "knn_queries_per_s": x["qps"], "edges_per_step": x["edges"], "phases_ms": x["phase_ms"],
             "knn_fp32_frac": (2.0 * x["D"] * x["n_local"] * x["n"] / (x_knn * 1e-3)) / fp32_peak,
             "fallback_queries": x["fallback_queries"], "clocks": x["clocks"]}
 
-    if not args.no_extra and args.workload == "c2":
+    if not args.no_extra:
         line["extra_c3_rrt_connect_batch"] = measure_rrt_batch(world_size, rank, dist if world_size > 1 else None)
 
     if rank == 0:
