@@ -190,6 +190,25 @@ int mpb_trees_append(double *nodes, int32_t *parents, int32_t *sizes, int64_t n_
                      const int32_t *tree_ids, const double *from, const double *to, const int32_t *lo,
                      const int32_t *hi, const uint8_t *reverse, const int32_t *parent0, int64_t n_ext,
                      double step, int32_t *out_last, int32_t *out_overflow, void *stream);
+/* rrt_connect (rrt_connect.py:31-72) for n_queries independent queries in ONE launch, one thread block per
+ * query: per iteration the swap decision (rrt_connect.py:26-29) from swap_draws[q, it], the target
+ * targets[q, it, :] (the value sample_fn() returned), and two extend_towards steps (primitives.py:19-29) --
+ * block-wide first arg-min over the tree, the extend_fn waypoints (forward for the start tree, generated from
+ * the target and consumed reversed for the goal tree), collision_fn on every waypoint, one node per safe
+ * waypoint.  A query whose start or goal collides fails at once (rrt_connect.py:47).
+ * starts, goals dev [Q, dim]; swap_draws dev [Q, iters]; targets dev [Q, iters, dim]; weights HOST [dim];
+ * nodes dev [2Q, cap, dim] f64 / parents dev [2Q, cap] i32 / sizes dev [2Q] i32 receive the trees (tree 2q =
+ * start tree, 2q+1 = goal tree; contents on entry are ignored).  Per query: out_solved u8, out_iters i32
+ * (iterations consumed), out_swapped u8 (the swap flag of the connecting iteration) and out_last_a / out_last_b
+ * i32 = last node of the first- / second-extended tree of that iteration, from which the path is
+ * configs(path1[:-1] + path2[::-1]) (rrt_connect.py:65-71).  *out_overflow counts queries stopped because a
+ * tree reached cap.  Results equal composing mpb_trees_nearest, mpb_edges_check_pairs and mpb_trees_append. */
+int mpb_rrt_connect_batch(const mpb_world *world, const double *starts, const double *goals,
+                          int64_t n_queries, const double *weights, int metric, double step,
+                          const double *swap_draws, const double *targets, int iters, double *nodes,
+                          int32_t *parents, int32_t *sizes, int64_t cap, uint8_t *out_solved,
+                          int32_t *out_last_a, int32_t *out_last_b, uint8_t *out_swapped,
+                          int32_t *out_iters, int32_t *out_overflow, void *stream);
 /* One tree: nearest node to q and every node with distance_fn(node, q) < radius
  * (rrt_star.py:117,128).  out_nearest dev [1] i32; out_dist dev [n] f64 receives all
  * distances; out_count dev [1] i32; out_list dev [n] i32 the qualifying indices ascending. */

@@ -45,6 +45,8 @@ SIGNATURES = {
     "mpb_trees_nearest": (c_int, [c_vp, c_vp, c_i64, c_i64, c_int, c_vp, c_hostf64, c_int, c_vp, c_vp, c_vp, c_vp]),
     "mpb_trees_append": (c_int, [c_vp, c_vp, c_vp, c_i64, c_i64, c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64,
                                  c_dbl, c_vp, c_vp, c_vp]),
+    "mpb_rrt_connect_batch": (c_int, [c_vp, c_vp, c_vp, c_i64, c_hostf64, c_int, c_dbl, c_vp, c_vp, c_int, c_vp, c_vp,
+                                      c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "mpb_scan_nearest_radius": (c_int, [c_vp, c_i64, c_int, c_vp, c_hostf64, c_int, c_dbl, c_vp, c_vp, c_vp, c_vp,
                                         c_vp]),
     "mpb_peak_fma_f32": (c_int, [c_int, c_int, c_int, c_vp, c_vp]),

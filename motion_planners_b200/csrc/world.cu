@@ -94,80 +94,6 @@ MPB_API int mpb_world_destroy(mpb_world *w)
 }
 
 // ------------------------------------------------------------------------------------------
-// world staged in shared memory
-// ------------------------------------------------------------------------------------------
-// Layout (doubles): box bounds interleaved {lo, hi} per (box, dim); sphere centres; sphere
-// radii; environment {lo, hi} per dim.
-static size_t world_smem_bytes(const WorldDev &w)
-{
-    return sizeof(double) * (2 * (size_t)w.n_box * w.dim + (size_t)w.n_sph * (w.dim + 1) + 2 * (size_t)w.dim);
-}
-
-struct WorldSmem {
-    const double2 *box;   // [n_box * dim] {lo, hi}
-    const double *sph_c;  // [n_sph * dim]
-    const double *sph_rb; // [n_sph]
-    const double2 *env;   // [dim] {lo, hi}
-};
-
-__device__ __forceinline__ WorldSmem stage_world(const WorldDev &w, double *sm)
-{
-    const int nbd = w.n_box * w.dim, nsd = w.n_sph * w.dim;
-    double2 *box = reinterpret_cast<double2 *>(sm);
-    double *sc = sm + 2 * nbd;
-    double *sr = sc + nsd;
-    int env_off = 2 * nbd + nsd + w.n_sph;
-    env_off += env_off & 1;   // keep the {lo, hi} pairs 16-byte aligned
-    double2 *env = reinterpret_cast<double2 *>(sm + env_off);
-    for (int i = threadIdx.x; i < nbd; i += blockDim.x) box[i] = make_double2(w.box_lo[i], w.box_hi[i]);
-    for (int i = threadIdx.x; i < nsd; i += blockDim.x) sc[i] = w.sph_c[i];
-    for (int i = threadIdx.x; i < w.n_sph; i += blockDim.x) sr[i] = w.sph_rb[i];
-    for (int i = threadIdx.x; i < w.dim; i += blockDim.x) env[i] = make_double2(w.env_lo[i], w.env_hi[i]);
-    __syncthreads();
-    WorldSmem s = {box, sc, sr, env};
-    return s;
-}
-
-template <int D>
-__device__ __forceinline__ bool outside_env(const WorldSmem &s, const double (&q)[D])
-{
-    bool in = true;
-#pragma unroll
-    for (int d = 0; d < D; ++d) {
-        double2 e = s.env[d];
-        in = in && (e.x <= q[d]) && (q[d] <= e.y);
-    }
-    return !in;
-}
-
-template <int D>
-__device__ __forceinline__ bool in_box(const WorldSmem &s, int b, const double (&q)[D])
-{
-    const double2 *bb = s.box + b * D;
-    bool in = true;
-#pragma unroll
-    for (int d = 0; d < D; ++d) {
-        double2 e = bb[d];
-        in = in && (e.x <= q[d]) && (q[d] <= e.y);
-    }
-    return in;
-}
-
-// ||q - c||_2 <= r + buffer with numpy's norm: sqrt of a sequentially fused dot (viewer.py:80-82)
-template <int D>
-__device__ __forceinline__ bool in_sphere(const WorldSmem &s, int k, const double (&q)[D])
-{
-    const double *c = s.sph_c + k * D;
-    double acc = 0.;
-#pragma unroll
-    for (int d = 0; d < D; ++d) {
-        double x = d_sub(q[d], c[d]);
-        acc = __fma_rn(x, x, acc);
-    }
-    return __dsqrt_rn(acc) <= s.sph_rb[k];
-}
-
-// ------------------------------------------------------------------------------------------
 // collision_fn over points
 // ------------------------------------------------------------------------------------------
 template <int D>
@@ -230,27 +156,6 @@ MPB_API int mpb_points_check(const mpb_world *world, const double *q, int64_t n,
 // of obstacles per waypoint instead of all of them.  Culling cannot change a result: every
 // waypoint is a convex combination of the previous one and q2 up to < n*2^-50 relative
 // rounding, far inside the 1e-9 relative margin (culling is disabled for n > 10^6).
-template <int D>
-__device__ __forceinline__ int waypoint_count(const double (&a)[D], const double (&b)[D], double step)
-{
-    double m = 0.;
-#pragma unroll
-    for (int d = 0; d < D; ++d) {
-        double v = fabs(__ddiv_rn(d_sub(b[d], a[d]), step));   // |(q2-q1)/step|, samplers.py:119
-        m = (v > m) ? v : m;                                    // norm(ord=inf) = max |.|
-    }
-    if (!(m < 2147483000.)) m = 2147483000.;
-    return (int)m + 1;                                          // int() truncates; steps + 1
-}
-
-template <int D>
-__device__ __forceinline__ void waypoint_step(double (&q)[D], const double (&b)[D], int n, int i)
-{
-    const double c = __ddiv_rn(1.0, (double)(n - i));   // 1. / (num_steps - i)
-#pragma unroll
-    for (int d = 0; d < D; ++d) q[d] = d_add(d_mul(c, d_sub(b[d], q[d])), q[d]);
-}
-
 enum { TEST_ENV = 0, TEST_BOX = 1, TEST_SPH = 2 };
 
 // Replays the waypoints of one edge against one obstacle group; updates `best`.

@@ -39,7 +39,7 @@ class TreeBatch(object):
     """Device state of B bidirectional queries."""
 
     def __init__(self, starts, goals, distance_fn, extend_fn, collision_fn, extensions_per_tree,
-                 memory_budget=32 << 30):
+                 memory_budget=32 << 30, zero_fill=True):
         self.dist, self.ext, self.col = distance_fn, extend_fn, collision_fn
         world = collision_fn.world
         self.B, self.D = starts.shape
@@ -52,8 +52,12 @@ class TreeBatch(object):
         if 2 * self.B * cap * per_tree > memory_budget:
             cap = max(self.max_new + 1, int(memory_budget // (2 * self.B * per_tree)))
         self.cap = cap
-        self.nodes = torch.zeros((2 * self.B, cap, self.D), dtype=torch.float64, device=dev)
-        self.parents = torch.full((2 * self.B, cap), -1, dtype=torch.int32, device=dev)
+        if zero_fill:
+            self.nodes = torch.zeros((2 * self.B, cap, self.D), dtype=torch.float64, device=dev)
+            self.parents = torch.full((2 * self.B, cap), -1, dtype=torch.int32, device=dev)
+        else:   # the one-launch kernel writes the roots itself and never reads past a tree's size
+            self.nodes = torch.empty((2 * self.B, cap, self.D), dtype=torch.float64, device=dev)
+            self.parents = torch.empty((2 * self.B, cap), dtype=torch.int32, device=dev)
         self.sizes = torch.ones(2 * self.B, dtype=torch.int32, device=dev)
         self.nodes[0::2, 0] = torch.as_tensor(starts, dtype=torch.float64, device=dev)
         self.nodes[1::2, 0] = torch.as_tensor(goals, dtype=torch.float64, device=dev)
@@ -112,6 +116,36 @@ class TreeBatch(object):
         self.solved |= newly
         self.active = active & ~success
 
+    def run_fused(self, u, targets):
+        """All iterations of all queries in one launch (mpb_rrt_connect_batch): one thread block per query.
+        u: [B, iters], targets: [B, iters, D] CUDA float64."""
+        import ctypes
+        from . import _lib
+        B, iters = u.shape
+        dev = u.device
+        solved = torch.empty(B, dtype=torch.uint8, device=dev)
+        swapped = torch.empty(B, dtype=torch.uint8, device=dev)
+        last_a = torch.empty(B, dtype=torch.int32, device=dev)
+        last_b = torch.empty(B, dtype=torch.int32, device=dev)
+        its = torch.empty(B, dtype=torch.int32, device=dev)
+        starts = self.nodes[0::2, 0].contiguous()
+        goals = self.nodes[1::2, 0].contiguous()
+        w = np.ascontiguousarray(self.dist.weights, dtype=np.float64)
+        p = lambda t: ctypes.c_void_p(t.data_ptr())
+        rc = _lib.lib().mpb_rrt_connect_batch(
+            self.col.obstacles._h, p(starts), p(goals), B, w.ctypes.data_as(ctypes.POINTER(ctypes.c_double)),
+            int(self.dist.metric), float(self.ext.step_size), p(u), p(targets), int(iters), p(self.nodes),
+            p(self.parents), p(self.sizes), int(self.cap), p(solved), p(last_a), p(last_b), p(swapped), p(its),
+            p(self.overflow), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+        _lib.check(rc, "mpb_rrt_connect_batch")
+        self.solved = solved.bool()
+        self.swapped = swapped.bool()
+        self.last_a = last_a.long()
+        self.last_b = last_b.long()
+        self.iters_used = its
+        self.active = ~self.solved
+        self.launches += 1
+
     def check_overflow(self):
         if int(self.overflow.item()):
             raise MemoryError('tree capacity %d exceeded; raise extensions_per_tree / memory_budget' % self.cap)
@@ -130,6 +164,8 @@ class TreeBatch(object):
             chain = []
             i = int(leaf)
             while i >= 0:
+                if len(chain) > size:
+                    raise RuntimeError('corrupt parent chain in tree %d' % tree)
                 chain.append(nodes[i])
                 i = int(par[i])
             return chain[::-1]
@@ -142,10 +178,11 @@ class TreeBatch(object):
 
 
 def rrt_connect_batch(starts, goals, distance_fn, extend_fn, collision_fn, swap_draws, targets, return_state=False,
-                      retrace=True):
+                      retrace=True, fused=True):
     """B independent rrt_connect runs.  starts, goals: [B, D]; swap_draws: [B, iters] uniforms in [0, 1);
     targets: [B, iters, D] sampled configurations (query q consumes column i at its iteration i).
-    -> list of B paths (lists of numpy configs) or None."""
+    -> list of B paths (lists of numpy configs) or None.  fused=True runs everything in one launch
+    (mpb_rrt_connect_batch); fused=False composes the stand-alone kernels iteration by iteration."""
     if not _accelerated(distance_fn, extend_fn, collision_fn):
         raise TypeError('rrt_connect_batch needs the accelerated primitives of motion_planners_b200.primitives')
     starts = np.ascontiguousarray(np.asarray(starts, dtype=np.float64))
@@ -154,6 +191,15 @@ def rrt_connect_batch(starts, goals, distance_fn, extend_fn, collision_fn, swap_
     u = torch.as_tensor(np.asarray(swap_draws, dtype=np.float64)).cuda()
     tg = torch.as_tensor(np.asarray(targets, dtype=np.float64)).cuda()
     iters = u.shape[1]
+    if fused:
+        state = TreeBatch(starts, goals, distance_fn, extend_fn, collision_fn, extensions_per_tree=iters,
+                          zero_fill=False)
+        state.run_fused(u.contiguous(), tg.contiguous())
+        state.check_overflow()
+        state.iterations = int(state.iters_used.max().item()) if B else 0
+        paths = [state.path(q) for q in range(B)] if retrace else None
+        return (paths, state) if return_state else paths
+    # lock-step composition of the stand-alone kernels (kept as the cross-check of the fused launch)
     state = TreeBatch(starts, goals, distance_fn, extend_fn, collision_fn, extensions_per_tree=iters)
     # rrt_connect.py:47: a colliding start or goal fails the query before any iteration
     bad = collision_fn.batch(np.concatenate([starts, goals])).view(2, B).any(0)

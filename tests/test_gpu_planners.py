@@ -211,12 +211,41 @@ def test_rrt_connect_matches_reference_runs(mp, golden, name):
         r = random.Random(seed)
         u[q] = [r.random() for _ in range(iters)]
         tg[q] = np.random.RandomState(seed).uniform(size=(iters, D))
-    paths = rrt_connect_batch(g["starts"], g["goals"], dist, ext, col, u, tg)
-    for q in range(B):
-        assert (paths[q] is None) == (ref_paths[q] is None)
-        if paths[q] is not None:
-            arr = np.array(paths[q])
-            assert arr.shape == ref_paths[q].shape and (arr == ref_paths[q]).all()
+    for fused in (True, False):
+        paths = rrt_connect_batch(g["starts"], g["goals"], dist, ext, col, u, tg, fused=fused)
+        for q in range(B):
+            assert (paths[q] is None) == (ref_paths[q] is None)
+            if paths[q] is not None:
+                arr = np.array(paths[q])
+                assert arr.shape == ref_paths[q].shape and (arr == ref_paths[q]).all()
+
+
+def test_rrt_connect_fused_equals_lockstep_on_a_large_batch(mp):
+    """512 7-DoF queries (some with colliding endpoints): the one-launch kernel and the composition of the
+    stand-alone kernels must build identical trees and report identical results."""
+    import random
+    from motion_planners_b200 import workloads
+    from motion_planners_b200.rrt_connect import rrt_connect_batch
+    world = workloads.c3_world()
+    dist, ext, col = _tree_primitives(mp, world)
+    rs = np.random.RandomState(8)
+    B, iters, D = 512, 40, 7
+    starts, goals = rs.uniform(size=(B, D)), rs.uniform(size=(B, D))
+    u = rs.uniform(size=(B, iters))
+    tg = rs.uniform(size=(B, iters, D))
+    _, a = rrt_connect_batch(starts, goals, dist, ext, col, u, tg, return_state=True, retrace=False, fused=True)
+    _, b = rrt_connect_batch(starts, goals, dist, ext, col, u, tg, return_state=True, retrace=False, fused=False)
+    assert torch.equal(a.solved, b.solved)
+    assert 0 < int(a.solved.sum()) < B
+    sel = a.solved
+    assert torch.equal(a.last_a[sel], b.last_a[sel]) and torch.equal(a.last_b[sel], b.last_b[sel])
+    assert torch.equal(a.swapped[sel], b.swapped[sel])
+    # trees of solved queries are identical node for node (unsolved ones too, up to the iteration budget)
+    assert torch.equal(a.sizes, b.sizes)
+    for q in torch.nonzero(sel).flatten()[:40].tolist():
+        for t in (2 * q, 2 * q + 1):
+            n = int(a.sizes[t])
+            assert torch.equal(a.nodes[t, :n], b.nodes[t, :n]) and torch.equal(a.parents[t, :n], b.parents[t, :n])
 
 
 @pytest.mark.parametrize("name", ["problem1", "mixed3d"])
