@@ -222,6 +222,8 @@ int mpb_scan_nearest_radius(const double *nodes, int64_t n, int dim, const doubl
  * blocks * threads.  sink: dev, at least blocks*threads elements. */
 int mpb_peak_fma_f32(int blocks, int threads, int iters, float *sink, void *stream);
 int mpb_peak_fma_f64(int blocks, int threads, int iters, double *sink, void *stream);
+/* The same with packed fp32 pairs (fma.rn.f32x2, SASS FFMA2): flops = 2 * 2 * 8 * iters * blocks * threads. */
+int mpb_peak_fma_f32x2(int blocks, int threads, int iters, float *sink, void *stream);
 
 #ifdef __cplusplus
 }

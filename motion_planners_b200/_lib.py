@@ -51,6 +51,7 @@ SIGNATURES = {
                                         c_vp]),
     "mpb_peak_fma_f32": (c_int, [c_int, c_int, c_int, c_vp, c_vp]),
     "mpb_peak_fma_f64": (c_int, [c_int, c_int, c_int, c_vp, c_vp]),
+    "mpb_peak_fma_f32x2": (c_int, [c_int, c_int, c_int, c_vp, c_vp]),
 }
 
 

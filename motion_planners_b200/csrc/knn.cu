@@ -290,15 +290,22 @@ __global__ void __launch_bounds__(kWarps * 32, 2)
 
     // ---- this warp's Q queries, as -2*fl32(e_q - c), uniform across the lanes
     const int64_t q0 = ((int64_t)blockIdx.x * kWarps + warp) * Q;
-    float qm[Q][D];
+    // kept as packed pairs (queries 2p and 2p+1): one FFMA2 scores a candidate for both
+    static_assert(Q % 2 == 0, "queries are processed in pairs");
+    f32x2_t qmp[Q / 2][D];
 #pragma unroll
-    for (int qi = 0; qi < Q; ++qi) {
-        int64_t q = q0 + qi;
-        if (q >= M) q = M - 1;
+    for (int p = 0; p < Q / 2; ++p) {
 #pragma unroll
         for (int d = 0; d < D; ++d) {
-            const double e = d_mul(wt.w[d], qs[q * D + d]);
-            qm[qi][d] = -2.f * (float)d_sub(e, h->center[d]);
+            float v[2];
+#pragma unroll
+            for (int hq = 0; hq < 2; ++hq) {
+                int64_t q = q0 + 2 * p + hq;
+                if (q >= M) q = M - 1;
+                const double e = d_mul(wt.w[d], qs[q * D + d]);
+                v[hq] = -2.f * (float)d_sub(e, h->center[d]);
+            }
+            qmp[p][d] = pack_f32x2(v[0], v[1]);
         }
     }
     float thr[Q], lk[NREG];
@@ -313,6 +320,55 @@ __global__ void __launch_bounds__(kWarps * 32, 2)
 
     const uint32_t smem0 = smem_u32(stage_base) + (uint32_t)lane * 16u;
 
+    // Insertion rounds for one group of 32 candidates (lane <-> candidate cbase + lane) whose keys are `key32`.
+    // Every round gives each query at most one of its passing candidates; the rounds are branch-free so that
+    // the shuffle chains of all list registers overlap.  A candidate that no longer beats its list (or "no
+    // candidate": key = +inf) lands at position SEG, i.e. nowhere.
+    auto insert_group = [&](const float (&key32)[Q], int cbase) {
+        unsigned m[Q];
+#pragma unroll
+        for (int qi = 0; qi < Q; ++qi) m[qi] = __ballot_sync(FULL_MASK, key32[qi] < thr[qi]);
+        bool more = true;
+        while (more) {
+            more = false;
+#pragma unroll
+            for (int r = 0; r < NREG; ++r) {
+                float key = INFINITY;
+                int cidx = -1;
+#pragma unroll
+                for (int hs = 0; hs < PER; ++hs) {
+                    const int qi = r * PER + hs;
+                    const int src = (__ffs(m[qi]) - 1) & 31;
+                    const float kq = __shfl_sync(FULL_MASK, key32[qi], src);
+                    if (seg == hs) {
+                        key = m[qi] ? kq : INFINITY;
+                        cidx = cbase + src;
+                    }
+                    m[qi] &= m[qi] - 1;
+                    more = more || (m[qi] != 0);
+                }
+                const unsigned le = __ballot_sync(FULL_MASK, lk[r] <= key);
+                const int pos = __popc((le >> ((SEG * seg) & 31)) & SEGMASK);
+                const float upk = __shfl_up_sync(FULL_MASK, lk[r], 1, SEG);
+                const int upi = __shfl_up_sync(FULL_MASK, li[r], 1, SEG);
+                if (sl > pos) {
+                    lk[r] = upk;
+                    li[r] = upi;
+                } else if (sl == pos) {
+                    lk[r] = key;
+                    li[r] = cidx;
+                }
+#pragma unroll
+                for (int hs = 0; hs < PER; ++hs)
+                    thr[r * PER + hs] = __shfl_sync(FULL_MASK, lk[r], SEG * hs + SEG - 1);
+            }
+        }
+    };
+    float prev[Q];              // keys of the group scored one step ago, not yet compared
+    int prev_base = 0;
+#pragma unroll
+    for (int qi = 0; qi < Q; ++qi) prev[qi] = INFINITY;
+
     // ---- stream every tile through the ring
     for (int t = 0; t < n_tiles; ++t) {
         const int s = t % kStages;
@@ -321,6 +377,11 @@ __global__ void __launch_bounds__(kWarps * 32, 2)
 
         const uint32_t tbase = smem0 + (uint32_t)s * (uint32_t)SM::STAGE_BYTES;
         const int cbase0 = t * TILE;
+        // Software pipeline: while the FFMA2 chains of this group of 32 candidates run, the keys of the
+        // PREVIOUS group (complete long ago) are compared with the thresholds and, if any of them passes,
+        // inserted -- so the compare/vote/branch tail never waits for the arithmetic it follows.  The keys in
+        // flight cross tile boundaries in registers (`prev`, `prev_base`); the last group is drained after the
+        // tile loop.
         float4 nxt[P];
 #pragma unroll
         for (int p = 0; p < P; ++p) nxt[p] = lds128(tbase + (uint32_t)(p * TILE) * 16u);
@@ -338,61 +399,21 @@ __global__ void __launch_bounds__(kWarps * 32, 2)
 #pragma unroll
                 for (int p = 0; p < P; ++p) nxt[p] = lds128(tbase + (uint32_t)(p * TILE + c0 + 32) * 16u);
             }
-            float acc[Q];
             bool pass = false;
 #pragma unroll
-            for (int qi = 0; qi < Q; ++qi) {
-                float a = xv[D];
+            for (int qi = 0; qi < Q; ++qi) pass = pass || (prev[qi] < thr[qi]);
+            float acc[Q];
 #pragma unroll
-                for (int d = 0; d < D; ++d) a = __fmaf_rn(qm[qi][d], xv[d], a);
-                acc[qi] = a;
-                pass = pass || (a < thr[qi]);
+            for (int p = 0; p < Q / 2; ++p) {
+                f32x2_t a = pack_f32x2(xv[D], xv[D]);
+#pragma unroll
+                for (int d = 0; d < D; ++d) a = fma_f32x2(qmp[p][d], pack_f32x2(xv[d], xv[d]), a);
+                unpack_f32x2(a, acc[2 * p], acc[2 * p + 1]);
             }
-            if (__any_sync(FULL_MASK, pass)) {
-                // Insertion rounds.  Every round gives each query at most one of its passing candidates;
-                // the rounds are branch-free so that the shuffle chains of all list registers overlap.
-                // A candidate that no longer beats its list (or "no candidate": key = +inf) lands at
-                // position SEG, i.e. nowhere.
-                const int cbase = cbase0 + c0;
-                unsigned m[Q];
+            if (__any_sync(FULL_MASK, pass)) insert_group(prev, prev_base);
 #pragma unroll
-                for (int qi = 0; qi < Q; ++qi) m[qi] = __ballot_sync(FULL_MASK, acc[qi] < thr[qi]);
-                bool more = true;
-                while (more) {
-                    more = false;
-#pragma unroll
-                    for (int r = 0; r < NREG; ++r) {
-                        float key = INFINITY;
-                        int cidx = -1;
-#pragma unroll
-                        for (int hs = 0; hs < PER; ++hs) {
-                            const int qi = r * PER + hs;
-                            const int src = (__ffs(m[qi]) - 1) & 31;
-                            const float kq = __shfl_sync(FULL_MASK, acc[qi], src);
-                            if (seg == hs) {
-                                key = m[qi] ? kq : INFINITY;
-                                cidx = cbase + src;
-                            }
-                            m[qi] &= m[qi] - 1;
-                            more = more || (m[qi] != 0);
-                        }
-                        const unsigned le = __ballot_sync(FULL_MASK, lk[r] <= key);
-                        const int pos = __popc((le >> ((SEG * seg) & 31)) & SEGMASK);
-                        const float upk = __shfl_up_sync(FULL_MASK, lk[r], 1, SEG);
-                        const int upi = __shfl_up_sync(FULL_MASK, li[r], 1, SEG);
-                        if (sl > pos) {
-                            lk[r] = upk;
-                            li[r] = upi;
-                        } else if (sl == pos) {
-                            lk[r] = key;
-                            li[r] = cidx;
-                        }
-#pragma unroll
-                        for (int hs = 0; hs < PER; ++hs)
-                            thr[r * PER + hs] = __shfl_sync(FULL_MASK, lk[r], SEG * hs + SEG - 1);
-                    }
-                }
-            }
+            for (int qi = 0; qi < Q; ++qi) prev[qi] = acc[qi];
+            prev_base = cbase0 + c0;
         }
         // The last warp to release a slot requests its next tenant: nobody waits for anybody.
         __syncwarp();
@@ -406,6 +427,13 @@ __global__ void __launch_bounds__(kWarps * 32, 2)
             }
         }
         __syncwarp();
+    }
+
+    {   // drain the software pipeline: the last group scored has not been compared yet
+        bool pass = false;
+#pragma unroll
+        for (int qi = 0; qi < Q; ++qi) pass = pass || (prev[qi] < thr[qi]);
+        if (__any_sync(FULL_MASK, pass)) insert_group(prev, prev_base);
     }
 
     // ---- exact re-rank of the survivors and the certificate; the PER lists of a register are handled
@@ -425,9 +453,14 @@ __global__ void __launch_bounds__(kWarps * 32, 2)
 #pragma unroll
         for (int d = 0; d < D; ++d) {
             eq[d] = d_mul(wt.w[d], qs[qc * D + d]);
-            float qmd = qm[r * PER][d];
+            float qmd = 0.f;
 #pragma unroll
-            for (int hs = 1; hs < PER; ++hs) qmd = (seg == hs) ? qm[r * PER + hs][d] : qmd;
+            for (int hs = 0; hs < PER; ++hs) {
+                float lo, hi;
+                unpack_f32x2(qmp[(r * PER + hs) / 2][d], lo, hi);
+                const float v = ((r * PER + hs) & 1) ? hi : lo;
+                qmd = (hs == 0 || seg == hs) ? v : qmd;
+            }
             const double qh = -0.5 * (double)qmd;
             nq2 += qh * qh;
         }

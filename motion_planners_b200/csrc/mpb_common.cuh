@@ -133,6 +133,25 @@ __device__ __forceinline__ double metric_dist(const double (&a)[D], const double
 }
 
 
+// ---- packed fp32 pairs (Blackwell FFMA2: one issue slot, two fused multiply-adds) ----------------
+typedef unsigned long long f32x2_t;
+__device__ __forceinline__ f32x2_t pack_f32x2(float lo, float hi)
+{
+    f32x2_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack_f32x2(f32x2_t v, float &lo, float &hi)
+{
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2_t fma_f32x2(f32x2_t a, f32x2_t b, f32x2_t c)
+{
+    f32x2_t d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+
 // ---- mbarrier + 1-D bulk async copy (TMA engine, no tensor map) ---------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void *p)
 {

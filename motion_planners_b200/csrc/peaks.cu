@@ -31,6 +31,29 @@ __global__ void __launch_bounds__(1024) peak_fma_kernel(int iters, T *sink)
     sink[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
 }
 
+// The same with packed pairs: 8 independent chains of FFMA2, 2 fused multiply-adds per instruction and lane.
+__global__ void __launch_bounds__(1024) peak_fma2_kernel(int iters, float *sink)
+{
+    const float bf = 1.0000001f + (float)threadIdx.x * 1e-9f;
+    const f32x2_t b = pack_f32x2(bf, bf), c = pack_f32x2(1e-7f, 1e-7f);
+    f32x2_t a[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] = pack_f32x2((float)threadIdx.x + j, (float)threadIdx.x - j);
+#pragma unroll 8
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) a[j] = fma_f32x2(a[j], b, c);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        float lo, hi;
+        unpack_f32x2(a[j], lo, hi);
+        s += lo + hi;
+    }
+    sink[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
 template <typename T>
 static int run_peak(const char *who, int blocks, int threads, int iters, T *sink, void *stream)
 {
@@ -48,4 +71,12 @@ MPB_API int mpb_peak_fma_f32(int blocks, int threads, int iters, float *sink, vo
 MPB_API int mpb_peak_fma_f64(int blocks, int threads, int iters, double *sink, void *stream)
 {
     return run_peak<double>("mpb_peak_fma_f64", blocks, threads, iters, sink, stream);
+}
+
+MPB_API int mpb_peak_fma_f32x2(int blocks, int threads, int iters, float *sink, void *stream)
+{
+    MPB_REQUIRE(blocks > 0 && threads > 0 && threads <= 1024 && iters > 0 && sink, "mpb_peak_fma_f32x2: bad argument");
+    peak_fma2_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(iters, sink);
+    MPB_LAUNCH_CHECK();
+    return MPB_OK;
 }

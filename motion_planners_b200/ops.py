@@ -291,12 +291,15 @@ def scan_nearest_radius(nodes, q, radius, weights=None, metric=METRIC_SAMPLERS):
     return nearest, dist, count, lst
 
 
-def peak_fma(dtype=torch.float32, iters=4096, repeats=5):
-    """Measured FMA issue peak of this GPU in FLOP/s (2 flops per FMA) -- bench.py's roofline denominator."""
+def peak_fma(dtype=torch.float32, iters=4096, repeats=5, packed=False):
+    """Measured FMA issue peak of this GPU in FLOP/s (2 flops per FMA) -- bench.py's roofline denominator.
+    packed=True measures the fp32 pipe through FFMA2 (two fused multiply-adds per instruction)."""
     props = torch.cuda.get_device_properties(torch.cuda.current_device())
     blocks, threads = props.multi_processor_count * 8, 256
     sink = torch.empty(blocks * threads, dtype=dtype, device="cuda")
     fn = _lib.lib().mpb_peak_fma_f32 if dtype == torch.float32 else _lib.lib().mpb_peak_fma_f64
+    if packed:
+        fn = _lib.lib().mpb_peak_fma_f32x2
     best = 0.0
     for _ in range(repeats + 1):
         e0 = torch.cuda.Event(enable_timing=True)
@@ -306,5 +309,5 @@ def peak_fma(dtype=torch.float32, iters=4096, repeats=5):
         e1.record()
         e1.synchronize()
         ms = e0.elapsed_time(e1)
-        best = max(best, 2.0 * 8 * iters * blocks * threads / (ms * 1e-3))
+        best = max(best, (2.0 if packed else 1.0) * 2.0 * 8 * iters * blocks * threads / (ms * 1e-3))
     return best
