@@ -84,6 +84,14 @@ int mpb_points_check(const mpb_world *world, const double *q, int64_t n, uint8_t
 int mpb_edges_check(const mpb_world *world, const double *samples, int64_t n_samples,
                     const int64_t *src, const int64_t *dst, int64_t n_edges, double step, int mode,
                     int skip_last, int32_t *out_hit, int32_t *out_n, void *stream);
+/* edges as the rows of a neighbour matrix (the output of the kNN entry points, consumed in place): entry
+ * (r, j) is the edge from sample row_offset + r to sample nbr[r, j]; nbr dev [n_rows, row_len] i64, outputs
+ * dev [n_rows, row_len] i32.  Same verdicts as mpb_edges_check on those pairs (negative = no neighbour:
+ * out_hit = -1, out_n = 0), but the obstacle culling is done once per row instead of once per edge.
+ * This is lazy_prm.py:211-215 check_roadmap over the edges lazy_prm.py:148-160 add_samples creates. */
+int mpb_edges_check_knn(const mpb_world *world, const double *samples, int64_t n_samples,
+                        const int64_t *nbr, int64_t n_rows, int row_len, int64_t row_offset, double step,
+                        int mode, int skip_last, int32_t *out_hit, int32_t *out_n, void *stream);
 /* edges as explicit endpoint arrays: q1, q2 dev [E, dim] f64 */
 int mpb_edges_check_pairs(const mpb_world *world, const double *q1, const double *q2,
                           int64_t n_edges, double step, int mode, int skip_last, int32_t *out_hit,

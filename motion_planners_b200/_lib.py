@@ -29,6 +29,8 @@ SIGNATURES = {
     "mpb_world_destroy": (c_int, [c_vp]),
     "mpb_points_check": (c_int, [c_vp, c_vp, c_i64, c_vp, c_vp]),
     "mpb_edges_check": (c_int, [c_vp, c_vp, c_i64, c_vp, c_vp, c_i64, c_dbl, c_int, c_int, c_vp, c_vp, c_vp]),
+    "mpb_edges_check_knn": (c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, c_int, c_i64, c_dbl, c_int, c_int, c_vp, c_vp,
+                                    c_vp]),
     "mpb_edges_check_pairs": (c_int, [c_vp, c_vp, c_vp, c_i64, c_dbl, c_int, c_int, c_vp, c_vp, c_vp]),
     "mpb_edges_count": (c_int, [c_vp, c_vp, c_i64, c_int, c_dbl, c_vp, c_vp]),
     "mpb_edges_waypoints": (c_int, [c_vp, c_vp, c_i64, c_int, c_dbl, c_vp, c_vp, c_vp]),

@@ -9,11 +9,11 @@
 // fp32 filter: samples are packed once into fp32 tiles (centred on the bounding-box
 // midpoint, plus the squared norm), streamed through shared memory with 1-D bulk async
 // copies (TMA engine) in a multi-stage mbarrier ring, and each warp scores 32 candidates per
-// step for Q register-resident queries with the expansion key = |x|^2 - 2 q.x (D FFMA per
-// pair).  Each query keeps its 32 best candidates in a warp-distributed sorted list (one
-// entry per lane, shuffle insert).  At the end the exact fp64 keys of those 32 are ranked
-// and a rounding-error bound certifies that nothing outside the list can enter the top k;
-// uncertified queries are queued for the exact kernel.
+// step for Q register-resident queries with the expansion key = |x|^2 - 2 q.x: one packed
+// FFMA2 per coordinate serves two queries.  Each query keeps its 16 (k <= 12) or 32 best
+// candidates in a warp-distributed sorted list (shuffle insert).  At the end the exact fp64
+// keys of the survivors are ranked and a rounding-error bound certifies that nothing outside
+// the list can enter the top k; uncertified queries are queued for the exact kernel.
 #include <math.h>
 
 #include <mutex>

@@ -349,6 +349,169 @@ MPB_API int mpb_edges_check_pairs(const mpb_world *world, const double *q1, cons
 }
 
 // ------------------------------------------------------------------------------------------
+// the same verdicts for a neighbour matrix: one thread per ROW (a sample and its k+1 neighbours)
+// ------------------------------------------------------------------------------------------
+// All edges of a row leave the same sample and are short, so the obstacles are culled ONCE against the
+// bounding box of the sample and all its neighbours; each edge then replays its waypoints against the
+// few survivors.  Entry (r, j) equals mpb_edges_check on the pair (row_offset + r, nbr[r, j]).
+template <int D>
+__global__ void __launch_bounds__(128)
+    edges_check_rows_kernel(WorldDev w, const double *__restrict__ X, const int64_t *__restrict__ nbr, int64_t M,
+                            int kk, int64_t row_offset, double step, int mode, int skip_last,
+                            int32_t *__restrict__ out_hit, int32_t *__restrict__ out_n)
+{
+    extern __shared__ __align__(16) double sm[];
+    const WorldSmem s = stage_world(w, sm);
+    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < M; r += (int64_t)gridDim.x * blockDim.x) {
+        double a[D];
+        const double *pa = X + (row_offset + r) * D;
+#pragma unroll
+        for (int d = 0; d < D; ++d) a[d] = pa[d];
+        // bounding box of the row, inflated like the per-edge boxes of edges_check_kernel
+        double lo[D], hi[D];
+#pragma unroll
+        for (int d = 0; d < D; ++d) lo[d] = hi[d] = a[d];
+        bool cull = true;
+        const int64_t *row = nbr + r * kk;
+        int32_t *hit_row = out_hit + r * kk;
+        for (int j = 0; j < kk; ++j) {
+            const int64_t v = row[j];
+            hit_row[j] = -1;
+            if (v < 0) {
+                if (out_n) out_n[r * kk + j] = 0;
+                continue;
+            }
+            double b[D];
+            const double *pb = X + v * D;
+#pragma unroll
+            for (int d = 0; d < D; ++d) {
+                b[d] = pb[d];
+                lo[d] = fmin(lo[d], b[d]);
+                hi[d] = fmax(hi[d], b[d]);
+            }
+            const int n = waypoint_count<D>(a, b, step);
+            if (out_n) out_n[r * kk + j] = n;
+            cull = cull && (n <= 1000000);
+        }
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            const double m = 1e-9 * (1.0 + fmax(fabs(lo[d]), fabs(hi[d])));
+            lo[d] -= m;
+            hi[d] += m;
+        }
+        // one pass per obstacle group: 0 = environment, then boxes, then spheres, 64 at a time
+        bool inside = cull;
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            const double2 ev = s.env[d];
+            inside = inside && (ev.x <= lo[d]) && (hi[d] <= ev.y);
+        }
+        const int n_groups = 1 + (w.n_box + 63) / 64 + (w.n_sph + 63) / 64;
+        for (int g = 0; g < n_groups; ++g) {
+            int kind, base = 0;
+            unsigned long long mask = 0ull;
+            if (g == 0) {
+                kind = TEST_ENV;
+                if (inside) continue;
+            } else if (g <= (w.n_box + 63) / 64) {
+                kind = TEST_BOX;
+                base = (g - 1) * 64;
+                const int cnt = min(64, w.n_box - base);
+                for (int j = 0; j < cnt; ++j) {
+                    const double2 *bb = s.box + (base + j) * D;
+                    bool ov = true;
+#pragma unroll
+                    for (int d = 0; d < D; ++d) {
+                        const double2 bv = bb[d];
+                        ov = ov && (bv.x <= hi[d]) && (lo[d] <= bv.y);
+                    }
+                    if (ov || !cull) mask |= 1ull << j;
+                }
+                if (!mask) continue;
+            } else {
+                kind = TEST_SPH;
+                base = (g - 1 - (w.n_box + 63) / 64) * 64;
+                const int cnt = min(64, w.n_sph - base);
+                for (int j = 0; j < cnt; ++j) {
+                    const double *c = s.sph_c + (base + j) * D;
+                    const double rr = s.sph_rb[base + j] * (1.0 + 1e-9) + 1e-12;
+                    bool ov = true;
+#pragma unroll
+                    for (int d = 0; d < D; ++d) ov = ov && (c[d] - rr <= hi[d]) && (lo[d] <= c[d] + rr);
+                    if (ov || !cull) mask |= 1ull << j;
+                }
+                if (!mask) continue;
+            }
+            for (int j = 0; j < kk; ++j) {
+                const int64_t v = row[j];
+                if (v < 0) continue;
+                int best = hit_row[j];
+                if (mode == MPB_EDGE_ANY && best >= 0) continue;
+                double b[D];
+                const double *pb = X + v * D;
+#pragma unroll
+                for (int d = 0; d < D; ++d) b[d] = pb[d];
+                const int n = waypoint_count<D>(a, b, step);
+                const int lim = n - (skip_last ? 1 : 0);
+                if (kind == TEST_ENV)
+                    sweep<D, TEST_ENV>(s, a, b, n, lim, mode, 0, 0ull, best);
+                else if (kind == TEST_BOX)
+                    sweep<D, TEST_BOX>(s, a, b, n, lim, mode, base, mask, best);
+                else
+                    sweep<D, TEST_SPH>(s, a, b, n, lim, mode, base, mask, best);
+                hit_row[j] = best;
+            }
+        }
+    }
+}
+
+template <int D>
+static int launch_edges_rows(const mpb_world *world, const double *X, const int64_t *nbr, int64_t M, int kk,
+                             int64_t row_offset, double step, int mode, int skip_last, int32_t *out_hit,
+                             int32_t *out_n, cudaStream_t st)
+{
+    const size_t smem = world_smem_bytes(world->dev) + 16;
+    const int threads = 128;
+    int64_t blocks = (M + threads - 1) / threads;
+    int sms = 148;
+    {
+        int dev = 0;
+        if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    if (blocks > (int64_t)sms * 16) blocks = (int64_t)sms * 16;
+    if (smem > 48 * 1024)
+        MPB_CUDA_CHECK(cudaFuncSetAttribute(edges_check_rows_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)smem));
+    edges_check_rows_kernel<D><<<(unsigned)blocks, threads, smem, st>>>(world->dev, X, nbr, M, kk, row_offset, step,
+                                                                        mode, skip_last, out_hit, out_n);
+    MPB_LAUNCH_CHECK();
+    return MPB_OK;
+}
+
+MPB_API int mpb_edges_check_knn(const mpb_world *world, const double *samples, int64_t n_samples, const int64_t *nbr,
+                                int64_t n_rows, int row_len, int64_t row_offset, double step, int mode, int skip_last,
+                                int32_t *out_hit, int32_t *out_n, void *stream)
+{
+    MPB_REQUIRE(world != nullptr, "mpb_edges_check_knn: world is NULL");
+    MPB_REQUIRE(n_rows >= 0 && row_len >= 1 && row_offset >= 0 && row_offset + n_rows <= n_samples,
+                "mpb_edges_check_knn: rows [%lld, %lld) outside the %lld samples", (long long)row_offset,
+                (long long)(row_offset + n_rows), (long long)n_samples);
+    MPB_REQUIRE(mode == MPB_EDGE_ANY || mode == MPB_EDGE_FIRST || mode == MPB_EDGE_LAST,
+                "mpb_edges_check_knn: bad mode %d", mode);
+    MPB_REQUIRE(step > 0., "mpb_edges_check_knn: step must be positive");
+    if (n_rows == 0) return MPB_OK;
+    MPB_REQUIRE(samples && nbr && out_hit, "mpb_edges_check_knn: NULL buffer");
+    MPB_REQUIRE(world_smem_bytes(world->dev) + 16 <= kMaxWorldSmem,
+                "mpb_edges_check_knn: obstacle set (%zu bytes) exceeds the %zu-byte shared-memory budget",
+                world_smem_bytes(world->dev), kMaxWorldSmem);
+    cudaStream_t st = (cudaStream_t)stream;
+#define CALL(DD) launch_edges_rows<DD>(world, samples, nbr, n_rows, row_len, row_offset, step, mode, skip_last, out_hit, out_n, st)
+    MPB_DISPATCH_DIM(world->dev.dim, CALL)
+#undef CALL
+    return MPB_EINVAL;
+}
+
+// ------------------------------------------------------------------------------------------
 // extend_fn output (the waypoints themselves)
 // ------------------------------------------------------------------------------------------
 template <int D>

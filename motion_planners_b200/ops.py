@@ -103,6 +103,21 @@ class ObstacleSet(object):
         _lib.check(rc, "mpb_edges_check")
         return hit, cnt
 
+    # -- the same for the rows of a neighbour matrix (culling once per row)
+    def edges_check_knn(self, samples, nbr, row_offset=0, mode=EDGE_ANY, skip_last=False, step=STEP_SIZE,
+                        want_counts=False):
+        samples = _f64(samples, "samples", self.dim)
+        if not (nbr.is_cuda and nbr.dtype == torch.int64 and nbr.dim() == 2 and nbr.is_contiguous()):
+            raise TypeError("nbr must be a contiguous 2-D int64 CUDA tensor")
+        M, kk = nbr.shape
+        hit = torch.empty((M, kk), dtype=torch.int32, device=samples.device)
+        cnt = torch.empty((M, kk), dtype=torch.int32, device=samples.device) if want_counts else None
+        rc = _lib.lib().mpb_edges_check_knn(self._h, _ptr(samples), samples.shape[0], _ptr(nbr), M, kk,
+                                            int(row_offset), float(step), int(mode), int(bool(skip_last)),
+                                            _ptr(hit), _ptr(cnt), _stream())
+        _lib.check(rc, "mpb_edges_check_knn")
+        return hit, cnt
+
     # -- the same for explicit endpoint arrays
     def edges_check_pairs(self, q1, q2, mode=EDGE_ANY, skip_last=False, step=STEP_SIZE, want_counts=True):
         q1 = _f64(q1, "q1", self.dim)

@@ -74,6 +74,8 @@ def gather_rows(local, group=None):
 
 
 class DeviceRoadmap(object):
+    ROWS_KERNEL_MIN = 300000     # rows from which the per-row edge kernel beats the per-edge one
+
     def __init__(self, world, k=10, weights=None, max_distance=math.inf, step=STEP_SIZE, group=None):
         self.world = world
         self.k = int(k)
@@ -138,16 +140,21 @@ class DeviceRoadmap(object):
             self.vertex_hit = self.obstacles.points_check(queries)
             launches += 1
             mark("vertices")
-            if self._src is None or self._src.numel() != n_local * self.kk or self._src_offset != offset:
-                self._src = (torch.arange(n_local, device=samples.device, dtype=torch.int64) + offset) \
-                    .repeat_interleave(self.kk)
-                self._src_offset = offset
-            dst = self.nbr_idx.view(-1)
             # self-edges (one waypoint) and missing neighbours (-1, skipped) ride along, so the neighbour
             # matrix is consumed in place with no compaction pass
-            hit, _ = self.obstacles.edges_check(samples, self._src, dst, mode=ops.EDGE_ANY, step=self.step,
-                                                want_counts=False)
-            self.edge_hit = hit.view(n_local, self.kk)
+            if n_local >= self.ROWS_KERNEL_MIN:
+                # one thread per row: obstacles culled once per sample (1.7x faster at 1M rows, measured)
+                self.edge_hit, _ = self.obstacles.edges_check_knn(samples, self.nbr_idx, row_offset=offset,
+                                                                  mode=ops.EDGE_ANY, step=self.step)
+            else:
+                # one thread per edge: 11x more threads, which is what fills the GPU at 100k rows
+                if self._src is None or self._src.numel() != n_local * self.kk or self._src_offset != offset:
+                    self._src = (torch.arange(n_local, device=samples.device, dtype=torch.int64) + offset) \
+                        .repeat_interleave(self.kk)
+                    self._src_offset = offset
+                hit, _ = self.obstacles.edges_check(samples, self._src, self.nbr_idx.view(-1), mode=ops.EDGE_ANY,
+                                                    step=self.step, want_counts=False)
+                self.edge_hit = hit.view(n_local, self.kk)
             launches += 1
             mark("edges")
         self.launches = launches

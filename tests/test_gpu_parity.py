@@ -238,6 +238,32 @@ def test_edges_many_obstacles_and_long_edges(ops):
         assert (host(c) == n).all() and (host(f) == first).all() and (host(l) == last).all()
 
 
+@pytest.mark.parametrize("name", ["problem1", "boxes6d", "mixed3d"])
+def test_edges_knn_rows_equal_indexed_edges(ops, golden, name):
+    """The per-row form (culling shared by a sample's edges) gives the verdicts of the per-edge form."""
+    g = golden("edges_" + name)
+    obs, w = gpu_world(ops, g)
+    rs = np.random.RandomState(12)
+    N, kk = 6000, 7
+    X = rs.uniform(-0.01, 1.01, size=(N, w.dim))
+    xs = dev(X)
+    idx, _ = ops.knn(xs, xs, kk)
+    idx[::13, 3] = -1                                            # missing neighbours
+    idx[5::17, 5] = torch.randint(0, N, (idx[5::17, 5].numel(),), device="cuda")   # a few long edges
+    off, rows = 1000, 4000
+    nbr = idx[off:off + rows].contiguous()
+    src = (torch.arange(rows, device="cuda") + off).repeat_interleave(kk)
+    for mode in (ops.EDGE_FIRST, ops.EDGE_LAST):
+        for skip in (False, True):
+            ref, ref_n = obs.edges_check(xs, src, nbr.view(-1), mode=mode, skip_last=skip)
+            hit, cnt = obs.edges_check_knn(xs, nbr, row_offset=off, mode=mode, skip_last=skip, want_counts=True)
+            assert torch.equal(hit.view(-1), ref) and torch.equal(cnt.view(-1), ref_n)
+    ref, _ = obs.edges_check(xs, src, nbr.view(-1), mode=ops.EDGE_ANY)
+    hit, _ = obs.edges_check_knn(xs, nbr, row_offset=off, mode=ops.EDGE_ANY)
+    assert torch.equal(hit.view(-1) >= 0, ref >= 0)
+    assert 0 < int((ref >= 0).sum()) < ref.numel()
+
+
 def test_edges_empty(ops):
     from motion_planners_b200 import workloads
     obs, _ = gpu_world(ops, workloads.c2_world())
