@@ -268,7 +268,8 @@ def gen_prm():
     from motion_planners.tkinter.samplers import get_collision_fn, get_distance_fn, get_extend_fn, get_sample_fn
     ext = get_extend_fn()
     for name, num, deg, seed, cfree_samples in [("problem1", 250, 10, 11, True), ("problem1", 120, 4, 12, False),
-                                                ("boxes6d", 120, 6, 13, True)]:
+                                                ("boxes6d", 120, 6, 13, True),
+                                                ("problem1", 2000, 10, 0, True)]:     # configs[0] at full size
         world = WORLDS[name]()
         env, obs = _ref_world(world)
         col = get_collision_fn(env, obs)

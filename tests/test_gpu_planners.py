@@ -119,9 +119,10 @@ def test_roadmap_scalar_check_methods(mp, golden):
     assert len(a.get_path(v2, v1)) == len(path) and (a.get_path(v2, v1)[0] == path[-1]).all()
 
 
-@pytest.mark.parametrize("name", ["prm_problem1_s11", "prm_problem1_s12", "prm_boxes6d_s13"])
+@pytest.mark.parametrize("name", ["prm_problem1_s11", "prm_problem1_s12", "prm_boxes6d_s13", "prm_problem1_s0"])
 def test_prm_matches_reference_run(mp, golden, name):
-    """prm() = DegreePRM.grow + A* (prm.py:237-282): same edges in the same order, same path."""
+    """prm() = DegreePRM.grow + A* (prm.py:237-282): same edges in the same order, same path.
+    prm_problem1_s0 is BASELINE.json's configs[0] at full size (2-D demo fixture, 2000 samples, degree 10)."""
     g = golden(name)
     world = _world(mp, g)
     samples = [tuple(r) for r in g["samples"]]
