@@ -215,6 +215,36 @@ def measure_rrt_batch(world_size, rank, dist, total_queries=4096, iters=100):
             "kernel_launches": int(state.launches)}
 
 
+def measure_rrt_star(iters=1500):
+    """configs[4] as a rate: RRT* in the 3-D world (32 boxes + 8 spheres, radius 0.1); every rank runs its
+    own replica (the tree is sequential), so this is a per-GPU figure."""
+    import random as pyrandom
+    from motion_planners_b200 import primitives, workloads
+    from motion_planners_b200.rrt_star import rrt_star
+    world = workloads.c5_world()
+    env, obstacles = world.shapes()
+    col = primitives.GpuCollisionFn(world)
+    ext = primitives.get_extend_fn()
+    dfn = primitives.get_distance_fn(np.ones(world.dim))
+    pyrandom.seed(0)
+    np.random.seed(0)
+    cfree = primitives.get_sample_fn(env, obstacles=obstacles)
+    while True:
+        s, g = cfree(), cfree()
+        if np.linalg.norm(s - g) > 0.8:
+            break
+    sample_fn = primitives.get_sample_fn(env, obstacles=[])
+    pyrandom.seed(1)
+    np.random.seed(1)
+    t0 = time.perf_counter()
+    path = rrt_star(s, g, dfn, sample_fn, ext, col, radius=0.1, max_iterations=iters)
+    sec = time.perf_counter() - t0
+    return {"description": "configs[4]: rrt_star, 3-D, 32 boxes + 8 spheres, radius 0.1, %d iterations "
+                           "(one tree per GPU: replicas only)" % iters,
+            "seconds": sec, "iterations_per_s": iters / sec, "solved": path is not None,
+            "kernel_launches": int(getattr(rrt_star, "last_launches", 0))}
+
+
 # ------------------------------------------------------------------------------------------- main
 def main():
     ap = argparse.ArgumentParser()
@@ -434,6 +464,8 @@ def main():
 
     if not args.no_extra:
         line["extra_c3_rrt_connect_batch"] = measure_rrt_batch(world_size, rank, dist if world_size > 1 else None)
+        if rank == 0:
+            line["extra_c5_rrt_star"] = measure_rrt_star()
 
     if rank == 0:
         print(json.dumps(line))

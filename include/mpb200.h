@@ -224,6 +224,23 @@ int mpb_scan_nearest_radius(const double *nodes, int64_t n, int dim, const doubl
                             const double *weights, int metric, double radius, int32_t *out_nearest,
                             double *out_dist, int32_t *out_count, int32_t *out_list, void *stream);
 
+/* ---- shortest paths over a device-resident roadmap ------------------------------------------
+ * The graph search either side of check_path (lazy_prm.py:41-58 dijkstra, :70-98 wastar_search) for the
+ * roadmap the entry points above produce: nbr / nbr_dist dev [n_rows, row_len] (kNN output; row r = sample
+ * row_offset + r), edge_hit dev [n_rows, row_len] i32 (mpb_edges_check_knn output: >= 0 = colliding),
+ * vertex_hit dev [N] u8 indexed by sample (may be NULL).  Usable edges are travelled in both directions
+ * (lazy_prm.py:141-147 REVERSIBLE).  dist dev [N] f64: +inf everywhere except 0 at the source(s) on entry.
+ * mpb_roadmap_relax runs `sweeps` whole-graph relaxation sweeps, d[v] = min(d[v], fl(d[u] + w)), and sets
+ * *changed (dev i32) to 1 if any distance moved; call until it stays 0.  mpb_roadmap_parents then stores, for
+ * every reached vertex but the source, the smallest neighbour index u with fl(d[u] + w) == d[v]
+ * (parent dev [N] i64, pre-filled with INT64_MAX by the caller). */
+int mpb_roadmap_relax(const int64_t *nbr, const double *nbr_dist, const int32_t *edge_hit,
+                      const uint8_t *vertex_hit, int64_t n_rows, int row_len, int64_t row_offset,
+                      double *dist, int32_t *changed, int sweeps, void *stream);
+int mpb_roadmap_parents(const int64_t *nbr, const double *nbr_dist, const int32_t *edge_hit,
+                        const uint8_t *vertex_hit, int64_t n_rows, int row_len, int64_t row_offset,
+                        const double *dist, int64_t source, int64_t *parent, void *stream);
+
 /* ---- measurement helpers (not part of the planner path) ---------------------------------
  * Issue-rate micro-benchmarks used by bench.py for the roofline denominators: each thread
  * runs `iters` rounds of 8 independent dependent-FMA chains.  flops = 2 * 8 * iters *

@@ -187,6 +187,48 @@ class DeviceRoadmap(object):
         torch.cuda.current_stream().synchronize()
         return host
 
+    # -- shortest path over the built roadmap (lazy_prm.py:41-98: dijkstra / wastar_search, on the device)
+    def shortest_path(self, source, target=None, max_rounds=4096):
+        """Shortest-path distances from sample `source` over the usable edges (free verdict, free end points,
+        both directions), cost = the kNN distance.  -> (dist [N] float64 CUDA tensor, path) where path is the list
+        of sample indices source..target (None when `target` is None or unreachable).  Single-rank roadmaps
+        only: gather nbr_idx / nbr_dist / edge_hit / vertex_hit with roadmap.gather_rows first otherwise."""
+        import ctypes
+        from . import _lib
+        N = self.samples.shape[0]
+        if self.offset != 0 or self.n_local != N:
+            raise NotImplementedError('shortest_path needs the whole roadmap on this rank (gather the shards first)')
+        dev = self.samples.device
+        dist = torch.full((N,), float('inf'), dtype=torch.float64, device=dev)
+        dist[int(source)] = 0.0
+        changed = torch.zeros(1, dtype=torch.int32, device=dev)
+        vhit = self.vertex_hit.to(torch.uint8).contiguous()
+        p = lambda t: ctypes.c_void_p(t.data_ptr())
+        st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+        lib = _lib.lib()
+        rounds = 0
+        while rounds < max_rounds:
+            changed.zero_()
+            _lib.check(lib.mpb_roadmap_relax(p(self.nbr_idx), p(self.nbr_dist), p(self.edge_hit), p(vhit), self.n_local,
+                                             self.kk, 0, p(dist), p(changed), 8, st), "mpb_roadmap_relax")
+            rounds += 8
+            if int(changed.item()) == 0:
+                break
+        self.sssp_sweeps = rounds
+        if target is None or not bool(torch.isfinite(dist[int(target)]).item()):
+            return dist, None
+        parent = torch.full((N,), torch.iinfo(torch.int64).max, dtype=torch.int64, device=dev)
+        _lib.check(lib.mpb_roadmap_parents(p(self.nbr_idx), p(self.nbr_dist), p(self.edge_hit), p(vhit), self.n_local,
+                                           self.kk, 0, p(dist), int(source), p(parent), st), "mpb_roadmap_parents")
+        par = parent.cpu().numpy()
+        path, v = [int(target)], int(target)
+        while v != int(source):
+            v = int(par[v])
+            if v == np.iinfo(np.int64).max or len(path) > N:
+                raise RuntimeError('broken parent chain (zero-length edges between distinct samples?)')
+            path.append(v)
+        return dist, path[::-1]
+
     # -- counts for the metric
     def n_edges_checked(self):
         """Directed sample->neighbour edges checked (self and missing slots excluded)."""

@@ -345,3 +345,38 @@ def test_scan_nearest_radius_matches_oracle(ops, metric):
         assert int(nearest) == i and host(dist)[i] == d
         assert c == len(ridx) and (host(lst)[:c] == ridx).all()
         assert (host(dist)[ridx] == rd).all()
+
+
+def test_roadmap_shortest_path_matches_host_dijkstra(ops):
+    """Device Bellman-Ford sweeps over the built roadmap against scipy's Dijkstra on the same usable edges:
+    identical distances (the fixed point of d[v] = min fl(d[u] + w) is order independent up to the last ulp:
+    compared at 1e-12) and a returned path that is a chain of usable edges with the reported cost."""
+    from scipy.sparse import coo_matrix
+    from scipy.sparse.csgraph import dijkstra
+    from motion_planners_b200 import workloads
+    from motion_planners_b200.roadmap import DeviceRoadmap
+    w = workloads.boxes_world(4, 40, 0.1, 0.3, seed=2)
+    N, k = 20000, 8
+    X = workloads.uniform_samples(N, 4, seed=9)
+    rm = DeviceRoadmap(w, k=k).build(dev(X))
+    idx, dist = host(rm.nbr_idx), host(rm.nbr_dist)
+    ehit, vhit = host(rm.edge_hit), host(rm.vertex_hit)
+    rows = np.repeat(np.arange(N), k + 1).reshape(N, k + 1)
+    ok = (idx >= 0) & (idx != rows) & (ehit < 0) & ~vhit[rows] & ~vhit[np.clip(idx, 0, N - 1)]
+    g = coo_matrix((dist[ok], (rows[ok], idx[ok])), shape=(N, N)).tocsr()
+    g = g.maximum(g.T)                                   # both directions
+    free = np.flatnonzero(~vhit)
+    src, dst = int(free[0]), int(free[-1])
+    ref = dijkstra(g, directed=False, indices=src)
+    d, path = rm.shortest_path(src, dst)
+    d = host(d)
+    both = np.isfinite(ref)
+    assert (np.isfinite(d) == both).all()
+    assert np.allclose(d[both], ref[both], rtol=1e-12, atol=0)
+    assert path is not None and path[0] == src and path[-1] == dst
+    cost = 0.0
+    for a, b in zip(path[:-1], path[1:]):
+        assert g[a, b] > 0                               # a usable edge of the roadmap
+        cost += g[a, b]
+    assert abs(cost - d[dst]) <= 1e-9 * d[dst]
+    assert both.sum() > N // 2
