@@ -112,6 +112,7 @@ def cpu_sample_rate(world, X, k, budget_s=12.0, first=8000):
     """The oracle port on a bounded sample: the first `first` queries (grown until ~budget_s of CPU work)."""
     from oracle import cpu_baseline
     from scipy.spatial import KDTree
+    cpu_baseline.cores()
     n = X.shape[0]
     t0 = time.perf_counter()
     tree = KDTree(X)
@@ -133,6 +134,7 @@ def run_reference_arm(args, rank):
         return 0
     from oracle import cpu_baseline
     from scipy.spatial import KDTree
+    cpu_baseline.cores()                                  # all host cores, whatever the launcher exported
     world, X, k, desc = make_workload(args.workload)
     n = X.shape[0]
     tree = KDTree(X)
@@ -470,6 +472,7 @@ def main():
     if rank == 0:
         print(json.dumps(line))
     if world_size > 1:
+        dist.barrier()                 # rank 0 may still be inside its single-rank extras
         dist.destroy_process_group()
     return 0
 

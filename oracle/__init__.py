@@ -204,3 +204,10 @@ def radius(nodes, q, r, w=None, mode=METRIC_SAMPLERS):
 
 def num_threads():
     return int(lib().orc_num_threads())
+
+
+def use_all_cores():
+    """Let the OpenMP loops of the C oracle use every host core (launchers such as torchrun set
+    OMP_NUM_THREADS=1 for their workers)."""
+    lib().orc_set_threads(int(os.cpu_count() or 1))
+    return num_threads()

@@ -88,4 +88,4 @@ def python_port_step(world, X, q_lo, q_hi, k):
 
 
 def cores():
-    return oracle.num_threads()
+    return oracle.use_all_cores()
