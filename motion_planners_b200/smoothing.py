@@ -125,3 +125,98 @@ def smooth_path(path, extend_fn, collision_fn, distance_fn=None, cost_fn=None, s
         cost = new_cost
         last_time = time.time()
     return [waypoints[0]] + refine_waypoints(waypoints, extend_fn)
+
+
+def smooth_paths_batch(paths, extend_fn, collision_fn, distance_fn, seeds, max_iterations=100, cost_fn=None):
+    """smooth_path for MANY paths in lock step (configs[4]: "linear shortcut smoothing of 10k paths").
+
+    Path i consumes its own generators random.Random(seeds[i]) / numpy RandomState(seeds[i]) with the same
+    calls in the same order as smooth_path does with the global ones, so the result for path i equals
+
+        random.seed(seeds[i]); np.random.seed(seeds[i]); smooth_path(paths[i], ..., max_iterations)
+
+    Per iteration the device sees three launches for the whole batch instead of three per path: the waypoints
+    of the two drawn segments of every path (extend_fn), the collision verdicts of all chosen points, and the
+    verdicts of all bridges.  The per-path bookkeeping (segment draw, cost test, splice) stays on the host.
+    Requires the accelerated primitives."""
+    import random as pyrandom
+    import torch
+    if not (isinstance(collision_fn, GpuCollisionFn) and isinstance(extend_fn, GpuExtendFn)):
+        raise TypeError('smooth_paths_batch needs the accelerated primitives of motion_planners_b200.primitives')
+    if cost_fn is None:
+        cost_fn = distance_fn
+    n = len(paths)
+    way = [waypoints_from_path(p) if p else p for p in paths]
+    cost = [compute_path_cost(w, cost_fn=cost_fn) if w else INF for w in way]
+    rpy = [pyrandom.Random(int(s)) for s in seeds]
+    rnp = [np.random.RandomState(int(s)) for s in seeds]
+    weights = [None] * n                     # cached segment lengths, recomputed when a path changes
+    obs = collision_fn.obstacles
+    for _ in range(int(max_iterations)):
+        # 1. per path: draw the two segments (host; identical generator calls to smooth_path)
+        drawn = []
+        for i in range(n):
+            w = way[i]
+            if not w or len(w) <= 2:
+                continue
+            if weights[i] is None:
+                weights[i] = [distance_fn(w[a], w[a + 1]) for a in range(len(w) - 1)]
+            prob = np.array(weights[i]) / sum(weights[i])
+            s1, s2 = rnp[i].choice(list(range(len(w) - 1)), size=2, replace=True, p=prob)
+            if s1 == s2:
+                continue
+            if s2 < s1:
+                s1, s2 = s2, s1
+            drawn.append((i, int(s1), int(s2)))
+        if not drawn:
+            if all((not w) or len(w) <= 2 for w in way):
+                break
+            continue
+        # 2. waypoints of both segments of every drawn path in one launch
+        q1 = np.array([way[i][s] for i, s1, s2 in drawn for s in (s1, s2)], dtype=np.float64)
+        q2 = np.array([way[i][s + 1] for i, s1, s2 in drawn for s in (s1, s2)], dtype=np.float64)
+        off, pts = extend_fn.batch(q1, q2)
+        off, pts = off.cpu().numpy(), pts.cpu().numpy()
+        cand = []
+        for j, (i, s1, s2) in enumerate(drawn):
+            seg_a = pts[off[2 * j]:off[2 * j + 1] - 1]            # list(extend_fn(...))[:-1]
+            seg_b = pts[off[2 * j + 1]:off[2 * j + 2] - 1]
+            if len(seg_a) == 0 or len(seg_b) == 0:
+                continue
+            p1 = rpy[i].choice(list(seg_a))
+            p2 = rpy[i].choice(list(seg_b))
+            w = way[i]
+            new_w = w[:s1 + 1] + [p1, p2] + w[s2 + 1:]
+            new_cost = compute_path_cost(new_w, cost_fn=cost_fn)
+            if new_cost >= cost[i] or (cost[i] - new_cost) / cost[i] <= 0.0:
+                continue
+            cand.append((i, p1, p2, new_w, new_cost))
+        if not cand:
+            continue
+        # 3. verdicts of all bridges: both end points, then the edge between them without its last waypoint
+        a = torch.from_numpy(np.ascontiguousarray(np.array([c[1] for c in cand]))).cuda()
+        b = torch.from_numpy(np.ascontiguousarray(np.array([c[2] for c in cand]))).cuda()
+        bad = obs.points_check(a) | obs.points_check(b)
+        hit, _ = obs.edges_check_pairs(a, b, mode=ops.EDGE_ANY, skip_last=True, step=extend_fn.step_size,
+                                       want_counts=False)
+        bad = (bad | (hit >= 0)).cpu().numpy()
+        for ok, (i, p1, p2, new_w, new_cost) in zip(~bad, cand):
+            if ok:
+                way[i], cost[i], weights[i] = new_w, new_cost, None
+    # 4. final re-discretisation of every path, one launch
+    out = [None] * n
+    idx = [i for i in range(n) if way[i]]
+    pairs = [(i, a) for i in idx for a in range(len(way[i]) - 1)]
+    if pairs:
+        q1 = np.array([way[i][a] for i, a in pairs], dtype=np.float64)
+        q2 = np.array([way[i][a + 1] for i, a in pairs], dtype=np.float64)
+        off, pts = extend_fn.batch(q1, q2)
+        off, pts = off.cpu().numpy(), pts.cpu().numpy()
+        for j, (i, a) in enumerate(pairs):
+            if out[i] is None:
+                out[i] = [way[i][0]]
+            out[i].extend(list(pts[off[j]:off[j + 1]]))
+    for i in range(n):
+        if out[i] is None:
+            out[i] = [way[i][0]] if way[i] else paths[i]
+    return out

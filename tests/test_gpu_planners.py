@@ -318,3 +318,30 @@ def test_solve_dispatch(mp, golden):
     with pytest.raises(NotImplementedError):
         solve(start, goal, dist, sample_fn, ext, col, algorithm="lattice")
     assert solve(np.array([0.5, 0.5]), goal, dist, sample_fn, ext, col) is False   # start inside the centre box
+
+
+@pytest.mark.parametrize("name", ["problem1", "boxes7d"])
+def test_smooth_paths_batch_equals_per_path_smoothing(mp, golden, name):
+    """Lock-step smoothing of many paths, each with its own seeded generators, equals smooth_path run path
+    by path under the same seeds (smooth_path itself is pinned to the reference through the birrt fixtures)."""
+    import random
+    from motion_planners_b200.smoothing import smooth_path, smooth_paths_batch
+    g = golden("rrt_connect_" + name)
+    world = _world(mp, g)
+    dist, ext, col = _tree_primitives(mp, world)
+    paths = [list(p) for p in _paths_from(g) if p is not None]
+    seeds = [500 + i for i in range(len(paths))]
+    expected = []
+    for p, s in zip(paths, seeds):
+        random.seed(s)
+        np.random.seed(s)
+        expected.append(smooth_path(p, ext, col, distance_fn=dist, max_iterations=30))
+    got = smooth_paths_batch(paths, ext, col, dist, seeds, max_iterations=30)
+    assert len(got) == len(expected)
+    shorter = 0
+    for a, b, p in zip(got, expected, paths):
+        a, b = np.array(a), np.array(b)
+        assert a.shape == b.shape and (a == b).all()
+        shorter += len(a) < len(p)
+        assert not col.batch(a).any()
+    assert shorter > 0
