@@ -8,7 +8,8 @@ import ctypes
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libmpb200.so")
+# MPB200_LIB overrides the in-tree library (A/B runs of kernel variants); there is still no other fallback
+LIB_PATH = os.environ.get("MPB200_LIB") or os.path.join(HERE, "lib", "libmpb200.so")
 
 _lib = None
 

@@ -24,8 +24,22 @@
 
 namespace {
 
-constexpr int kWarps = 8;          // consumer warps per block
-constexpr int kStages = 4;         // shared-memory ring depth
+#ifndef MPB_KNN_WARPS
+#define MPB_KNN_WARPS 8
+#endif
+constexpr int kWarps = MPB_KNN_WARPS;   // warps per block
+constexpr int kBlocksPerSM = 16 / MPB_KNN_WARPS;   // 16 warps of 128 registers fill an SM
+#ifndef MPB_KNN_STAGES
+#define MPB_KNN_STAGES 3
+#endif
+#ifndef MPB_KNN_TILE2
+#define MPB_KNN_TILE2 1024
+#endif
+#ifndef MPB_KNN_UNROLL
+#define MPB_KNN_UNROLL 8
+#endif
+constexpr int kStages = MPB_KNN_STAGES;   // shared-memory ring depth
+constexpr int kUnroll = MPB_KNN_UNROLL;   // candidate groups per unrolled loop body
 constexpr int kSmallListMaxK = 12; // k up to which 16 survivors per query are kept (else 32)
 constexpr int kHeaderBytes = 512;
 
@@ -39,7 +53,7 @@ struct KnnHeader {
 static_assert(sizeof(KnnHeader) <= kHeaderBytes, "header overflows its slot");
 
 __host__ __device__ constexpr int planes_for(int D) { return (D + 1 + 3) / 4; }
-__host__ __device__ constexpr int tile_for(int D) { return planes_for(D) == 1 ? 1024 : (planes_for(D) == 2 ? 512 : 256); }
+__host__ __device__ constexpr int tile_for(int D) { return planes_for(D) == 1 ? 1024 : (planes_for(D) == 2 ? MPB_KNN_TILE2 : 256); }
 
 __device__ __forceinline__ unsigned long long enc_f64(double v)
 {
@@ -249,7 +263,7 @@ __device__ __forceinline__ float4 lds128(uint32_t addr)
 // (Measured alternatives that lost, see profiles/r1_summary.md: a shared-memory append buffer with periodic
 // compaction; a fixed producer warp; staggered tile order between blocks.)
 template <int D, int Q, int SEG>
-__global__ void __launch_bounds__(kWarps * 32, 2)
+__global__ void __launch_bounds__(kWarps * 32, kBlocksPerSM)
     knn_filter_kernel(const double *__restrict__ x, int64_t N, const double *__restrict__ qs, int64_t M, Weights wt,
                       int k, double r2, const float4 *__restrict__ packed, int n_tiles, KnnHeader *__restrict__ h,
                       int *__restrict__ fb_list, int64_t *__restrict__ out_idx, double *__restrict__ out_dist)
@@ -385,7 +399,7 @@ __global__ void __launch_bounds__(kWarps * 32, 2)
         float4 nxt[P];
 #pragma unroll
         for (int p = 0; p < P; ++p) nxt[p] = lds128(tbase + (uint32_t)(p * TILE) * 16u);
-#pragma unroll 4
+#pragma unroll kUnroll
         for (int c0 = 0; c0 < TILE; c0 += 32) {
             float xv[4 * P];
 #pragma unroll
