@@ -229,6 +229,80 @@ class DeviceRoadmap(object):
             path.append(v)
         return dist, path[::-1]
 
+    # -- persistence and the reference-shaped view
+    def save(self, path):
+        """Store the built roadmap (tensors + obstacle set) with torch.save; the reference has no on-disk
+        form (lazy_prm.py:267 lists it as a TODO)."""
+        w = self.world
+        torch.save({'k': self.k, 'weights': self.weights, 'max_distance': self.max_distance, 'step': self.step,
+                    'offset': self.offset, 'samples': self.samples.cpu(), 'nbr_idx': self.nbr_idx.cpu(),
+                    'nbr_dist': self.nbr_dist.cpu(), 'vertex_hit': self.vertex_hit.cpu(),
+                    'edge_hit': self.edge_hit.cpu(),
+                    'world': {'dim': w.dim, 'env_lo': w.env_lo, 'env_hi': w.env_hi, 'box_lo': w.box_lo,
+                              'box_hi': w.box_hi, 'sph_c': w.sph_c, 'sph_r': w.sph_r, 'buffer': w.buffer}}, path)
+
+    @staticmethod
+    def load(path, group=None):
+        from .geometry import World
+        d = torch.load(path, weights_only=False)
+        rm = DeviceRoadmap(World(**d['world']), k=d['k'], weights=d['weights'], max_distance=d['max_distance'],
+                           step=d['step'], group=group)
+        rm.samples = d['samples'].cuda()
+        rm.offset = int(d['offset'])
+        rm.nbr_idx, rm.nbr_dist = d['nbr_idx'].cuda(), d['nbr_dist'].cuda()
+        rm.vertex_hit, rm.edge_hit = d['vertex_hit'].cuda(), d['edge_hit'].cuda()
+        rm.n_local = rm.nbr_idx.shape[0]
+        return rm
+
+    def to_reference_roadmap(self, extend_fn, collision_fn, cost_fn=None, samples=None):
+        """Materialise the reference-shaped lazy_prm.Roadmap (edge set, adjacency, colliding_* dictionaries
+        as check_roadmap would leave them) from the device tensors, without recomputing any neighbour or any
+        verdict that is already on the device.  `samples`: the configuration objects to store (default: rows of
+        the sample table).  Single-rank roadmaps only."""
+        from .lazy_prm import Roadmap
+        N = self.samples.shape[0]
+        if self.offset != 0 or self.n_local != N:
+            raise NotImplementedError('gather the shards first')
+        host = self.samples.cpu().numpy()
+        objs = list(samples) if samples is not None else [row for row in host]
+        weights = self.weights if self.weights is not None else np.ones(host.shape[1])
+        rm = Roadmap(extend_fn, weights=weights, cost_fn=cost_fn, max_degree=self.k, max_distance=self.max_distance)
+        list(rm.nearest.add_data(objs))
+        idx = self.nbr_idx.cpu().numpy()
+        for v1 in range(N):                       # the insert order of lazy_prm.py:148-160
+            for v2 in idx[v1]:
+                if v2 >= 0 and v2 != v1:
+                    rm.add_edge(v1, int(v2))
+        vhit = self.vertex_hit.cpu().numpy()
+        for v in range(N):
+            rm.colliding_vertices[v] = bool(vhit[v])
+        # check_roadmap evaluates the first-met direction of every undirected edge (set iteration order)
+        ehit = self.edge_hit.cpu().numpy()
+        known = {}
+        for v1 in range(N):
+            for j, v2 in enumerate(idx[v1]):
+                if v2 >= 0 and v2 != v1:
+                    known[v1, int(v2)] = bool(ehit[v1, j] >= 0)
+        first, seen = [], set()
+        for e in rm.edges:
+            if e not in seen:
+                first.append(e)
+                seen.add(e)
+                seen.add(e[::-1])
+        missing = [e for e in first if e not in known]
+        if missing:
+            src = torch.tensor([a for a, _ in missing], dtype=torch.int64, device='cuda')
+            dst = torch.tensor([b for _, b in missing], dtype=torch.int64, device='cuda')
+            hit, _ = self.obstacles.edges_check(self.samples, src, dst, mode=ops.EDGE_ANY, step=self.step,
+                                                want_counts=False)
+            for e, h in zip(missing, hit.cpu().numpy()):
+                known[e] = bool(h >= 0)
+        for a, b in first:
+            rm.colliding_edges[a, b] = known[a, b]
+            rm.colliding_edges[b, a] = known[a, b]
+            rm._note_direction(a, b)
+        return rm
+
     # -- counts for the metric
     def n_edges_checked(self):
         """Directed sample->neighbour edges checked (self and missing slots excluded)."""

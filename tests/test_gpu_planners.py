@@ -345,3 +345,29 @@ def test_smooth_paths_batch_equals_per_path_smoothing(mp, golden, name):
         shorter += len(a) < len(p)
         assert not col.batch(a).any()
     assert shorter > 0
+
+
+def test_device_roadmap_view_equals_dropin_roadmap(mp, golden, tmp_path):
+    """DeviceRoadmap -> save/load -> reference-shaped Roadmap equals the reference's own Roadmap after
+    add_samples + check_roadmap (golden), without recomputing what is already on the device."""
+    from motion_planners_b200.roadmap import DeviceRoadmap
+    g = golden("roadmap_boxes6d")
+    world = _world(mp, g)
+    X = g["samples"]
+    k = int(g["max_degree"])
+    built = DeviceRoadmap(world, k=k).build(torch.from_numpy(X).cuda())
+    f = str(tmp_path / "roadmap.pt")
+    built.save(f)
+    loaded = DeviceRoadmap.load(f)
+    assert torch.equal(loaded.nbr_idx, built.nbr_idx) and torch.equal(loaded.edge_hit, built.edge_hit)
+    ext = mp.primitives.get_extend_fn()
+    col = mp.primitives.GpuCollisionFn(world)
+    view = loaded.to_reference_roadmap(ext, col)
+    assert (_edge_array(view.edges) == g["edges"]).all()
+    cv = np.array([view.colliding_vertices[v] for v in range(len(X))])
+    assert (cv == g["colliding_vertices"]).all()
+    ce = np.array(sorted((a, b, int(fl)) for (a, b), fl in view.colliding_edges.items()), np.int64)
+    assert ce.shape == g["colliding_edges"].shape and (ce == g["colliding_edges"]).all()
+    # and it is a working Roadmap: a query over it finds a collision-free path
+    d, path = loaded.shortest_path(int(np.flatnonzero(~cv)[0]), int(np.flatnonzero(~cv)[-1]))
+    assert path is None or not cv[path].any()
