@@ -35,11 +35,29 @@ constexpr int kBlocksPerSM = 16 / MPB_KNN_WARPS;   // 16 warps of 128 registers 
 #ifndef MPB_KNN_TILE2
 #define MPB_KNN_TILE2 1024
 #endif
+// Two builds of the filter kernel, chosen by the number of candidates (measured, profiles/r1_summary.md):
+//  * LONG scans spend their time in the multiply-add stream: 8 groups per loop body and every plane of the next
+//    group prefetched keep the FMA pipe fed;
+//  * SHORT scans (up to kShortScanMax candidates) still insert into the lists at most steps, the instruction
+//    stream runs through the insertion code all the time, and a body that fits the instruction cache wins:
+//    2 groups per body, no prefetch registers.
 #ifndef MPB_KNN_UNROLL
 #define MPB_KNN_UNROLL 8
 #endif
+#ifndef MPB_KNN_PREFETCH
+#define MPB_KNN_PREFETCH 8   // planes of the next group fetched one step ahead (clamped to the planes there are)
+#endif
+#ifndef MPB_KNN_UNROLL_SHORT
+#define MPB_KNN_UNROLL_SHORT 2
+#endif
+#ifndef MPB_KNN_PREFETCH_SHORT
+#define MPB_KNN_PREFETCH_SHORT 0
+#endif
+#ifndef MPB_KNN_SHORT_MAX
+#define MPB_KNN_SHORT_MAX 262144
+#endif
+constexpr int64_t kShortScanMax = MPB_KNN_SHORT_MAX;
 constexpr int kStages = MPB_KNN_STAGES;   // shared-memory ring depth
-constexpr int kUnroll = MPB_KNN_UNROLL;   // candidate groups per unrolled loop body
 constexpr int kSmallListMaxK = 12; // k up to which 16 survivors per query are kept (else 32)
 constexpr int kHeaderBytes = 512;
 
@@ -130,9 +148,8 @@ __global__ void knn_finalize_kernel(KnnHeader *h, int D)
     h->R = sqrt(r2) * (1.0 + 1e-6) + 1e-300;
 }
 
-// Tile-planar layout: tile t holds TILE candidates as P planes of TILE float4 each;
-// component index D of a candidate's P*4 floats is its squared norm, the rest of the
-// padding is zero.  Slots past N carry an infinite norm so that they never qualify.
+// Tile t holds TILE candidates, 4P floats each: the centred fp32 coordinates, at index D the squared norm,
+// zeros after it.  Slots past N carry an infinite norm so that they never qualify.
 template <int D>
 __global__ void __launch_bounds__(256)
     knn_pack_kernel(const double *__restrict__ x, int64_t N, int64_t Npad, Weights wt, const KnnHeader *__restrict__ h,
@@ -157,11 +174,19 @@ __global__ void __launch_bounds__(256)
     } else {
         v[D] = INFINITY;
     }
+    // Tile layout for the pair-wise scoring of the filter kernel: within a group of 64 candidates lane l owns
+    // candidates l ("a") and 32 + l ("b"); value i of both sits side by side, two values per float4:
+    //   plane m (0 .. 2P-1), entry g*32 + l  =  (a[2m], b[2m], a[2m+1], b[2m+1])
+    // so that one LDS.128 delivers two ready-made (a, b) register pairs for FFMA2.
     const int64_t t = j / TILE;
     const int c = (int)(j - t * TILE);
+    const int g = c >> 6, r = c & 63, l = r & 31, half = r >> 5;
+    float *base = reinterpret_cast<float *>(packed) + (size_t)t * TILE * P * 4;
 #pragma unroll
-    for (int p = 0; p < P; ++p)
-        packed[(t * P + p) * TILE + c] = make_float4(v[4 * p], v[4 * p + 1], v[4 * p + 2], v[4 * p + 3]);
+    for (int i = 0; i < 4 * P; ++i) {
+        const int m = i >> 1;
+        base[((size_t)m * (TILE / 2) + (size_t)(g * 32 + l)) * 4 + (i & 1) * 2 + half] = v[i];
+    }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -262,7 +287,7 @@ __device__ __forceinline__ float4 lds128(uint32_t addr)
 // query q of the warp lives in register q / (32/SEG), lanes [SEG*(q % (32/SEG)), +SEG), sorted ascending.
 // (Measured alternatives that lost, see profiles/r1_summary.md: a shared-memory append buffer with periodic
 // compaction; a fixed producer warp; staggered tile order between blocks.)
-template <int D, int Q, int SEG>
+template <int D, int Q, int SEG, int UNROLL, int PREFETCH>
 __global__ void __launch_bounds__(kWarps * 32, kBlocksPerSM)
     knn_filter_kernel(const double *__restrict__ x, int64_t N, const double *__restrict__ qs, int64_t M, Weights wt,
                       int k, double r2, const float4 *__restrict__ packed, int n_tiles, KnnHeader *__restrict__ h,
@@ -304,22 +329,21 @@ __global__ void __launch_bounds__(kWarps * 32, kBlocksPerSM)
 
     // ---- this warp's Q queries, as -2*fl32(e_q - c), uniform across the lanes
     const int64_t q0 = ((int64_t)blockIdx.x * kWarps + warp) * Q;
-    // kept as packed pairs (queries 2p and 2p+1): one FFMA2 scores a candidate for both
-    static_assert(Q % 2 == 0, "queries are processed in pairs");
-    f32x2_t qmp[Q / 2][D];
+    // Every lane computes the same value; passing it through a warp reduction lands it in a UNIFORM register
+    // (REDUX writes one), and FFMA2 takes a uniform scalar as its broadcast operand.  With the coefficients off
+    // the vector register file, and the candidate pair reused by the Q chains of a coordinate, each FFMA2 reads
+    // a single fresh vector operand (its accumulator) and the FMA pipe runs at its full rate; with a second
+    // fresh vector operand it sustains only ~63 % of that (operand-pattern micro-benchmarks, profiles/).
+    float qm[Q][D];
 #pragma unroll
-    for (int p = 0; p < Q / 2; ++p) {
+    for (int qi = 0; qi < Q; ++qi) {
+        int64_t q = q0 + qi;
+        if (q >= M) q = M - 1;
 #pragma unroll
         for (int d = 0; d < D; ++d) {
-            float v[2];
-#pragma unroll
-            for (int hq = 0; hq < 2; ++hq) {
-                int64_t q = q0 + 2 * p + hq;
-                if (q >= M) q = M - 1;
-                const double e = d_mul(wt.w[d], qs[q * D + d]);
-                v[hq] = -2.f * (float)d_sub(e, h->center[d]);
-            }
-            qmp[p][d] = pack_f32x2(v[0], v[1]);
+            const double e = d_mul(wt.w[d], qs[q * D + d]);
+            const float v = -2.f * (float)d_sub(e, h->center[d]);
+            qm[qi][d] = __uint_as_float(__reduce_or_sync(FULL_MASK, __float_as_uint(v)));
         }
     }
     float thr[Q], lk[NREG];
@@ -335,18 +359,26 @@ __global__ void __launch_bounds__(kWarps * 32, kBlocksPerSM)
     const uint32_t smem0 = smem_u32(stage_base) + (uint32_t)lane * 16u;
 
     // Insertion rounds for one group of 32 candidates (lane <-> candidate cbase + lane) whose keys are `key32`.
-    // Every round gives each query at most one of its passing candidates; the rounds are branch-free so that
-    // the shuffle chains of all list registers overlap.  A candidate that no longer beats its list (or "no
-    // candidate": key = +inf) lands at position SEG, i.e. nowhere.
+    // Every round gives each query at most one of its passing candidates, so the shuffle chains of the list
+    // registers that have a taker overlap.  A candidate that no longer beats its list (or "no candidate":
+    // key = +inf) lands at position SEG, i.e. nowhere.
     auto insert_group = [&](const float (&key32)[Q], int cbase) {
         unsigned m[Q];
 #pragma unroll
         for (int qi = 0; qi < Q; ++qi) m[qi] = __ballot_sync(FULL_MASK, key32[qi] < thr[qi]);
-        bool more = true;
+        bool more = false;
+#pragma unroll
+        for (int qi = 0; qi < Q; ++qi) more = more || (m[qi] != 0);
         while (more) {
             more = false;
 #pragma unroll
             for (int r = 0; r < NREG; ++r) {
+                // late in the scan a group has a taker for one query at most: skip the list registers with none
+                // (the masks are ballots, so the branch is uniform)
+                unsigned any_r = 0;
+#pragma unroll
+                for (int hs = 0; hs < PER; ++hs) any_r |= m[r * PER + hs];
+                if (any_r == 0) continue;
                 float key = INFINITY;
                 int cidx = -1;
 #pragma unroll
@@ -378,55 +410,82 @@ __global__ void __launch_bounds__(kWarps * 32, kBlocksPerSM)
             }
         }
     };
-    float prev[Q];              // keys of the group scored one step ago, not yet compared
+    // Both halves of a group of 64 go through ONE inlined copy of the insertion code: the scan loop is unrolled,
+    // and every copy costs instruction-cache space (fetch stalls are visible in the profile of this loop).
+    auto insert_halves = [&](const float (&ka)[Q], const float (&kb)[Q], int cbase, bool any_a, bool any_b) {
+#pragma unroll 1
+        for (int hh = 0; hh < 2; ++hh) {
+            if (!(hh ? any_b : any_a)) continue;
+            float key32[Q];
+#pragma unroll
+            for (int qi = 0; qi < Q; ++qi) key32[qi] = hh ? kb[qi] : ka[qi];
+            insert_group(key32, cbase + 32 * hh);
+        }
+    };
+    float prev_a[Q], prev_b[Q];   // keys of the 64 candidates scored one step ago, not yet compared
     int prev_base = 0;
 #pragma unroll
-    for (int qi = 0; qi < Q; ++qi) prev[qi] = INFINITY;
+    for (int qi = 0; qi < Q; ++qi) prev_a[qi] = prev_b[qi] = INFINITY;
 
     // ---- stream every tile through the ring
     for (int t = 0; t < n_tiles; ++t) {
         const int s = t % kStages;
         const uint32_t ph = (uint32_t)(t / kStages) & 1u;
-        mbar_wait(&full[s], ph);
+        mbar_wait_warp(&full[s], ph);
 
         const uint32_t tbase = smem0 + (uint32_t)s * (uint32_t)SM::STAGE_BYTES;
         const int cbase0 = t * TILE;
-        // Software pipeline: while the FFMA2 chains of this group of 32 candidates run, the keys of the
-        // PREVIOUS group (complete long ago) are compared with the thresholds and, if any of them passes,
-        // inserted -- so the compare/vote/branch tail never waits for the arithmetic it follows.  The keys in
-        // flight cross tile boundaries in registers (`prev`, `prev_base`); the last group is drained after the
-        // tile loop.
-        float4 nxt[P];
+        // Each step scores 64 candidates: lane l owns candidates l and 32 + l of the group as a register PAIR per
+        // coordinate, and one FFMA2 advances both keys of one query.  Software pipeline: while the FFMA2 chains
+        // of this group run, the keys of the PREVIOUS group (complete long ago) are compared with the thresholds
+        // and, if any of them passes, inserted -- so the compare/vote/branch tail never waits for the arithmetic
+        // it follows.  The keys in flight cross tile boundaries in registers (`prev_a`, `prev_b`, `prev_base`);
+        // the last group is drained after the tile loop.
+        constexpr int NV = 2 * P;        // float4 per lane per group
+        static_assert(TILE % 64 == 0, "tiles hold whole groups of 64 candidates");
+        // Planes 0 .. NPF-1 of a group are fetched one step ahead (their values are needed the moment the step
+        // starts); the remaining planes are loaded at the top of their own step, where the FFMA2 chains of the
+        // earlier planes cover the shared-memory latency.  Prefetching everything costs 4 registers per plane and
+        // pushes the loop over the 128-register budget.
+        constexpr int NPF = (PREFETCH < NV) ? PREFETCH : NV;
+        float4 nxt[NPF > 0 ? NPF : 1];
 #pragma unroll
-        for (int p = 0; p < P; ++p) nxt[p] = lds128(tbase + (uint32_t)(p * TILE) * 16u);
-#pragma unroll kUnroll
-        for (int c0 = 0; c0 < TILE; c0 += 32) {
-            float xv[4 * P];
+        for (int m = 0; m < NPF; ++m) nxt[m] = lds128(tbase + (uint32_t)(m * (TILE / 2)) * 16u);
+#pragma unroll UNROLL
+        for (int c0 = 0; c0 < TILE; c0 += 64) {
+            f32x2_t xv[4 * P];           // xv[i] = (value i of candidate a, value i of candidate b)
 #pragma unroll
-            for (int p = 0; p < P; ++p) {
-                xv[4 * p + 0] = nxt[p].x;
-                xv[4 * p + 1] = nxt[p].y;
-                xv[4 * p + 2] = nxt[p].z;
-                xv[4 * p + 3] = nxt[p].w;
+            for (int m = 0; m < NV; ++m) {
+                const float4 f = (m < NPF) ? nxt[m] : lds128(tbase + (uint32_t)(m * (TILE / 2) + c0 / 2) * 16u);
+                xv[2 * m + 0] = pack_f32x2(f.x, f.y);
+                xv[2 * m + 1] = pack_f32x2(f.z, f.w);
             }
-            if (c0 + 32 < TILE) {   // next group's candidates are in flight while this one is scored
+            if (c0 + 64 < TILE) {
 #pragma unroll
-                for (int p = 0; p < P; ++p) nxt[p] = lds128(tbase + (uint32_t)(p * TILE + c0 + 32) * 16u);
+                for (int m = 0; m < NPF; ++m)
+                    nxt[m] = lds128(tbase + (uint32_t)(m * (TILE / 2) + (c0 + 64) / 2) * 16u);
             }
-            bool pass = false;
+            bool pass_a = false, pass_b = false;
 #pragma unroll
-            for (int qi = 0; qi < Q; ++qi) pass = pass || (prev[qi] < thr[qi]);
-            float acc[Q];
-#pragma unroll
-            for (int p = 0; p < Q / 2; ++p) {
-                f32x2_t a = pack_f32x2(xv[D], xv[D]);
-#pragma unroll
-                for (int d = 0; d < D; ++d) a = fma_f32x2(qmp[p][d], pack_f32x2(xv[d], xv[d]), a);
-                unpack_f32x2(a, acc[2 * p], acc[2 * p + 1]);
+            for (int qi = 0; qi < Q; ++qi) {
+                pass_a = pass_a || (prev_a[qi] < thr[qi]);
+                pass_b = pass_b || (prev_b[qi] < thr[qi]);
             }
-            if (__any_sync(FULL_MASK, pass)) insert_group(prev, prev_base);
+            float acc_a[Q], acc_b[Q];
 #pragma unroll
-            for (int qi = 0; qi < Q; ++qi) prev[qi] = acc[qi];
+            for (int qi = 0; qi < Q; ++qi) {
+                f32x2_t a = xv[D];
+#pragma unroll
+                for (int d = 0; d < D; ++d) a = fma_f32x2(xv[d], pack_f32x2(qm[qi][d], qm[qi][d]), a);
+                unpack_f32x2(a, acc_a[qi], acc_b[qi]);
+            }
+            const bool any_a = __any_sync(FULL_MASK, pass_a), any_b = __any_sync(FULL_MASK, pass_b);
+            if (any_a || any_b) insert_halves(prev_a, prev_b, prev_base, any_a, any_b);
+#pragma unroll
+            for (int qi = 0; qi < Q; ++qi) {
+                prev_a[qi] = acc_a[qi];
+                prev_b[qi] = acc_b[qi];
+            }
             prev_base = cbase0 + c0;
         }
         // The last warp to release a slot requests its next tenant: nobody waits for anybody.
@@ -444,10 +503,7 @@ __global__ void __launch_bounds__(kWarps * 32, kBlocksPerSM)
     }
 
     {   // drain the software pipeline: the last group scored has not been compared yet
-        bool pass = false;
-#pragma unroll
-        for (int qi = 0; qi < Q; ++qi) pass = pass || (prev[qi] < thr[qi]);
-        if (__any_sync(FULL_MASK, pass)) insert_group(prev, prev_base);
+        insert_halves(prev_a, prev_b, prev_base, true, true);
     }
 
     // ---- exact re-rank of the survivors and the certificate; the PER lists of a register are handled
@@ -467,14 +523,8 @@ __global__ void __launch_bounds__(kWarps * 32, kBlocksPerSM)
 #pragma unroll
         for (int d = 0; d < D; ++d) {
             eq[d] = d_mul(wt.w[d], qs[qc * D + d]);
-            float qmd = 0.f;
-#pragma unroll
-            for (int hs = 0; hs < PER; ++hs) {
-                float lo, hi;
-                unpack_f32x2(qmp[(r * PER + hs) / 2][d], lo, hi);
-                const float v = ((r * PER + hs) & 1) ? hi : lo;
-                qmd = (hs == 0 || seg == hs) ? v : qmd;
-            }
+            // the query's fp32 coordinate, recomputed exactly as it was for the scan (eq[d] is this lane's query)
+            const float qmd = -2.f * (float)d_sub(eq[d], h->center[d]);
             const double qh = -0.5 * (double)qmd;
             nq2 += qh * qh;
         }
@@ -615,26 +665,41 @@ int launch_prepare(const double *x, int64_t N, const Weights &wt, void *ws, cuda
     return MPB_OK;
 }
 
+template <int D, int Q, int SEG, int UNROLL, int PREFETCH>
+int launch_filter_as(const double *x, int64_t N, const double *qs, int64_t M, const Weights &wt, int k, double r2,
+                     const float4 *packed, int n_tiles, KnnHeader *h, int *fb, int64_t *out_idx, double *out_dist,
+                     cudaStream_t st)
+{
+    using SM = FilterSmem<D, Q>;
+    auto kernel = knn_filter_kernel<D, Q, SEG, UNROLL, PREFETCH>;
+    MPB_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SM::BYTES));
+    const int64_t blocks = (M + (int64_t)kWarps * Q - 1) / ((int64_t)kWarps * Q);
+    kernel<<<(unsigned)blocks, kWarps * 32, SM::BYTES, st>>>(x, N, qs, M, wt, k, r2, packed, n_tiles, h, fb, out_idx,
+                                                             out_dist);
+    MPB_LAUNCH_CHECK();
+    return MPB_OK;
+}
+
 template <int D, int Q, int SEG>
 int launch_filter(const double *x, int64_t N, const double *qs, int64_t M, const Weights &wt, int k, double r2,
                   const float4 *packed, int n_tiles, KnnHeader *h, int *fb, int64_t *out_idx, double *out_dist,
                   cudaStream_t st)
 {
-    using SM = FilterSmem<D, Q>;
-    MPB_CUDA_CHECK(cudaFuncSetAttribute(knn_filter_kernel<D, Q, SEG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        (int)SM::BYTES));
-    const int64_t blocks = (M + (int64_t)kWarps * Q - 1) / ((int64_t)kWarps * Q);
-    knn_filter_kernel<D, Q, SEG><<<(unsigned)blocks, kWarps * 32, SM::BYTES, st>>>(x, N, qs, M, wt, k, r2, packed,
-                                                                                  n_tiles, h, fb, out_idx, out_dist);
-    MPB_LAUNCH_CHECK();
-    return MPB_OK;
+    if (N <= kShortScanMax)
+        return launch_filter_as<D, Q, SEG, MPB_KNN_UNROLL_SHORT, MPB_KNN_PREFETCH_SHORT>(
+            x, N, qs, M, wt, k, r2, packed, n_tiles, h, fb, out_idx, out_dist, st);
+    return launch_filter_as<D, Q, SEG, MPB_KNN_UNROLL, MPB_KNN_PREFETCH>(x, N, qs, M, wt, k, r2, packed, n_tiles, h,
+                                                                         fb, out_idx, out_dist, st);
 }
 
 template <int D>
 int launch_search(const double *x, int64_t N, const double *qs, int64_t M, const Weights &wt, int k, double r2,
                   void *ws, int64_t *out_idx, double *out_dist, int64_t *stats, cudaStream_t st)
 {
-    constexpr int Q = (D <= 8) ? 8 : 4;
+#ifndef MPB_KNN_Q
+#define MPB_KNN_Q 8
+#endif
+    constexpr int Q = (D <= 8) ? MPB_KNN_Q : 4;
     const WsLayout L = ws_layout(N, M, D);
     KnnHeader *h = reinterpret_cast<KnnHeader *>(ws);
     const float4 *packed = reinterpret_cast<const float4 *>(reinterpret_cast<char *>(ws) + L.packed_off);

@@ -189,6 +189,14 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
         if (spins > (1u << 26)) __trap();
     }
 }
+// The same for a whole (converged) warp: the loop condition is a vote, so the wait introduces no divergence
+// and the compiler may keep treating the code after it as warp-uniform.
+__device__ __forceinline__ void mbar_wait_warp(uint64_t *bar, uint32_t parity)
+{
+    for (uint32_t spins = 0; !__all_sync(0xffffffffu, mbar_try_wait(bar, parity)); ++spins) {
+        if (spins > (1u << 26)) __trap();
+    }
+}
 __device__ __forceinline__ void bulk_copy_g2s(void *smem_dst, const void *gmem_src, uint32_t bytes, uint64_t *bar)
 {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
