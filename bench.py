@@ -31,7 +31,7 @@ if ROOT not in sys.path:
 
 import numpy as np  # noqa: E402
 
-NCU_DRAM_BYTES_PER_LAUNCH = {"c4lite": 1.012007e9 + 184.279808e6}
+NCU_DRAM_BYTES_PER_LAUNCH = {"c4lite": 978.515968e6 + 182.364672e6}
 
 METRIC = "PRM edges collision-checked/sec (kNN k=10 + vertex + edge checks per roadmap build step)"
 UNIT = "edges/s"
