@@ -105,6 +105,27 @@ int mpb_edges_count(const double *q1, const double *q2, int64_t n_edges, int dim
 int mpb_edges_waypoints(const double *q1, const double *q2, int64_t n_edges, int dim, double step,
                         const int64_t *offsets, double *out, void *stream);
 
+/* ---- circular (wrap-around) coordinates ---------------------------------------------------
+ * The same three operations for configurations with circular joints: tkinter/samplers.py:113-127
+ * get_extend_fn(circular=...) with primitives.py:74-78 get_difference_fn and utils.py:364-369,381-384
+ * wrap_interval / circular_difference (Python float %: result takes the sign of the divisor).
+ * circ_lo, circ_hi: HOST [dim]; a coordinate with (-inf, +inf) is not circular, otherwise the interval
+ * must be finite with lower < upper.  Waypoints: q <- c*diff(q2, q) + q, then every circular coordinate
+ * wrapped into its interval; n = int(max_d |diff(q2, q1)_d / step|) + 1.
+ * mpb_edges_check_circular: src/dst both NULL = explicit endpoint arrays a, b dev [E, dim]; otherwise
+ * a = samples dev [N, dim], b unused, src/dst dev [E] i64 (negative = no edge: out_hit -1, out_n 0).
+ * Modes, skip_last and outputs as mpb_edges_check. */
+int mpb_edges_check_circular(const mpb_world *world, const double *a, const double *b,
+                             const int64_t *src, const int64_t *dst, int64_t n_edges,
+                             const double *circ_lo, const double *circ_hi, double step, int mode,
+                             int skip_last, int32_t *out_hit, int32_t *out_n, void *stream);
+int mpb_edges_count_circular(const double *q1, const double *q2, int64_t n_edges, int dim,
+                             const double *circ_lo, const double *circ_hi, double step,
+                             int32_t *out_n, void *stream);
+int mpb_edges_waypoints_circular(const double *q1, const double *q2, int64_t n_edges, int dim,
+                                 const double *circ_lo, const double *circ_hi, double step,
+                                 const int64_t *offsets, double *out, void *stream);
+
 /* ---- k nearest neighbours ---------------------------------------------------------------
  * Replaces nearest.py:36-85 KDNeighbors.query_neighbors (scipy cKDTree, p = 2, eps = 0,
  * no circular dimensions) as called per sample by lazy_prm.py:148-160, and the full
@@ -129,6 +150,16 @@ int mpb_knn_f64(const double *samples, int64_t n_samples, const double *queries,
 int mpb_knn_f64_metric(const double *samples, int64_t n_samples, const double *queries,
                        int64_t n_queries, int dim, const double *weights, int metric, int k,
                        double max_dist, int64_t *out_idx, double *out_dist, void *stream);
+
+/* mpb_knn_f64 with circular coordinates: nearest.py:7-20 expand_circular + nearest.py:74-85
+ * query_neighbors shift the query by {-E, 0, +E} (E = upper - lower) in every circular coordinate,
+ * query the kd-tree once per image and keep each index's smallest distance.  Here every sample's
+ * key is the kd-tree sum over the per-coordinate smallest of the three image terms (equal to the
+ * smallest image key, because rounded addition is monotone).  circ_lo / circ_hi as above. */
+int mpb_knn_f64_circular(const double *samples, int64_t n_samples, const double *queries,
+                         int64_t n_queries, int dim, const double *weights, const double *circ_lo,
+                         const double *circ_hi, int k, double max_dist, int64_t *out_idx,
+                         double *out_dist, void *stream);
 
 /* Tiled fp32 filter + fp64 re-rank, same results bit for bit: an fp32 pass over
  * shared-memory tiles keeps 32 candidates per query, the exact fp64 keys of those

@@ -35,6 +35,13 @@ SIGNATURES = {
     "mpb_edges_check_pairs": (c_int, [c_vp, c_vp, c_vp, c_i64, c_dbl, c_int, c_int, c_vp, c_vp, c_vp]),
     "mpb_edges_count": (c_int, [c_vp, c_vp, c_i64, c_int, c_dbl, c_vp, c_vp]),
     "mpb_edges_waypoints": (c_int, [c_vp, c_vp, c_i64, c_int, c_dbl, c_vp, c_vp, c_vp]),
+    "mpb_edges_check_circular": (c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_hostf64, c_hostf64, c_dbl, c_int,
+                                         c_int, c_vp, c_vp, c_vp]),
+    "mpb_edges_count_circular": (c_int, [c_vp, c_vp, c_i64, c_int, c_hostf64, c_hostf64, c_dbl, c_vp, c_vp]),
+    "mpb_edges_waypoints_circular": (c_int, [c_vp, c_vp, c_i64, c_int, c_hostf64, c_hostf64, c_dbl, c_vp, c_vp,
+                                             c_vp]),
+    "mpb_knn_f64_circular": (c_int, [c_vp, c_i64, c_vp, c_i64, c_int, c_hostf64, c_hostf64, c_hostf64, c_int, c_dbl,
+                                     c_vp, c_vp, c_vp]),
     "mpb_knn_f64": (c_int, [c_vp, c_i64, c_vp, c_i64, c_int, c_hostf64, c_int, c_dbl, c_vp, c_vp, c_vp]),
     "mpb_knn_f64_metric": (c_int, [c_vp, c_i64, c_vp, c_i64, c_int, c_hostf64, c_int, c_int, c_dbl, c_vp, c_vp, c_vp]),
     "mpb_knn_workspace_bytes": (c_sz, [c_i64, c_i64, c_int]),

@@ -270,7 +270,8 @@ class Roadmap(object):
                 rows1, rows2 = self._sample_rows([v1]), self._sample_rows([v2])
                 h, _ = collision_fn.obstacles.edges_check_pairs(torch.from_numpy(rows1).cuda(),
                                                                 torch.from_numpy(rows2).cuda(), mode=ops.EDGE_ANY,
-                                                                step=self.extend_fn.step_size, want_counts=False)
+                                                                step=self.extend_fn.step_size, want_counts=False,
+                                                            circular=getattr(self.extend_fn, 'circular', None))
                 hit = bool(h[0].item() >= 0)
             else:
                 path = self.get_path(v1, v2)
@@ -333,7 +334,8 @@ class Roadmap(object):
                 src = torch.tensor([a for a, _ in todo], dtype=torch.int64, device='cuda')
                 dst = torch.tensor([b for _, b in todo], dtype=torch.int64, device='cuda')
                 hit, _ = collision_fn.obstacles.edges_check(dev, src, dst, mode=ops.EDGE_ANY,
-                                                            step=self.extend_fn.step_size, want_counts=False)
+                                                            step=self.extend_fn.step_size, want_counts=False,
+                                                            circular=getattr(self.extend_fn, 'circular', None))
                 pre_e = {e: bool(h >= 0) for e, h in zip(todo, hit.cpu().numpy())}
         for v1, v2 in order:
             self.check_edge(v1, v2, collision_fn, pre_e)

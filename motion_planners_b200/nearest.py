@@ -25,14 +25,12 @@ class NearestNeighbors(object):
 
 class GpuNeighbors(NearestNeighbors):
     def __init__(self, data=[], circular={}, embed_fn=None, weights=None, **kwargs):
-        if circular:
-            raise NotImplementedError('circular dimensions are outside the accelerated path')
         if weights is None and embed_fn is not None:
             weights = getattr(embed_fn, 'weights', None)
             if weights is None:
                 raise NotImplementedError('only weighted embeddings (get_embed_fn(weights)) are accelerated')
         self.weights = None if weights is None else np.array(weights, dtype=np.float64)
-        self.circular = circular
+        self.circular = dict(circular) if circular else {}   # {coordinate: (lower, upper)}, nearest.py:7-20
         self.data = []
         self._rows = []
         self._dev = None
@@ -81,7 +79,10 @@ class GpuNeighbors(NearestNeighbors):
         kk = min(int(k), ops.MAX_K)
         if int(k) > ops.MAX_K:
             raise NotImplementedError('k > %d' % ops.MAX_K)
-        if q.shape[0] < 64:                    # a handful of queries: one warp each, no tile pass
+        if self.circular:                      # three images per circular coordinate: exact kernel
+            idx, dist = ops.knn(self._dev, q, kk, weights=self.weights, max_dist=float(distance_upper_bound),
+                                method='f64', circular=self.circular)
+        elif q.shape[0] < 64:                  # a handful of queries: one warp each, no tile pass
             idx, dist = ops.knn(self._dev, q, kk, weights=self.weights, max_dist=float(distance_upper_bound),
                                 method='f64')
         else:

@@ -51,6 +51,24 @@ def _host_weights(weights, dim):
     return w, w.ctypes.data_as(ctypes.POINTER(ctypes.c_double))
 
 
+def _host_circular(circular, dim):
+    """circular: {coordinate: (lower, upper)} as the reference passes it (nearest.py:43, samplers.py:113);
+    -> (keep-alive arrays, lo pointer, hi pointer) or None when no coordinate is circular."""
+    if not circular:
+        return None
+    lo = np.full(dim, -np.inf)
+    hi = np.full(dim, np.inf)
+    for d, interval in dict(circular).items():
+        d = int(d)
+        if not 0 <= d < dim:
+            raise ValueError("circular coordinate %d outside [0, %d)" % (d, dim))
+        lo[d], hi[d] = float(interval[0]), float(interval[1])
+    if not (np.isfinite(lo) | np.isfinite(hi)).any():
+        return None
+    hp = lambda a: a.ctypes.data_as(ctypes.POINTER(ctypes.c_double))
+    return (lo, hi), hp(lo), hp(hi)
+
+
 class ObstacleSet(object):
     """Device-resident obstacle set (mpb_world) for one World on the current CUDA device."""
 
@@ -88,7 +106,8 @@ class ObstacleSet(object):
         return out.bool()
 
     # -- extend_fn + collision_fn over directed edges given as index pairs
-    def edges_check(self, samples, src, dst, mode=EDGE_ANY, skip_last=False, step=STEP_SIZE, want_counts=True):
+    def edges_check(self, samples, src, dst, mode=EDGE_ANY, skip_last=False, step=STEP_SIZE, want_counts=True,
+                    circular=None):
         samples = _f64(samples, "samples", self.dim)
         src = _i64(src, "src")
         dst = _i64(dst, "dst")
@@ -97,6 +116,13 @@ class ObstacleSet(object):
         E = src.shape[0]
         hit = torch.empty(E, dtype=torch.int32, device=samples.device)
         cnt = torch.empty(E, dtype=torch.int32, device=samples.device) if want_counts else None
+        circ = _host_circular(circular, self.dim)
+        if circ is not None:
+            rc = _lib.lib().mpb_edges_check_circular(self._h, _ptr(samples), None, _ptr(src), _ptr(dst), E, circ[1],
+                                                     circ[2], float(step), int(mode), int(bool(skip_last)),
+                                                     _ptr(hit), _ptr(cnt), _stream())
+            _lib.check(rc, "mpb_edges_check_circular")
+            return hit, cnt
         rc = _lib.lib().mpb_edges_check(self._h, _ptr(samples), samples.shape[0], _ptr(src), _ptr(dst), E,
                                         float(step), int(mode), int(bool(skip_last)), _ptr(hit), _ptr(cnt),
                                         _stream())
@@ -119,7 +145,8 @@ class ObstacleSet(object):
         return hit, cnt
 
     # -- the same for explicit endpoint arrays
-    def edges_check_pairs(self, q1, q2, mode=EDGE_ANY, skip_last=False, step=STEP_SIZE, want_counts=True):
+    def edges_check_pairs(self, q1, q2, mode=EDGE_ANY, skip_last=False, step=STEP_SIZE, want_counts=True,
+                          circular=None):
         q1 = _f64(q1, "q1", self.dim)
         q2 = _f64(q2, "q2", self.dim)
         if q1.shape != q2.shape:
@@ -127,35 +154,54 @@ class ObstacleSet(object):
         E = q1.shape[0]
         hit = torch.empty(E, dtype=torch.int32, device=q1.device)
         cnt = torch.empty(E, dtype=torch.int32, device=q1.device) if want_counts else None
+        circ = _host_circular(circular, self.dim)
+        if circ is not None:
+            rc = _lib.lib().mpb_edges_check_circular(self._h, _ptr(q1), _ptr(q2), None, None, E, circ[1], circ[2],
+                                                     float(step), int(mode), int(bool(skip_last)), _ptr(hit),
+                                                     _ptr(cnt), _stream())
+            _lib.check(rc, "mpb_edges_check_circular")
+            return hit, cnt
         rc = _lib.lib().mpb_edges_check_pairs(self._h, _ptr(q1), _ptr(q2), E, float(step), int(mode),
                                               int(bool(skip_last)), _ptr(hit), _ptr(cnt), _stream())
         _lib.check(rc, "mpb_edges_check_pairs")
         return hit, cnt
 
 
-def edges_count(q1, q2, step=STEP_SIZE):
+def edges_count(q1, q2, step=STEP_SIZE, circular=None):
     """Number of waypoints extend_fn(q1[e], q2[e]) yields (tkinter/samplers.py:119-120) -> int32 [E]."""
     q1 = _f64(q1, "q1")
     q2 = _f64(q2, "q2", q1.shape[1])
     E, D = q1.shape
     out = torch.empty(E, dtype=torch.int32, device=q1.device)
+    circ = _host_circular(circular, D)
+    if circ is not None:
+        rc = _lib.lib().mpb_edges_count_circular(_ptr(q1), _ptr(q2), E, D, circ[1], circ[2], float(step), _ptr(out),
+                                                 _stream())
+        _lib.check(rc, "mpb_edges_count_circular")
+        return out
     rc = _lib.lib().mpb_edges_count(_ptr(q1), _ptr(q2), E, D, float(step), _ptr(out), _stream())
     _lib.check(rc, "mpb_edges_count")
     return out
 
 
-def edges_waypoints(q1, q2, counts=None, step=STEP_SIZE):
+def edges_waypoints(q1, q2, counts=None, step=STEP_SIZE, circular=None):
     """extend_fn(q1[e], q2[e]) for a batch -> (offsets[E+1] int64, waypoints[sum(counts), D])."""
     q1 = _f64(q1, "q1")
     q2 = _f64(q2, "q2", q1.shape[1])
     E, D = q1.shape
     if counts is None:
-        counts = edges_count(q1, q2, step)
+        counts = edges_count(q1, q2, step, circular=circular)
     offsets = torch.zeros(E + 1, dtype=torch.int64, device=q1.device)
     if E:
         offsets[1:] = torch.cumsum(counts.to(torch.int64), 0)
     total = int(offsets[-1].item()) if E else 0
     out = torch.empty((total, D), dtype=torch.float64, device=q1.device)
+    circ = _host_circular(circular, D)
+    if circ is not None:
+        rc = _lib.lib().mpb_edges_waypoints_circular(_ptr(q1), _ptr(q2), E, D, circ[1], circ[2], float(step),
+                                                     _ptr(offsets), _ptr(out), _stream())
+        _lib.check(rc, "mpb_edges_waypoints_circular")
+        return offsets, out
     rc = _lib.lib().mpb_edges_waypoints(_ptr(q1), _ptr(q2), E, D, float(step), _ptr(offsets), _ptr(out), _stream())
     _lib.check(rc, "mpb_edges_waypoints")
     return offsets, out
@@ -207,13 +253,29 @@ class KnnIndex(object):
         return idx, dist
 
 
-def knn(samples, queries, k, weights=None, max_dist=math.inf, method="f32filter", stats=None, metric=METRIC_KDTREE):
+def knn(samples, queries, k, weights=None, max_dist=math.inf, method="f32filter", stats=None, metric=METRIC_KDTREE,
+        circular=None):
     """k nearest stored samples per query, bit-exact to nearest.py:74-85 (see include/mpb200.h).
     method: "f32filter" (tiled fp32 filter + fp64 re-rank) or "f64" (exact brute force).
     metric: METRIC_KDTREE ranks like scipy's cKDTree; METRIC_PRIMITIVES / METRIC_SAMPLERS rank by the
-    value the corresponding distance_fn returns (exact kernel only)."""
+    value the corresponding distance_fn returns (exact kernel only).
+    circular: {coordinate: (lower, upper)}; the three-image metric of nearest.py:7-20 (kd-tree metric, exact
+    kernel)."""
     samples = _f64(samples, "samples")
     queries = _f64(queries, "queries", samples.shape[1])
+    circ = _host_circular(circular, samples.shape[1])
+    if circ is not None:
+        if metric != METRIC_KDTREE:
+            raise ValueError("circular coordinates are defined for the kd-tree metric only (nearest.py:74-85)")
+        N, D = samples.shape
+        M = queries.shape[0]
+        idx = torch.empty((M, k), dtype=torch.int64, device=queries.device)
+        dist = torch.empty((M, k), dtype=torch.float64, device=queries.device)
+        _, wp = _host_weights(weights, D)
+        rc = _lib.lib().mpb_knn_f64_circular(_ptr(samples), N, _ptr(queries), M, D, wp, circ[1], circ[2], int(k),
+                                             float(max_dist), _ptr(idx), _ptr(dist), _stream())
+        _lib.check(rc, "mpb_knn_f64_circular")
+        return idx, dist
     if metric != METRIC_KDTREE:
         N, D = samples.shape
         M = queries.shape[0]

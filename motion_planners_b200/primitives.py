@@ -52,11 +52,13 @@ class GpuCollisionFn(object):
 
 
 class GpuExtendFn(object):
-    """extend_fn(q1, q2) -> waypoints (q1 excluded, last one ~ q2), samplers.py:113-127 with
-    circular = {} and norm = INF: n = int(max|diff/step|) + 1 points of the serial recurrence."""
+    """extend_fn(q1, q2) -> waypoints (q1 excluded, last one ~ q2), samplers.py:113-127 with norm = INF:
+    n = int(max|diff/step|) + 1 points of the serial recurrence.  `circular` = {coordinate: (lower, upper)}
+    switches on the wrapped differences and positions of primitives.py:74-78 / utils.py:364-384."""
 
-    def __init__(self, step_size=STEP_SIZE):
+    def __init__(self, step_size=STEP_SIZE, circular=None):
         self.step_size = float(step_size)
+        self.circular = dict(circular) if circular else {}
 
     def __call__(self, q1, q2):
         _, way = self.batch(np.asarray(q1, dtype=np.float64).reshape(1, -1),
@@ -66,10 +68,16 @@ class GpuExtendFn(object):
 
     def batch(self, q1, q2):
         """-> (offsets [E+1] int64, waypoints [total, D]) CUDA tensors."""
-        return ops.edges_waypoints(_to_dev(q1), _to_dev(q2), step=self.step_size)
+        return ops.edges_waypoints(_to_dev(q1), _to_dev(q2), step=self.step_size, circular=self.circular)
 
     def counts(self, q1, q2):
-        return ops.edges_count(_to_dev(q1), _to_dev(q2), step=self.step_size)
+        return ops.edges_count(_to_dev(q1), _to_dev(q2), step=self.step_size, circular=self.circular)
+
+
+def require_plain_extend(extend_fn, who):
+    """Planners whose batched edge checks are not wired for circular joints say so instead of ignoring them."""
+    if getattr(extend_fn, 'circular', None):
+        raise NotImplementedError('%s: circular joints are supported by lazy_prm and the primitives only' % who)
 
 
 class GpuDistanceFn(object):
@@ -128,11 +136,9 @@ def get_collision_fn(environment, obstacles, buffer=None):
 
 
 def get_extend_fn(circular={}, step_size=STEP_SIZE, norm=INF):
-    if circular:
-        raise NotImplementedError('circular joints are outside the accelerated path (SURVEY.md section 8f, rank 4)')
     if norm != INF:
         raise NotImplementedError('only the reference default norm=INF is accelerated')
-    return GpuExtendFn(step_size)
+    return GpuExtendFn(step_size, circular=circular)
 
 
 def get_distance_fn(weights, p_norm=None):

@@ -21,7 +21,7 @@ import numpy as np
 import torch
 
 from . import ops
-from .primitives import GpuCollisionFn, GpuDistanceFn, GpuExtendFn
+from .primitives import GpuCollisionFn, GpuDistanceFn, GpuExtendFn, require_plain_extend
 from .utils import INF, as_config_array, bisect_order
 
 
@@ -258,6 +258,7 @@ class DegreePRM(object):
 def prm(start, goal, distance_fn, sample_fn, extend_fn, collision_fn, target_degree=4, connect_distance=INF,
         num_samples=100):
     """:return: path [q', ..., q"] or None (prm.py:260-282)."""
+    require_plain_extend(extend_fn, 'prm')
     start = tuple(start)
     goal = tuple(goal)
     samples = [start, goal] + [tuple(sample_fn()) for _ in range(num_samples)]

@@ -26,7 +26,7 @@ import numpy as np
 import torch
 
 from . import ops
-from .primitives import GpuCollisionFn, GpuDistanceFn, GpuExtendFn
+from .primitives import GpuCollisionFn, GpuDistanceFn, GpuExtendFn, require_plain_extend
 from .utils import INF, RRT_ITERATIONS, elapsed_time, first_argmin
 
 
@@ -183,6 +183,7 @@ def rrt_connect_batch(starts, goals, distance_fn, extend_fn, collision_fn, swap_
     targets: [B, iters, D] sampled configurations (query q consumes column i at its iteration i).
     -> list of B paths (lists of numpy configs) or None.  fused=True runs everything in one launch
     (mpb_rrt_connect_batch); fused=False composes the stand-alone kernels iteration by iteration."""
+    require_plain_extend(extend_fn, 'rrt_connect_batch')
     if not _accelerated(distance_fn, extend_fn, collision_fn):
         raise TypeError('rrt_connect_batch needs the accelerated primitives of motion_planners_b200.primitives')
     starts = np.ascontiguousarray(np.asarray(starts, dtype=np.float64))
@@ -266,6 +267,7 @@ def rrt_connect(start, goal, distance_fn, sample_fn, extend_fn, collision_fn, ma
     """:return: path [q', ..., q"] or None (rrt_connect.py:31-72).  Random numbers are drawn from the global
     `random` / numpy generators in the reference's order (one random.random(), then one sample_fn(), per
     iteration), so a seeded run consumes the same streams."""
+    require_plain_extend(extend_fn, 'rrt_connect')
     tree_frequency = kwargs.get('tree_frequency', 1)
     if not _accelerated(distance_fn, extend_fn, collision_fn) or tree_frequency != 1:
         return _rrt_connect_reference_order(start, goal, distance_fn, sample_fn, extend_fn, collision_fn,
@@ -307,6 +309,7 @@ def _regrow(old, s, g, distance_fn, extend_fn, collision_fn, budget):
 
 def birrt(start, goal, distance_fn, sample_fn, extend_fn, collision_fn, **kwargs):
     """:return: path or None (rrt_connect.py:76-93): random restarts of rrt_connect with shortcut smoothing."""
+    require_plain_extend(extend_fn, 'birrt')
     from .meta import random_restarts
     solutions = random_restarts(rrt_connect, start, goal, distance_fn, sample_fn, extend_fn, collision_fn,
                                 max_solutions=1, **kwargs)

@@ -20,7 +20,7 @@ import numpy as np
 import torch
 
 from . import ops
-from .primitives import GpuCollisionFn, GpuDistanceFn, GpuExtendFn
+from .primitives import GpuCollisionFn, GpuDistanceFn, GpuExtendFn, require_plain_extend
 from .utils import INF, elapsed_time, first_argmin
 
 EPSILON = 1e-6          # rrt_star.py:8
@@ -133,6 +133,7 @@ def _rrt_star_reference_order(start, goal, distance_fn, sample_fn, extend_fn, co
 def rrt_star(start, goal, distance_fn, sample_fn, extend_fn, collision_fn, radius, max_time=INF, max_iterations=INF,
              goal_probability=.2, informed=True, verbose=False):
     """:return: path [q', ..., q"] or None (rrt_star.py:86-146)."""
+    require_plain_extend(extend_fn, 'rrt_star')
     if not (isinstance(distance_fn, GpuDistanceFn) and isinstance(extend_fn, GpuExtendFn)
             and isinstance(collision_fn, GpuCollisionFn)):
         return _rrt_star_reference_order(start, goal, distance_fn, sample_fn, extend_fn, collision_fn, radius,

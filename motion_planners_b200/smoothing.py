@@ -14,7 +14,7 @@ from random import choice
 import numpy as np
 
 from . import ops
-from .primitives import GpuCollisionFn, GpuExtendFn
+from .primitives import GpuCollisionFn, GpuExtendFn, require_plain_extend
 from .utils import INF, bisect_order, compute_path_cost, elapsed_time, get_pairs
 
 
@@ -82,6 +82,7 @@ def _bridge_collides(shortcut, extend_fn, collision_fn):
 def smooth_path(path, extend_fn, collision_fn, distance_fn=None, cost_fn=None, sample_fn=None, max_iterations=100,
                 max_time=INF, converge_fraction=0.0, converge_time=INF, print_frequency=1., verbose=False):
     """:return: smoothed, re-discretised path (smoothing.py:51-144)."""
+    require_plain_extend(extend_fn, 'smooth_path')
     start_time = last_time = time.time()
     if not path or not max_iterations:
         return path
@@ -139,6 +140,7 @@ def smooth_paths_batch(paths, extend_fn, collision_fn, distance_fn, seeds, max_i
     of the two drawn segments of every path (extend_fn), the collision verdicts of all chosen points, and the
     verdicts of all bridges.  The per-path bookkeeping (segment draw, cost test, splice) stays on the host.
     Requires the accelerated primitives."""
+    require_plain_extend(extend_fn, 'smooth_paths_batch')
     import random as pyrandom
     import torch
     if not (isinstance(collision_fn, GpuCollisionFn) and isinstance(extend_fn, GpuExtendFn)):

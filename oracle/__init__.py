@@ -38,6 +38,8 @@ def lib():
         _lib.orc_extend.restype = ctypes.c_int64
         _lib.orc_nearest.restype = ctypes.c_int64
         _lib.orc_radius.restype = ctypes.c_int64
+        _lib.orc_extend_circ_count.restype = ctypes.c_int64
+        _lib.orc_extend_circ.restype = ctypes.c_int64
     return _lib
 
 
@@ -91,6 +93,22 @@ class World:
         rc = lib().orc_edges_check(*self._args(), _p(q1, _f64p), _p(q2, _f64p), ctypes.c_int64(E),
                                    ctypes.c_double(step), ctypes.c_int(int(skip_last)), _p(n, _i32p),
                                    _p(first, _i32p), _p(last, _i32p))
+        assert rc == 0
+        return n, first, last
+
+    def edges_check_circular(self, q1, q2, circular, step=1e-2, skip_last=False):
+        """edges_check with circular coordinates ({coordinate: (lower, upper)})."""
+        q1 = _c(q1).reshape(-1, self.dim)
+        q2 = _c(q2).reshape(-1, self.dim)
+        E = q1.shape[0]
+        lo, hi = _circ_arrays(circular, self.dim)
+        n = np.empty(E, np.int32)
+        first = np.empty(E, np.int32)
+        last = np.empty(E, np.int32)
+        rc = lib().orc_edges_check_circ(*self._args(), _p(q1, _f64p), _p(q2, _f64p), ctypes.c_int64(E),
+                                        _p(lo, _f64p), _p(hi, _f64p), ctypes.c_double(step),
+                                        ctypes.c_int(int(skip_last)), _p(n, _i32p), _p(first, _i32p),
+                                        _p(last, _i32p))
         assert rc == 0
         return n, first, last
 
@@ -159,6 +177,48 @@ def extend(q1, q2, step=1e-2):
                            _p(out, _f64p), ctypes.c_int64(n))
     assert got == n
     return out
+
+
+def _circ_arrays(circular, D):
+    """{coordinate: (lower, upper)} -> (lo[D], hi[D]) with (-inf, +inf) where not circular."""
+    lo = np.full(D, -np.inf)
+    hi = np.full(D, np.inf)
+    for d, interval in dict(circular or {}).items():
+        lo[int(d)], hi[int(d)] = float(interval[0]), float(interval[1])
+    return lo, hi
+
+
+def extend_circular(q1, q2, circular, step=1e-2):
+    """Waypoints of get_extend_fn(circular)(q1, q2) (tkinter/samplers.py:113-127 with primitives.py:74-78,
+    utils.py:364-384)."""
+    q1 = _c(q1)
+    q2 = _c(q2)
+    D = q1.shape[0]
+    lo, hi = _circ_arrays(circular, D)
+    n = lib().orc_extend_circ_count(_p(q1, _f64p), _p(q2, _f64p), ctypes.c_int(D), _p(lo, _f64p), _p(hi, _f64p),
+                                    ctypes.c_double(step))
+    out = np.empty((n, D))
+    got = lib().orc_extend_circ(_p(q1, _f64p), _p(q2, _f64p), ctypes.c_int(D), _p(lo, _f64p), _p(hi, _f64p),
+                                ctypes.c_double(step), _p(out, _f64p), ctypes.c_int64(n))
+    assert got == n
+    return out
+
+
+def knn_circular(samples, queries, k, circular, weights=None, max_dist=np.inf):
+    """KDNeighbors(circular=...).query_neighbors for a batch (nearest.py:7-20,74-85), 3^c images spelled out."""
+    samples = _c(samples)
+    queries = _c(queries)
+    N, D = samples.shape
+    M = queries.shape[0]
+    w = np.ones(D) if weights is None else _c(weights)
+    lo, hi = _circ_arrays(circular, D)
+    idx = np.empty((M, k), np.int64)
+    dist = np.empty((M, k), np.float64)
+    rc = lib().orc_knn_circ(_p(samples, _f64p), ctypes.c_int64(N), _p(queries, _f64p), ctypes.c_int64(M),
+                            ctypes.c_int(D), _p(w, _f64p), _p(lo, _f64p), _p(hi, _f64p), ctypes.c_int(k),
+                            ctypes.c_double(max_dist), _p(idx, _i64p), _p(dist, _f64p))
+    assert rc == 0
+    return idx, dist
 
 
 def dist_primitives(q1, q2, w):

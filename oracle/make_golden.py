@@ -399,9 +399,124 @@ def gen_birrt():
               paths=np.concatenate(flat), **_world_arrays(world))
 
 
+# ---------------------------------------------------------------------- circular
+CIRCULAR_CASES = {
+    # name: (D, {coordinate: (lower, upper)}, world name or None)
+    "d3": (3, {0: (0., 1.), 2: (0., 1.)}, "mixed3d"),
+    "d6": (6, {1: (0., 1.), 4: (-0.25, 1.25)}, "boxes6d"),
+    "d7": (7, {0: (0., 1.), 3: (0., 1.), 6: (-np.pi, np.pi)}, None),
+}
+
+
+def gen_circular():
+    """Circular joints: get_extend_fn(circular=...) waypoints (tkinter/samplers.py:113-127 with
+    primitives.py:74-78 and utils.py:364-384), collision flags along them, and
+    KDNeighbors(circular=...).query_neighbors (nearest.py:7-20,74-85)."""
+    from motion_planners.nearest import KDNeighbors
+    from motion_planners.primitives import get_embed_fn
+    from motion_planners.tkinter.samplers import get_collision_fn, get_extend_fn
+    for name, (D, circular, wname) in CIRCULAR_CASES.items():
+        rs = np.random.RandomState(900 + D)
+        lo = np.full(D, -np.inf)
+        hi = np.full(D, np.inf)
+        for d, (a, b) in circular.items():
+            lo[d], hi[d] = a, b
+        span_lo = np.where(np.isfinite(lo), lo, 0.)
+        span_hi = np.where(np.isfinite(hi), hi, 1.)
+        # -- extend (+ collision flags where the case has a world)
+        ext = get_extend_fn(circular=circular)
+        E = 120
+        q1 = span_lo + (span_hi - span_lo) * rs.uniform(size=(E, D))
+        q2 = span_lo + (span_hi - span_lo) * rs.uniform(size=(E, D))
+        short = np.arange(E) % 3 == 0
+        q2[short] = q1[short] + 0.08 * (rs.uniform(size=(short.sum(), D)) - 0.5)   # may leave the interval
+        q2[0] = q1[0]
+        col = None
+        world_arrays = {}
+        if wname is not None:
+            world = WORLDS[wname]()
+            env, obs = _ref_world(world)
+            col = get_collision_fn(env, obs)
+            world_arrays = _world_arrays(world)
+        counts, flat, first, last = [], [], [], []
+        for a, b in zip(q1, q2):
+            pts = np.array(list(ext(a, b)))
+            counts.append(len(pts))
+            flat.append(pts)
+            if col is not None:
+                hits = [i for i, q in enumerate(pts) if col(q)]
+                first.append(hits[0] if hits else -1)
+                last.append(hits[-1] if hits else -1)
+        # -- kNN
+        N, k = 700, 11
+        X = span_lo + (span_hi - span_lo) * rs.uniform(size=(N, D))
+        w = rs.uniform(0.5, 2.0, size=D)
+        nn = KDNeighbors(circular=circular, embed_fn=get_embed_fn(w))
+        nn.add_data(list(X))
+        idx = np.full((N, k), -1, np.int64)
+        dist = np.full((N, k), np.inf)
+        for v, x in enumerate(X):
+            res = nn.query_neighbors(x, k=k, eps=0., p=2, distance_upper_bound=float("inf"))
+            idx[v, :len(res)] = [i for _, i, _ in res]
+            dist[v, :len(res)] = [d for d, _, _ in res]
+        rad = float(np.median(dist[:, 5]))
+        idx_r = np.full((N, k), -1, np.int64)
+        dist_r = np.full((N, k), np.inf)
+        for v, x in enumerate(X[:200]):
+            res = nn.query_neighbors(x, k=k, eps=0., p=2, distance_upper_bound=rad)
+            idx_r[v, :len(res)] = [i for _, i, _ in res]
+            dist_r[v, :len(res)] = [d for d, _, _ in res]
+        _save("circular_%s" % name, circ_lo=lo, circ_hi=hi, q1=q1, q2=q2, counts=np.array(counts, np.int64),
+              waypoints=np.concatenate(flat), first=np.array(first, np.int32), last=np.array(last, np.int32),
+              samples=X, weights=w, k=np.int64(k), idx=idx, dist=dist, radius=np.float64(rad), idx_r=idx_r[:200],
+              dist_r=dist_r[:200], **world_arrays)
+
+
+def gen_lazy_prm_circular():
+    """lazy_prm() with circular joints (lazy_prm.py:253-337 with circular=..., as run.py:254 sketches):
+    wrapped kNN when the roadmap is built, wrapped waypoints when edges are checked."""
+    from motion_planners.lazy_prm import Roadmap, lazy_prm, sample_until
+    from motion_planners.primitives import get_distance_fn as prim
+    from motion_planners.tkinter.samplers import get_collision_fn, get_extend_fn, get_sample_fn
+    runs = [("problem1", {0: (0., 1.), 1: (0., 1.)}, 200, 10, 11, True),
+            ("mixed3d", {0: (0., 1.), 2: (0., 1.)}, 200, 8, 12, False)]
+    for name, circular, num, deg, seed, lazy in runs:
+        world = WORLDS[name]()
+        env, obs = _ref_world(world)
+        col = get_collision_fn(env, obs)
+        ext = get_extend_fn(circular=circular)
+        D = world.dim
+        random.seed(seed)
+        np.random.seed(seed)
+        sample_fn = get_sample_fn(env, obstacles=[], use_halton=False)
+        cfree = get_sample_fn(env, obstacles=obs, use_halton=False)
+        start, goal = cfree(), cfree()
+        w = np.ones(D)
+        rm = Roadmap(ext, weights=w, cost_fn=prim(w), max_degree=deg, circular=circular)
+        with redirect_stdout(io.StringIO()):
+            rm.add_samples([start, goal] + sample_until(sample_fn, num))
+            sol = lazy_prm(start, goal, sample_fn, ext, col, roadmap=rm, num_samples=num, weights=w,
+                           circular=circular, lazy=lazy, verbose=False)
+        lo = np.full(D, -np.inf)
+        hi = np.full(D, np.inf)
+        for d, (a, b) in circular.items():
+            lo[d], hi[d] = a, b
+        path = np.array(sol.path) if sol.path is not None else np.zeros((0, D))
+        cv = np.array(sorted((v, int(f)) for v, f in sol.colliding_vertices.items()), np.int64).reshape(-1, 2)
+        ce = np.array(sorted((a, b, int(f)) for (a, b), f in sol.colliding_edges.items()), np.int64).reshape(-1, 3)
+        cost = sum(prim(w)(a, b) for a, b in zip(path[:-1], path[1:])) if len(path) else np.inf
+        print("  circular %s: solved=%s, %d path points, %d edges" % (name, sol.path is not None, len(path),
+                                                                        len(sol.edges)))
+        _save("lazy_prm_circ_%s_s%d" % (name, seed), start=start, goal=goal, samples=np.array(sol.samples),
+              circ_lo=lo, circ_hi=hi, max_degree=np.int64(deg), lazy=np.bool_(lazy),
+              solved=np.bool_(sol.path is not None), path=path, cost=np.float64(cost),
+              edges=_edge_array(sol.edges), colliding_vertices=cv, colliding_edges=ce, **_world_arrays(world))
+
+
 GENERATORS = {"knn": gen_knn, "extend": gen_extend, "collide": gen_collide, "edges": gen_edges, "dist": gen_dist,
               "lazy_prm": gen_lazy_prm, "prm": gen_prm, "rrt_connect": gen_rrt_connect, "rrt_star": gen_rrt_star,
-              "birrt": gen_birrt}
+              "birrt": gen_birrt, "circular": gen_circular,
+              "lazy_prm_circular": gen_lazy_prm_circular}
 
 
 def main(argv):

@@ -75,3 +75,44 @@ def test_nearest_and_radius_tiebreak():
     assert i == 1                               # first minimum wins (utils.py:61-65)
     idx, dd = oracle.radius(nodes, np.array([0.2, 0.2]), 0.5)
     assert idx.tolist() == [0, 1, 3]
+
+
+def _circ_dict(g):
+    lo, hi = g["circ_lo"], g["circ_hi"]
+    return {d: (float(lo[d]), float(hi[d])) for d in range(len(lo)) if np.isfinite(lo[d])}
+
+
+@pytest.mark.parametrize("name", ["d3", "d6", "d7"])
+def test_circular_extend_matches_reference(golden, name):
+    g = golden("circular_%s" % name)
+    circ = _circ_dict(g)
+    q1, q2, counts, way = g["q1"], g["q2"], g["counts"], g["waypoints"]
+    off = np.concatenate([[0], np.cumsum(counts)])
+    wrapped = 0
+    for e in range(len(q1)):
+        got = oracle.extend_circular(q1[e], q2[e], circ)
+        ref = way[off[e]:off[e + 1]]
+        assert got.shape == ref.shape and (got == ref).all()
+        plain = oracle.extend(q1[e], q2[e])
+        wrapped += int(plain.shape != ref.shape or (plain != ref).any())
+    assert wrapped > len(q1) // 4              # the fixtures do exercise the wrap-around
+    if len(g["first"]):
+        world = world_from_npz(g, oracle.World)
+        n, first, last = world.edges_check_circular(q1, q2, circ)
+        assert (n == counts).all() and (first == g["first"]).all() and (last == g["last"]).all()
+        assert (first >= 0).any() and (first < 0).any()
+
+
+@pytest.mark.parametrize("name", ["d3", "d6", "d7"])
+def test_circular_knn_matches_reference(golden, name):
+    g = golden("circular_%s" % name)
+    circ = _circ_dict(g)
+    X, w, k = g["samples"], g["weights"], int(g["k"])
+    idx, dist = oracle.knn_circular(X, X, k, circ, w)
+    assert (dist == g["dist"]).all()           # bit-exact distances (min over the 3^c images)
+    assert (idx == g["idx"]).all()
+    plain, _ = oracle.knn(X, X, k, w)
+    assert (plain != idx).any()                # the images change the answer on this data
+    nr = g["idx_r"].shape[0]
+    idx_r, dist_r = oracle.knn_circular(X, X[:nr], k, circ, w, max_dist=float(g["radius"]))
+    assert (idx_r == g["idx_r"]).all() and (dist_r == g["dist_r"]).all()
