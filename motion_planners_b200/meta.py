@@ -87,6 +87,10 @@ def solve(start, goal, distance_fn, sample_fn, extend_fn, collision_fn, algorith
         path = lazy_prm(start, goal, sample_fn, extend_fn, collision_fn, num_samples=num_samples, max_time=remaining,
                         weights=weights, circular=circular, distance_fn=distance_fn, cost_fn=cost_fn,
                         verbose=verbose)[0]
+    elif algorithm == 'rrt':
+        from .rrt import rrt
+        path = rrt(start, goal, distance_fn, sample_fn, extend_fn, collision_fn, max_iterations=max_iterations,
+                   max_time=remaining)
     elif algorithm == 'rrt_connect':
         path = rrt_connect(start, goal, distance_fn, sample_fn, extend_fn, collision_fn,
                            max_iterations=max_iterations, max_time=remaining)
@@ -97,7 +101,7 @@ def solve(start, goal, distance_fn, sample_fn, extend_fn, collision_fn, algorith
         path = rrt_star(start, goal, distance_fn, sample_fn, extend_fn, collision_fn, radius=1,
                         max_iterations=max_iterations, max_time=remaining)
     else:
-        raise NotImplementedError(algorithm)     # meta.py:139 (rrt, lattice, lazy_prm_star: out of scope here)
+        raise NotImplementedError(algorithm)     # meta.py:139 (lattice, lazy_prm_star: out of scope here)
     if not smooth:
         return path
     remaining = min(smooth_time, max_time - elapsed_time(start_time))

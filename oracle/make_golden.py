@@ -327,6 +327,48 @@ def gen_rrt_connect():
               paths=np.concatenate(flat), **_world_arrays(world))
 
 
+# --------------------------------------------------------------------------- rrt
+def gen_rrt():
+    """rrt() (rrt.py:49-85), goal-biased single tree, under per-query seeds; one case passes a goal_test."""
+    from motion_planners.rrt import rrt
+    from motion_planners.tkinter.samplers import get_collision_fn, get_distance_fn, get_extend_fn, get_sample_fn
+    ext = get_extend_fn()
+    for name, nq, iters, seed0 in [("problem1", 10, 150, 120), ("boxes7d", 8, 200, 140), ("mixed3d", 8, 150, 160)]:
+        world = WORLDS[name]()
+        env, obs = _ref_world(world)
+        col = get_collision_fn(env, obs)
+        D = world.dim
+        dist = get_distance_fn(np.ones(D))
+        starts, goals, solved, lens, flat, seeds, use_test = [], [], [], [], [], [], []
+        for q in range(nq):
+            seed = seed0 + q
+            random.seed(seed)
+            np.random.seed(seed)
+            cfree = get_sample_fn(env, obstacles=obs, use_halton=False)
+            start, goal = cfree(), cfree()
+            random.seed(seed)
+            np.random.seed(seed)
+            sample_fn = get_sample_fn(env, obstacles=[], use_halton=False)
+            with_test = (q % 3 == 2)
+            goal_test = (lambda c, g=goal: float(np.max(np.abs(np.array(c) - g))) < 0.15) if with_test \
+                else (lambda c: False)
+            path = rrt(start, goal, dist, sample_fn, ext, col, goal_test=goal_test, goal_probability=.2,
+                       max_iterations=iters)
+            starts.append(start)
+            goals.append(goal)
+            seeds.append(seed)
+            use_test.append(with_test)
+            solved.append(path is not None)
+            p = np.array(path) if path is not None else np.zeros((0, D))
+            lens.append(len(p))
+            flat.append(p)
+        print("  rrt %s: solved %d of %d" % (name, sum(solved), nq))
+        _save("rrt_%s" % name, starts=np.array(starts), goals=np.array(goals), seeds=np.array(seeds, np.int64),
+              use_goal_test=np.array(use_test), goal_tolerance=np.float64(0.15), max_iterations=np.int64(iters),
+              solved=np.array(solved), path_len=np.array(lens, np.int64), paths=np.concatenate(flat),
+              **_world_arrays(world))
+
+
 # ---------------------------------------------------------------------- rrt_star
 def gen_rrt_star():
     """rrt_star() as executed on Python 3 (rrt_star.py:86-146; the second rewire loop never
@@ -516,7 +558,7 @@ def gen_lazy_prm_circular():
 GENERATORS = {"knn": gen_knn, "extend": gen_extend, "collide": gen_collide, "edges": gen_edges, "dist": gen_dist,
               "lazy_prm": gen_lazy_prm, "prm": gen_prm, "rrt_connect": gen_rrt_connect, "rrt_star": gen_rrt_star,
               "birrt": gen_birrt, "circular": gen_circular,
-              "lazy_prm_circular": gen_lazy_prm_circular}
+              "lazy_prm_circular": gen_lazy_prm_circular, "rrt": gen_rrt}
 
 
 def main(argv):

@@ -371,3 +371,38 @@ def test_device_roadmap_view_equals_dropin_roadmap(mp, golden, tmp_path):
     # and it is a working Roadmap: a query over it finds a collision-free path
     d, path = loaded.shortest_path(int(np.flatnonzero(~cv)[0]), int(np.flatnonzero(~cv)[-1]))
     assert path is None or not cv[path].any()
+
+
+@pytest.mark.parametrize("name", ["problem1", "boxes7d", "mixed3d"])
+def test_rrt_matches_reference_runs(mp, golden, name):
+    """rrt() (rrt.py:49-85) under the same seeds as the reference run: identical paths, with and without a
+    goal_test, through the accelerated primitives and through plain callables."""
+    import random
+    from motion_planners_b200.rrt import rrt
+    g = golden("rrt_" + name)
+    world = _world(mp, g)
+    dist, ext, col = _tree_primitives(mp, world)
+    env, _ = world.shapes()
+    ref_paths = _paths_from(g)
+    iters = int(g["max_iterations"])
+    tol = float(g["goal_tolerance"])
+    for q in range(len(ref_paths)):
+        seed = int(g["seeds"][q])
+        goal = g["goals"][q]
+        goal_test = (lambda c, gg=goal: float(np.max(np.abs(np.array(c) - gg))) < tol) if g["use_goal_test"][q] \
+            else None
+        for plain in (False, True):
+            if plain and q % 4:
+                continue                      # the callable-by-callable form on every fourth query
+            random.seed(seed)
+            np.random.seed(seed)
+            sample_fn = mp.primitives.get_sample_fn(env, obstacles=[])
+            kw = {} if goal_test is None else {"goal_test": goal_test}
+            prims = (lambda a, b: dist(a, b), sample_fn, lambda a, b: ext(a, b), lambda c: col(c)) if plain \
+                else (dist, sample_fn, ext, col)
+            path = rrt(g["starts"][q], goal, prims[0], prims[1], prims[2], prims[3], goal_probability=.2,
+                       max_iterations=iters, **kw)
+            assert (path is None) == (ref_paths[q] is None)
+            if path is not None:
+                arr = np.array(path)
+                assert arr.shape == ref_paths[q].shape and (arr == ref_paths[q]).all()
