@@ -217,7 +217,7 @@ def measure_rrt_batch(world_size, rank, dist, total_queries=4096, iters=100):
             "kernel_launches": int(state.launches)}
 
 
-def measure_rrt_star(iters=1500):
+def measure_rrt_star(iters=20000):
     """configs[4] as a rate: RRT* in the 3-D world (32 boxes + 8 spheres, radius 0.1); every rank runs its
     own replica (the tree is sequential), so this is a per-GPU figure."""
     import random as pyrandom

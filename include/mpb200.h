@@ -255,6 +255,32 @@ int mpb_scan_nearest_radius(const double *nodes, int64_t n, int dim, const doubl
                             const double *weights, int metric, double radius, int32_t *out_nearest,
                             double *out_dist, int32_t *out_count, int32_t *out_list, void *stream);
 
+/* ---- one RRT* iteration ---------------------------------------------------------------------
+ * The device work of one iteration of rrt_star.py:100-137 (as executed on Python 3) in one call:
+ *   nearest   = first arg-min over nodes [0, n_nodes) of distance_fn(node, sample)        (rrt_star.py:117)
+ *   safe      = len(safe_path(extend_fn(nearest, sample), collision_fn))                  (:118, :76-82)
+ *   new       = waypoint safe-1 of that extension, stored in table[n_nodes] when safe > 0 (:121)
+ *   candidates = every node j in [0, n_nodes] with distance_fn(node_j, new) < radius      (:128, strict)
+ *   per candidate: d = that distance, safe_j = len(safe_path(extend_fn(node_j, new))), and
+ *   ok = safe_j > 0 and distance_fn(new, last safe waypoint) < eps                        (:133-136)
+ * The sequential cost / rewire bookkeeping (:134-137, OptimalNode) stays with the caller.
+ * table dev [capacity, dim] f64 (dim from the world); sample, weights HOST; metric = MPB_METRIC_*;
+ * workspace dev, 256-byte aligned, >= mpb_rrt_star_workspace_bytes(capacity);
+ * out_record HOST (pinned for speed), >= mpb_rrt_star_record_bytes(capacity), written as
+ *   { i32 nearest, first (-1 = none), cnt (waypoints of the extension), safe, n_cand, pad;
+ *     f64 d_near_new; f64 new_cfg[MPB_MAX_DIM]; }                 = MPB_RRTSTAR_HEADER_BYTES
+ *   followed by n_cand records { i32 idx, safe, ok, pad; f64 d; } = MPB_RRTSTAR_CAND_BYTES each,
+ *   in no particular order (sort by idx for the reference's iteration order).
+ * The call synchronises the stream (it returns host data). */
+#define MPB_RRTSTAR_HEADER_BYTES 160
+#define MPB_RRTSTAR_CAND_BYTES 24
+size_t mpb_rrt_star_workspace_bytes(int64_t capacity);
+size_t mpb_rrt_star_record_bytes(int64_t capacity);
+int mpb_rrt_star_step(const mpb_world *world, double *table, int64_t n_nodes, int64_t capacity,
+                      const double *sample, double radius, const double *weights, int metric,
+                      double step, double eps, void *workspace, size_t workspace_bytes,
+                      void *out_record, size_t record_bytes, void *stream);
+
 /* ---- shortest paths over a device-resident roadmap ------------------------------------------
  * The graph search either side of check_path (lazy_prm.py:41-58 dijkstra, :70-98 wastar_search) for the
  * roadmap the entry points above produce: nbr / nbr_dist dev [n_rows, row_len] (kNN output; row r = sample

@@ -7,11 +7,11 @@ extension towards the sample, one new node, and the choose-parent pass over the 
 an already exhausted `filter` object and therefore never runs (rrt_star.py:138-143); it is not
 reproduced.
 
-Device work per iteration: one fused distance scan over all nodes (mpb_scan_nearest_radius: arg-min and
-the ordered radius list share the distances), the first-hit edge check of the extension, and one batched
-first-hit check of every candidate parent -> new edge.  The tree bookkeeping (costs, children, solution
-flags: OptimalNode, rrt_star.py:11-73) is sequential and stays on the host; node configurations live in a
-device array that grows geometrically.
+Device work per iteration: ONE library call (mpb_rrt_star_step: nearest-node scan, the extension's safe
+prefix, the new node, the radius scan and the safe prefix of every candidate parent -> new edge; four launches,
+one small pinned host record back).  The tree bookkeeping (costs, children, solution flags: OptimalNode,
+rrt_star.py:11-73) is sequential and stays on the host; node configurations live in a device array that grows
+geometrically.
 """
 import time
 from random import random
@@ -130,6 +130,64 @@ def _rrt_star_reference_order(start, goal, distance_fn, sample_fn, extend_fn, co
     return goal_n.retrace(lambda p: p or [])
 
 
+class _StepState(object):
+    """Device node table, scratch and the pinned host record of mpb_rrt_star_step; grows geometrically."""
+
+    HEAD = np.dtype([('nearest', '<i4'), ('first', '<i4'), ('cnt', '<i4'), ('safe', '<i4'), ('n_cand', '<i4'),
+                     ('pad', '<i4'), ('d_near_new', '<f8'), ('new_cfg', '<f8', (ops.MAX_DIM,))])
+    CAND = np.dtype([('idx', '<i4'), ('safe', '<i4'), ('ok', '<i4'), ('pad', '<i4'), ('d', '<f8')])
+
+    def __init__(self, obstacles, dim, cap):
+        self.obs, self.D, self.cap = obstacles, dim, 0
+        self.table = None
+        self._alloc(cap)
+
+    def _alloc(self, cap):
+        from . import _lib
+        lib = _lib.lib()
+        dev = torch.device('cuda')
+        table = torch.zeros((cap, self.D), dtype=torch.float64, device=dev)
+        if self.table is not None:
+            table[:self.cap] = self.table
+        self.table, self.cap = table, cap
+        self.ws_bytes = int(lib.mpb_rrt_star_workspace_bytes(cap))
+        self.rec_bytes = int(lib.mpb_rrt_star_record_bytes(cap))
+        self.ws = torch.empty(self.ws_bytes + 256, dtype=torch.uint8, device=dev)
+        self.ws_ptr = (self.ws.data_ptr() + 255) & ~255
+        self.rec = torch.empty(self.rec_bytes, dtype=torch.uint8).pin_memory()
+        self.rec_np = self.rec.numpy()
+        self.head = self.rec_np[:self.HEAD.itemsize].view(self.HEAD)[0]
+        self.cands = self.rec_np[self.HEAD.itemsize:].view(self.CAND)
+
+    def reserve(self, n):
+        if n >= self.cap:
+            self._alloc(2 * self.cap)
+
+    def bind(self, radius, weights, metric, step, eps):
+        """Fix the per-run arguments once: the per-iteration call then only passes the node count."""
+        import ctypes
+        from . import _lib
+        dp = ctypes.POINTER(ctypes.c_double)
+        self._fn = _lib.lib().mpb_rrt_star_step
+        self._check = _lib.check
+        self._sample = np.zeros(self.D, dtype=np.float64)
+        self._weights = np.ascontiguousarray(weights, dtype=np.float64)
+        self._fixed = (self._sample.ctypes.data_as(dp), float(radius), self._weights.ctypes.data_as(dp), int(metric),
+                       float(step), float(eps))
+        self._stream = ops._stream()
+
+    def step(self, n_nodes, sample):
+        self._sample[:] = sample
+        f = self._fixed
+        rc = self._fn(self.obs._h, self.table.data_ptr(), n_nodes, self.cap, f[0], f[1], f[2], f[3], f[4], f[5],
+                      self.ws_ptr, self.ws_bytes, self.rec.data_ptr(), self.rec_bytes, self._stream)
+        if rc:
+            self._check(rc, "mpb_rrt_star_step")
+        head = self.head
+        n_cand = int(head['n_cand']) if head['safe'] > 0 else 0
+        return head, self.cands[:n_cand]
+
+
 def rrt_star(start, goal, distance_fn, sample_fn, extend_fn, collision_fn, radius, max_time=INF, max_iterations=INF,
              goal_probability=.2, informed=True, verbose=False):
     """:return: path [q', ..., q"] or None (rrt_star.py:86-146)."""
@@ -145,18 +203,12 @@ def rrt_star(start, goal, distance_fn, sample_fn, extend_fn, collision_fn, radiu
         return None
     obs = collision_fn.obstacles
     step = extend_fn.step_size
-    dev = torch.device('cuda')
-    cap = 4096
-    table = torch.zeros((cap, D), dtype=torch.float64, device=dev)
-    table[0] = torch.from_numpy(start)
+    state = _StepState(obs, D, 4096)
+    state.table[0] = torch.from_numpy(start)
+    state.bind(radius, distance_fn.weights, distance_fn.metric, step, EPSILON)
     nodes = [OptimalNode(start)]
     goal_n = None
     launches = 0
-
-    def waypoint(frm, to, index):
-        """Waypoint `index` of extend_fn(frm, to) (host copy)."""
-        off, way = extend_fn.batch(frm.reshape(1, -1), to.reshape(1, -1))
-        return way[index].cpu().numpy()
 
     def expand(recipe):
         if not recipe:
@@ -180,66 +232,32 @@ def rrt_star(start, goal, distance_fn, sample_fn, extend_fn, collision_fn, radiu
         iteration += 1
 
         n_nodes = len(nodes)
-        s_dev = torch.from_numpy(s).to(dev)
-        nearest_i, _, _, _ = ops.scan_nearest_radius(table[:n_nodes], s_dev, 0.0, weights=distance_fn.weights,
-                                                     metric=distance_fn.metric)
-        nearest = nodes[int(nearest_i.item())]
-        near_dev = torch.from_numpy(np.asarray(nearest.config, dtype=np.float64)).to(dev).reshape(1, -1)
-        first, cnt = obs.edges_check_pairs(near_dev, s_dev.reshape(1, -1), mode=ops.EDGE_FIRST, step=step)
-        launches += 3
-        first, cnt = int(first.item()), int(cnt.item())
-        safe = cnt if first < 0 else first               # len(safe_path(...)), rrt_star.py:118
+        state.reserve(n_nodes + 1)
+        head, cands = state.step(n_nodes, s)
+        launches += 4
+        safe = int(head['safe'])                          # len(safe_path(...)), rrt_star.py:118
         if safe == 0:
             continue
-        new_config = waypoint(np.asarray(nearest.config, dtype=np.float64), s, safe - 1)
-        new = OptimalNode(new_config, parent=nearest, d=distance_fn(nearest.config, new_config),
+        nearest = nodes[int(head['nearest'])]
+        new_config = np.array(head['new_cfg'][:D])
+        new = OptimalNode(new_config, parent=nearest, d=float(head['d_near_new']),
                           path=(np.asarray(nearest.config, dtype=np.float64), s, safe - 1), iteration=iteration)
         if do_goal and (distance_fn(new.config, goal) < EPSILON):
             goal_n = new
             goal_n.set_solution(True)
-        if n_nodes == cap:                                # grow the device table
-            cap *= 2
-            bigger = torch.zeros((cap, D), dtype=torch.float64, device=dev)
-            bigger[:n_nodes] = table[:n_nodes]
-            table = bigger
-        new_dev = torch.from_numpy(new_config).to(dev)
-        table[n_nodes] = new_dev
         nodes.append(new)
 
-        # choose-parent pass over the nodes strictly closer than `radius` (rrt_star.py:128-137)
-        _, dist, count, lst = ops.scan_nearest_radius(table[:n_nodes + 1], new_dev, radius,
-                                                      weights=distance_fn.weights, metric=distance_fn.metric)
-        c = int(count.item())
-        launches += 2
-        if c == 0:
-            continue
-        cand = lst[:c].long()
-        d_all = dist[cand].cpu().numpy()
-        cand_host = cand.cpu().numpy()
-        q1 = table[cand]
-        q2 = new_dev.reshape(1, -1).expand(c, D).contiguous()
-        first_c, cnt_c = obs.edges_check_pairs(q1, q2, mode=ops.EDGE_FIRST, step=step)
-        first_c, cnt_c = first_c.cpu().numpy(), cnt_c.cpu().numpy()
-        launches += 1
-        for j in range(c):
-            n = nodes[int(cand_host[j])]
-            d = float(d_all[j])
+        # choose-parent pass over the nodes strictly closer than `radius` (rrt_star.py:128-137), index order
+        order = np.argsort(cands['idx'], kind='stable') if len(cands) > 1 else range(len(cands))
+        for j in order:
+            c = cands[j]
+            n = nodes[int(c['idx'])]
+            d = float(c['d'])
             if (n.cost + d) < new.cost:
-                safe_j = int(cnt_c[j]) if first_c[j] < 0 else int(first_c[j])
-                if safe_j == 0:
-                    continue
-                n_cfg = np.asarray(n.config, dtype=np.float64)
-                end = new_config if (first_c[j] < 0 and _ends_on_target(n_cfg, new_config, step)) else \
-                    waypoint(n_cfg, new_config, safe_j - 1)
-                if distance_fn(new.config, end) < EPSILON:
-                    new.rewire(n, d, (n_cfg, new_config, safe_j - 1), iteration=iteration)
+                if c['ok']:
+                    new.rewire(n, d, (np.asarray(n.config, dtype=np.float64), new_config, int(c['safe']) - 1),
+                               iteration=iteration)
     rrt_star.last_launches = launches
     if goal_n is None:
         return None
     return goal_n.retrace(expand)
-
-
-def _ends_on_target(q1, q2, step):
-    """False: always fetch the true last waypoint (the recurrence's final value may differ from q2 by an
-    ulp; the EPSILON test is insensitive to it, but the stored configuration must be the real one)."""
-    return False
