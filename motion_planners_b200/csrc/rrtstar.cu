@@ -39,7 +39,7 @@ struct Partial {
     int32_t i, pad;
 };
 
-const int kInlineCands = 64;   // candidates copied to the host together with the header
+const int kInlineCands = 256;   // candidates copied to the host together with the header
 
 // header + candidate records, rounded up so that the partials behind them stay 16-byte aligned
 inline size_t cand_region_bytes(int64_t capacity)

@@ -207,6 +207,7 @@ def rrt_star(start, goal, distance_fn, sample_fn, extend_fn, collision_fn, radiu
     state.table[0] = torch.from_numpy(start)
     state.bind(radius, distance_fn.weights, distance_fn.metric, step, EPSILON)
     nodes = [OptimalNode(start)]
+    costs = np.zeros(4096)            # costs[i] = nodes[i].cost
     goal_n = None
     launches = 0
 
@@ -247,16 +248,26 @@ def rrt_star(start, goal, distance_fn, sample_fn, extend_fn, collision_fn, radiu
             goal_n.set_solution(True)
         nodes.append(new)
 
-        # choose-parent pass over the nodes strictly closer than `radius` (rrt_star.py:128-137), index order
-        order = np.argsort(cands['idx'], kind='stable') if len(cands) > 1 else range(len(cands))
-        for j in order:
-            c = cands[j]
-            n = nodes[int(c['idx'])]
-            d = float(c['d'])
-            if (n.cost + d) < new.cost:
-                if c['ok']:
-                    new.rewire(n, d, (np.asarray(n.config, dtype=np.float64), new_config, int(c['safe']) - 1),
-                               iteration=iteration)
+        # choose-parent pass over the nodes strictly closer than `radius` (rrt_star.py:128-137), index order.
+        # A node's cost is final once its own pass is over (the reference's second loop, which would rewire
+        # the neighbours, never runs), so `costs` is append-only and the candidates that cannot beat the new
+        # node's first cost -- almost all of them -- are dropped in one vector operation.
+        if n_nodes >= len(costs):
+            costs = np.concatenate([costs, np.empty(len(costs))])
+        costs[n_nodes] = new.cost          # the new node is its own candidate (distance 0): never a parent
+        if len(cands) > 1:
+            idx = cands['idx']
+            keep = np.flatnonzero((cands['ok'] != 0) & (costs[idx] + cands['d'] < new.cost))
+            if len(keep):
+                keep = keep[np.argsort(idx[keep], kind='stable')]
+                for j in keep:
+                    c = cands[j]
+                    n = nodes[int(c['idx'])]
+                    d = float(c['d'])
+                    if (n.cost + d) < new.cost:
+                        new.rewire(n, d, (np.asarray(n.config, dtype=np.float64), new_config, int(c['safe']) - 1),
+                                   iteration=iteration)
+        costs[n_nodes] = new.cost
     rrt_star.last_launches = launches
     if goal_n is None:
         return None
