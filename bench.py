@@ -247,6 +247,30 @@ def measure_rrt_star(iters=20000):
             "kernel_launches": int(getattr(rrt_star, "last_launches", 0))}
 
 
+def measure_prm_c1(num=2000, degree=10):
+    """configs[0], the reference's own CPU-runnable case: prm() on the 2-D demo fixture (3 boxes + 1 disc), 2000
+    collision-free samples, target degree 10, seed 0 (the same draws as tests/golden/prm_problem1_s0.npz).  The
+    reference needs about 33.5 s for this build on one core."""
+    import random as pyrandom
+    from motion_planners_b200 import primitives, workloads
+    from motion_planners_b200.prm import prm
+    world, _, _ = workloads.problem1_world()
+    env, obstacles = world.shapes()
+    col = primitives.GpuCollisionFn(world)
+    ext = primitives.get_extend_fn()
+    dfn = primitives.get_distance_fn(np.ones(world.dim))
+    pyrandom.seed(0)
+    np.random.seed(0)
+    cfree = primitives.get_sample_fn(env, obstacles=obstacles)
+    start, goal = tuple(cfree()), tuple(cfree())
+    t0 = time.perf_counter()
+    path = prm(start, goal, dfn, cfree, ext, col, target_degree=degree, num_samples=num)
+    sec = time.perf_counter() - t0
+    return {"description": "configs[0]: prm() on the 2-D demo fixture, %d c-free samples, target degree %d, "
+                           "sampling included; reference: ~33.5 s on one core (SURVEY.md 8a A3)" % (num, degree),
+            "seconds": sec, "solved": path is not None, "path_points": 0 if path is None else len(path)}
+
+
 # ------------------------------------------------------------------------------------------- main
 def main():
     ap = argparse.ArgumentParser()
@@ -468,6 +492,7 @@ def main():
         line["extra_c3_rrt_connect_batch"] = measure_rrt_batch(world_size, rank, dist if world_size > 1 else None)
         if rank == 0:
             line["extra_c5_rrt_star"] = measure_rrt_star()
+            line["extra_c1_prm"] = measure_prm_c1()
 
     if rank == 0:
         print(json.dumps(line))

@@ -436,3 +436,56 @@ def lazy_prm(start, goal, sample_fn, extend_fn, collision_fn, distance_fn=None, 
     roadmap._prefetch_paths(get_pairs(path)) if isinstance(extend_fn, GpuExtendFn) else None
     solution = [start] + flatten(roadmap.get_path(v1, v2) for v1, v2 in get_pairs(path))
     return Solution(solution, samples, edges, roadmap.colliding_vertices, roadmap.colliding_edges)
+
+
+def create_param_sequence(initial_samples=100, step_samples=100, **kwargs):
+    """lazy_prm.py:340-344: the endless schedule num_samples = initial, initial + step, ..."""
+    num_samples = initial_samples
+    while True:
+        params = dict(kwargs)
+        params['num_samples'] = num_samples
+        yield params
+        num_samples += step_samples
+
+
+def lazy_prm_star(start, goal, sample_fn, extend_fn, collision_fn, distance_fn=None, cost_fn=None, max_cost=INF,
+                  success_cost=INF, param_sequence=None, resuse=True, weights=None, circular={}, p_norm=2,
+                  max_time=INF, verbose=False, **kwargs):
+    """:return: the cheapest path found, or None (lazy_prm.py:346-389): lazy_prm on a roadmap that is augmented
+    round after round along `param_sequence`, each round bounded by the best cost so far.  (The keyword really
+    is spelled `resuse` in the reference.)"""
+    start_time = time.time()
+    weights, distance_fn, cost_fn = get_metrics(start, weights=weights, p_norm=p_norm, distance_fn=distance_fn,
+                                                cost_fn=cost_fn)
+    if param_sequence is None:
+        param_sequence = create_param_sequence()
+    roadmap = None
+    best_path = None
+    best_cost = max_cost
+    for i, params in enumerate(param_sequence):
+        remaining_time = max_time - elapsed_time(start_time)
+        if remaining_time <= 0.:
+            break
+        if verbose:
+            print('\nIteration: {} | Cost: {:.3f} | Elapsed: {:.3f} | Remaining: {:.3f} | Params: {}'.format(
+                i, best_cost, elapsed_time(start_time), remaining_time, params))
+        if (roadmap is None) or not resuse:
+            roadmap = Roadmap(extend_fn, weights=weights, distance_fn=distance_fn, cost_fn=cost_fn, circular=circular)
+            roadmap.add_samples([start, goal] + sample_until(sample_fn, params['num_samples']))
+        call = dict(kwargs)
+        call.update(params)
+        new_path = lazy_prm(start, goal, sample_fn, extend_fn, collision_fn, roadmap=roadmap, cost_fn=cost_fn,
+                            weights=weights, circular=circular, p_norm=p_norm, max_time=remaining_time,
+                            max_cost=best_cost, verbose=verbose, **call)[0]
+        new_cost = compute_path_cost(new_path, cost_fn=cost_fn)
+        if verbose:
+            print('Path: {} | Cost: {:.3f} | Length: {}'.format(new_path is not None, new_cost,
+                                                                INF if new_path is None else len(new_path)))
+        if new_cost < best_cost:
+            best_path = new_path
+            best_cost = new_cost
+        if best_cost < success_cost:
+            break
+    if roadmap is not None:
+        ROADMAPS.append(roadmap)
+    return best_path

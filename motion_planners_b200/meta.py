@@ -87,6 +87,14 @@ def solve(start, goal, distance_fn, sample_fn, extend_fn, collision_fn, algorith
         path = lazy_prm(start, goal, sample_fn, extend_fn, collision_fn, num_samples=num_samples, max_time=remaining,
                         weights=weights, circular=circular, distance_fn=distance_fn, cost_fn=cost_fn,
                         verbose=verbose)[0]
+    elif algorithm == 'lazy_prm_star':
+        from .lazy_prm import create_param_sequence, lazy_prm_star
+        if weights is not None:
+            distance_fn = None
+        path = lazy_prm_star(start, goal, sample_fn, extend_fn, collision_fn,
+                             param_sequence=create_param_sequence(initial_samples=num_samples), max_time=remaining,
+                             weights=weights, circular=circular, distance_fn=distance_fn, cost_fn=cost_fn,
+                             success_cost=success_cost, verbose=verbose)
     elif algorithm == 'rrt':
         from .rrt import rrt
         path = rrt(start, goal, distance_fn, sample_fn, extend_fn, collision_fn, max_iterations=max_iterations,
@@ -101,7 +109,7 @@ def solve(start, goal, distance_fn, sample_fn, extend_fn, collision_fn, algorith
         path = rrt_star(start, goal, distance_fn, sample_fn, extend_fn, collision_fn, radius=1,
                         max_iterations=max_iterations, max_time=remaining)
     else:
-        raise NotImplementedError(algorithm)     # meta.py:139 (lattice, lazy_prm_star: out of scope here)
+        raise NotImplementedError(algorithm)     # meta.py:139 (lattice: out of scope here)
     if not smooth:
         return path
     remaining = min(smooth_time, max_time - elapsed_time(start_time))

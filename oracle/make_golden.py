@@ -21,6 +21,7 @@ import numpy as np
 
 from . import ref_loader
 
+INF_ = float("inf")
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 sys.path.insert(0, ROOT)
@@ -555,10 +556,47 @@ def gen_lazy_prm_circular():
               edges=_edge_array(sol.edges), colliding_vertices=cv, colliding_edges=ce, **_world_arrays(world))
 
 
+def gen_lazy_prm_star():
+    """lazy_prm_star() (lazy_prm.py:346-389): rounds of lazy_prm on a growing roadmap, here along a finite
+    param_sequence (so the run ends without a wall-clock limit) and with success_cost = 0 (every round runs).
+    Stores every sample the run drew, in order, so the port can replay the stream."""
+    from motion_planners.lazy_prm import lazy_prm_star
+    from motion_planners.primitives import get_distance_fn as prim
+    from motion_planners.tkinter.samplers import get_collision_fn, get_extend_fn, get_sample_fn
+    ext = get_extend_fn()
+    for name, rounds, seed in [("problem1", [6, 40, 120], 31), ("mixed3d", [10, 60, 150, 260], 32)]:
+        world = WORLDS[name]()
+        env, obs = _ref_world(world)
+        col = get_collision_fn(env, obs)
+        D = world.dim
+        random.seed(seed)
+        np.random.seed(seed)
+        cfree = get_sample_fn(env, obstacles=obs, use_halton=False)
+        start, goal = cfree(), cfree()
+        inner = get_sample_fn(env, obstacles=[], use_halton=False)
+        drawn = []
+
+        def sample_fn():
+            q = inner()
+            drawn.append(np.array(q))
+            return q
+        w = np.ones(D)
+        with redirect_stdout(io.StringIO()):
+            path = lazy_prm_star(start, goal, sample_fn, ext, col, weights=w, success_cost=0.,
+                                 param_sequence=[{'num_samples': n} for n in rounds], verbose=False)
+        p = np.array(path) if path is not None else np.zeros((0, D))
+        cost = sum(prim(w)(a, b) for a, b in zip(p[:-1], p[1:])) if len(p) else np.inf
+        print("  lazy_prm_star %s: %d draws, solved=%s, cost %.4f" % (name, len(drawn), path is not None, cost))
+        _save("lazy_prm_star_%s_s%d" % (name, seed), start=start, goal=goal, draws=np.array(drawn),
+              rounds=np.array(rounds, np.int64), solved=np.bool_(path is not None), path=p, cost=np.float64(cost),
+              **_world_arrays(world))
+
+
 GENERATORS = {"knn": gen_knn, "extend": gen_extend, "collide": gen_collide, "edges": gen_edges, "dist": gen_dist,
               "lazy_prm": gen_lazy_prm, "prm": gen_prm, "rrt_connect": gen_rrt_connect, "rrt_star": gen_rrt_star,
               "birrt": gen_birrt, "circular": gen_circular,
-              "lazy_prm_circular": gen_lazy_prm_circular, "rrt": gen_rrt}
+              "lazy_prm_circular": gen_lazy_prm_circular, "rrt": gen_rrt,
+              "lazy_prm_star": gen_lazy_prm_star}
 
 
 def main(argv):

@@ -406,3 +406,31 @@ def test_rrt_matches_reference_runs(mp, golden, name):
             if path is not None:
                 arr = np.array(path)
                 assert arr.shape == ref_paths[q].shape and (arr == ref_paths[q]).all()
+
+
+@pytest.mark.parametrize("name", ["lazy_prm_star_problem1_s31", "lazy_prm_star_mixed3d_s32"])
+def test_lazy_prm_star_matches_reference_run(mp, golden, name):
+    """lazy_prm_star() (lazy_prm.py:346-389) over a finite parameter schedule: same draws consumed, same path."""
+    g = golden(name)
+    world = _world(mp, g)
+    D = world.dim
+    w = np.ones(D)
+    ext = mp.primitives.get_extend_fn()
+    col = mp.primitives.GpuCollisionFn(world)
+    draws = iter([np.array(r) for r in g["draws"]])
+    used = [0]
+
+    def sample_fn():
+        used[0] += 1
+        return next(draws)
+
+    path = mp.lazy_prm.lazy_prm_star(g["start"], g["goal"], sample_fn, ext, col, weights=w, success_cost=0.,
+                                     param_sequence=[{'num_samples': int(n)} for n in g["rounds"]], verbose=False)
+    assert used[0] == len(g["draws"])
+    assert (path is not None) == bool(g["solved"])
+    if path is not None:
+        arr = np.array(path)
+        assert arr.shape == g["path"].shape and (arr == g["path"]).all()
+        cost_fn = mp.primitives.get_distance_fn(w, p_norm=2)
+        cost = sum(cost_fn(a, b) for a, b in zip(arr[:-1], arr[1:]))
+        assert abs(cost - float(g["cost"])) <= 1e-9 * float(g["cost"])
