@@ -59,6 +59,7 @@ constexpr int kBlocksPerSM = 16 / MPB_KNN_WARPS;   // 16 warps of 128 registers 
 constexpr int64_t kShortScanMax = MPB_KNN_SHORT_MAX;
 constexpr int kStages = MPB_KNN_STAGES;   // shared-memory ring depth
 constexpr int kSmallListMaxK = 12; // k up to which 16 survivors per query are kept (else 32)
+constexpr int kFilterMaxK = 28;    // beyond this the 32-entry lists cannot certify anything: exact scan directly
 constexpr int kHeaderBytes = 512;
 
 struct KnnHeader {
@@ -704,6 +705,18 @@ int launch_search(const double *x, int64_t N, const double *qs, int64_t M, const
     KnnHeader *h = reinterpret_cast<KnnHeader *>(ws);
     const float4 *packed = reinterpret_cast<const float4 *>(reinterpret_cast<char *>(ws) + L.packed_off);
     int *fb = reinterpret_cast<int *>(reinterpret_cast<char *>(ws) + L.fb_off);
+    if (k > kFilterMaxK) {
+        // A 32-entry survivor list has no slack left to certify more than kFilterMaxK neighbours (measured: every
+        // query of a k = 32 search fell through to the exact scan after paying for the filter pass): scan exactly.
+        int rc0 = launch_exact<D>(x, N, qs, M, wt, MPB_METRIC_KDTREE, k, r2, nullptr, nullptr, out_idx, out_dist,
+                                  nullptr, st);
+        if (rc0 != MPB_OK) return rc0;
+        if (stats) {
+            const int64_t all = M;
+            MPB_CUDA_CHECK(cudaMemcpyAsync(stats, &all, sizeof(all), cudaMemcpyHostToDevice, st));
+        }
+        return MPB_OK;
+    }
     MPB_CUDA_CHECK(cudaMemsetAsync(&h->fb_count, 0, sizeof(int), st));
     // 16 survivors per query leave a comfortable certificate margin up to k = 12 (a PRM's k + 1 = 11) and
     // halve the insertion work; larger k keeps 32
