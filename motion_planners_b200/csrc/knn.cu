@@ -587,25 +587,54 @@ __global__ void __launch_bounds__(kWarps * 32, kBlocksPerSM)
     }
 }
 
+#include "knn_tc.cuh"
+
 // ------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------
+// The tensor-core scan (knn_tc.cuh) is an opt-in alternative for sample sets of up to seven dimensions: set
+// MPB200_KNN_TC=1 in the environment before the library is first used.  It is bit-exact like the default path but
+// slower on B200 (341 vs 245 ms at 1M x 7-DoF): every key has to be read out of tensor memory, and that read-out
+// runs at about 64 bytes per clock per SM.  It stays in the tree, tested, for hardware with a fused min on that
+// read-out.
+constexpr int64_t kTcMinSamples = 8192;
+
+bool tc_enabled()
+{
+    static const bool on = [] {
+        const char *e = getenv("MPB200_KNN_TC");
+        return e && e[0] == '1';
+    }();
+    return on;
+}
+
+bool use_tc(int64_t N, int D) { return tc_enabled() && D <= kTcMaxDim && N >= kTcMinSamples; }
+
 struct WsLayout {
-    size_t packed_off, packed_bytes, fb_off, fb_bytes, total;
-    int64_t n_tiles, n_pad;
+    size_t packed_off, packed_bytes, tc_off, tc_bytes, fb_off, fb_bytes, surv_off, surv_bytes, thr_off, thr_bytes, total;
+    int64_t n_tiles, n_pad, tc_tiles;
 };
 
-WsLayout ws_layout(int64_t N, int64_t M, int D)
+WsLayout ws_layout(int64_t N, int64_t M, int D, bool allow_tc = true)
 {
     WsLayout L;
     const int P = planes_for(D), TILE = tile_for(D);
+    const bool tc = allow_tc && use_tc(N, D);
+    const size_t m = (size_t)(M > 0 ? M : 1);
     L.n_tiles = (N + TILE - 1) / TILE;
     L.n_pad = L.n_tiles * TILE;
     L.packed_off = kHeaderBytes;
     L.packed_bytes = (size_t)L.n_pad * P * 16;
-    L.fb_off = (L.packed_off + L.packed_bytes + 255) & ~(size_t)255;
-    L.fb_bytes = ((size_t)(M > 0 ? M : 1) * sizeof(int) + 255) & ~(size_t)255;
-    L.total = L.fb_off + L.fb_bytes;
+    L.tc_tiles = tc ? (N + kTcTile - 1) / kTcTile : 0;
+    L.tc_off = (L.packed_off + L.packed_bytes + 1023) & ~(size_t)1023;
+    L.tc_bytes = (size_t)L.tc_tiles * kTcTileBytes;
+    L.fb_off = (L.tc_off + L.tc_bytes + 255) & ~(size_t)255;
+    L.fb_bytes = (m * sizeof(int) + 255) & ~(size_t)255;
+    L.surv_off = L.fb_off + L.fb_bytes;
+    L.surv_bytes = tc ? ((m * kTcSurvivors * sizeof(int) + 255) & ~(size_t)255) : 0;
+    L.thr_off = L.surv_off + L.surv_bytes;
+    L.thr_bytes = tc ? ((m * kTcParts * sizeof(float) + 255) & ~(size_t)255) : 0;
+    L.total = L.thr_off + L.thr_bytes;
     return L;
 }
 
@@ -644,9 +673,9 @@ int launch_exact(const double *x, int64_t N, const double *qs, int64_t M, const 
 }
 
 template <int D>
-int launch_prepare(const double *x, int64_t N, const Weights &wt, void *ws, cudaStream_t st)
+int launch_prepare(const double *x, int64_t N, const Weights &wt, void *ws, bool allow_tc, cudaStream_t st)
 {
-    const WsLayout L = ws_layout(N, 0, D);
+    const WsLayout L = ws_layout(N, 0, D, allow_tc);
     KnnHeader *h = reinterpret_cast<KnnHeader *>(ws);
     float4 *packed = reinterpret_cast<float4 *>(reinterpret_cast<char *>(ws) + L.packed_off);
     knn_init_kernel<<<1, 32, 0, st>>>(h);
@@ -662,6 +691,14 @@ int launch_prepare(const double *x, int64_t N, const Weights &wt, void *ws, cuda
     if (L.n_pad > 0) {
         knn_pack_kernel<D><<<(unsigned)((L.n_pad + 255) / 256), 256, 0, st>>>(x, N, L.n_pad, wt, h, packed);
         MPB_LAUNCH_CHECK();
+    }
+    if constexpr (D <= kTcMaxDim) {
+        if (L.tc_tiles > 0) {
+            unsigned char *tiles = reinterpret_cast<unsigned char *>(ws) + L.tc_off;
+            const int64_t npad = L.tc_tiles * kTcTile;
+            knn_tc_pack_kernel<D><<<(unsigned)((npad + 255) / 256), 256, 0, st>>>(x, N, npad, wt, h, tiles);
+            MPB_LAUNCH_CHECK();
+        }
     }
     return MPB_OK;
 }
@@ -695,13 +732,13 @@ int launch_filter(const double *x, int64_t N, const double *qs, int64_t M, const
 
 template <int D>
 int launch_search(const double *x, int64_t N, const double *qs, int64_t M, const Weights &wt, int k, double r2,
-                  void *ws, int64_t *out_idx, double *out_dist, int64_t *stats, cudaStream_t st)
+                  void *ws, bool allow_tc, int64_t *out_idx, double *out_dist, int64_t *stats, cudaStream_t st)
 {
 #ifndef MPB_KNN_Q
 #define MPB_KNN_Q 8
 #endif
     constexpr int Q = (D <= 8) ? MPB_KNN_Q : 4;
-    const WsLayout L = ws_layout(N, M, D);
+    const WsLayout L = ws_layout(N, M, D, allow_tc);
     KnnHeader *h = reinterpret_cast<KnnHeader *>(ws);
     const float4 *packed = reinterpret_cast<const float4 *>(reinterpret_cast<char *>(ws) + L.packed_off);
     int *fb = reinterpret_cast<int *>(reinterpret_cast<char *>(ws) + L.fb_off);
@@ -718,6 +755,26 @@ int launch_search(const double *x, int64_t N, const double *qs, int64_t M, const
         return MPB_OK;
     }
     MPB_CUDA_CHECK(cudaMemsetAsync(&h->fb_count, 0, sizeof(int), st));
+    if constexpr (D <= kTcMaxDim) {
+        if (L.tc_tiles > 0 && k <= kSmallListMaxK) {
+            // tensor-core scan -> 4 x 16 survivors per query -> exact re-rank + certificate -> exact re-do of the rest
+            char *base = reinterpret_cast<char *>(ws);
+            const unsigned char *tiles = reinterpret_cast<const unsigned char *>(base + L.tc_off);
+            int *surv = reinterpret_cast<int *>(base + L.surv_off);
+            float *sthr = reinterpret_cast<float *>(base + L.thr_off);
+            MPB_CUDA_CHECK(cudaFuncSetAttribute(knn_tc_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                (int)TcSmem::BYTES));
+            const int64_t ctas = (M + kTcQueries - 1) / kTcQueries;
+            knn_tc_kernel<D><<<(unsigned)ctas, kTcThreads, TcSmem::BYTES, st>>>(qs, M, wt, tiles, (int)L.tc_tiles, h, surv, sthr);
+            MPB_LAUNCH_CHECK();
+            const int64_t rthreads = M * 32;
+            knn_tc_rerank_kernel<D><<<(unsigned)((rthreads + 255) / 256), 256, 0, st>>>(x, N, qs, M, wt, k, r2, h, surv,
+                                                                                        sthr, fb, out_idx, out_dist);
+            MPB_LAUNCH_CHECK();
+            return launch_exact<D>(x, N, qs, M, wt, MPB_METRIC_KDTREE, k, r2, fb, &h->fb_count, out_idx, out_dist, stats,
+                                   st);
+        }
+    }
     // 16 survivors per query leave a comfortable certificate margin up to k = 12 (a PRM's k + 1 = 11) and
     // halve the insertion work; larger k keeps 32
     int rc = (k <= kSmallListMaxK)
@@ -735,17 +792,17 @@ int dispatch_exact(int D, const double *x, int64_t N, const double *qs, int64_t 
 #undef CALL
     return MPB_EINVAL;
 }
-int dispatch_prepare(int D, const double *x, int64_t N, const Weights &wt, void *ws, cudaStream_t st)
+int dispatch_prepare(int D, const double *x, int64_t N, const Weights &wt, void *ws, bool allow_tc, cudaStream_t st)
 {
-#define CALL(DD) launch_prepare<DD>(x, N, wt, ws, st)
+#define CALL(DD) launch_prepare<DD>(x, N, wt, ws, allow_tc, st)
     MPB_DISPATCH_DIM(D, CALL)
 #undef CALL
     return MPB_EINVAL;
 }
 int dispatch_search(int D, const double *x, int64_t N, const double *qs, int64_t M, const Weights &wt, int k, double r2,
-                    void *ws, int64_t *out_idx, double *out_dist, int64_t *stats, cudaStream_t st)
+                    void *ws, bool allow_tc, int64_t *out_idx, double *out_dist, int64_t *stats, cudaStream_t st)
 {
-#define CALL(DD) launch_search<DD>(x, N, qs, M, wt, k, r2, ws, out_idx, out_dist, stats, st)
+#define CALL(DD) launch_search<DD>(x, N, qs, M, wt, k, r2, ws, allow_tc, out_idx, out_dist, stats, st)
     MPB_DISPATCH_DIM(D, CALL)
 #undef CALL
     return MPB_EINVAL;
@@ -785,11 +842,11 @@ MPB_API size_t mpb_knn_workspace_bytes(int64_t n_samples, int64_t n_queries, int
     return ws_layout(n_samples, n_queries, dim).total;
 }
 
-static int check_ws(const char *who, void *ws, size_t ws_bytes, int64_t N, int64_t M, int D)
+static int check_ws(const char *who, void *ws, size_t ws_bytes, int64_t N, int64_t M, int D, bool allow_tc = true)
 {
     MPB_REQUIRE(ws != nullptr, "%s: workspace is NULL", who);
     MPB_REQUIRE(((uintptr_t)ws & 255) == 0, "%s: workspace must be 256-byte aligned", who);
-    const size_t need = ws_layout(N, M, D).total;
+    const size_t need = ws_layout(N, M, D, allow_tc).total;
     if (ws_bytes < need) {
         mpb_set_error("%s: workspace of %zu bytes is smaller than the %zu required", who, ws_bytes, need);
         return MPB_ENOMEM;
@@ -805,7 +862,7 @@ MPB_API int mpb_knn_prepare(const double *samples, int64_t n_samples, int dim, c
     MPB_REQUIRE(n_samples == 0 || samples, "mpb_knn_prepare: NULL sample buffer");
     int rc = check_ws("mpb_knn_prepare", workspace, workspace_bytes, n_samples, 0, dim);
     if (rc != MPB_OK) return rc;
-    return dispatch_prepare(dim, samples, n_samples, make_weights(weights, dim), workspace, (cudaStream_t)stream);
+    return dispatch_prepare(dim, samples, n_samples, make_weights(weights, dim), workspace, true, (cudaStream_t)stream);
 }
 
 MPB_API int mpb_knn_search(const double *samples, int64_t n_samples, const double *queries, int64_t n_queries, int dim,
@@ -819,21 +876,35 @@ MPB_API int mpb_knn_search(const double *samples, int64_t n_samples, const doubl
     if (rc != MPB_OK) return rc;
     if (n_queries == 0) return MPB_OK;
     return dispatch_search(dim, samples, n_samples, queries, n_queries, make_weights(weights, dim), k,
-                           max_dist * max_dist, workspace, out_idx, out_dist, stats, (cudaStream_t)stream);
+                           max_dist * max_dist, workspace, true, out_idx, out_dist, stats, (cudaStream_t)stream);
+}
+
+// prepare + search on one workspace; `allow_tc` = the workspace was sized with room for the tensor-core tiles
+static int filter_on_workspace(const char *who, const double *samples, int64_t n_samples, const double *queries,
+                               int64_t n_queries, int dim, const double *weights, int k, double max_dist,
+                               void *workspace, size_t workspace_bytes, bool allow_tc, int64_t *out_idx,
+                               double *out_dist, int64_t *stats, void *stream)
+{
+    int rc = check_common(who, samples, n_samples, queries, n_queries, dim, k, out_idx);
+    if (rc != MPB_OK) return rc;
+    MPB_REQUIRE(max_dist >= 0., "%s: max_dist must be >= 0", who);
+    MPB_REQUIRE(n_samples < 2147483647LL, "%s: bad sample count", who);
+    rc = check_ws(who, workspace, workspace_bytes, n_samples, n_queries, dim, allow_tc);
+    if (rc != MPB_OK) return rc;
+    const Weights wt = make_weights(weights, dim);
+    rc = dispatch_prepare(dim, samples, n_samples, wt, workspace, allow_tc, (cudaStream_t)stream);
+    if (rc != MPB_OK) return rc;
+    if (n_queries == 0) return MPB_OK;
+    return dispatch_search(dim, samples, n_samples, queries, n_queries, wt, k, max_dist * max_dist, workspace, allow_tc,
+                           out_idx, out_dist, stats, (cudaStream_t)stream);
 }
 
 MPB_API int mpb_knn_f32filter(const double *samples, int64_t n_samples, const double *queries, int64_t n_queries,
                               int dim, const double *weights, int k, double max_dist, void *workspace,
                               size_t workspace_bytes, int64_t *out_idx, double *out_dist, int64_t *stats, void *stream)
 {
-    int rc = check_common("mpb_knn_f32filter", samples, n_samples, queries, n_queries, dim, k, out_idx);
-    if (rc != MPB_OK) return rc;
-    rc = check_ws("mpb_knn_f32filter", workspace, workspace_bytes, n_samples, n_queries, dim);
-    if (rc != MPB_OK) return rc;
-    rc = mpb_knn_prepare(samples, n_samples, dim, weights, workspace, workspace_bytes, stream);
-    if (rc != MPB_OK) return rc;
-    return mpb_knn_search(samples, n_samples, queries, n_queries, dim, weights, k, max_dist, workspace, workspace_bytes,
-                          out_idx, out_dist, stats, stream);
+    return filter_on_workspace("mpb_knn_f32filter", samples, n_samples, queries, n_queries, dim, weights, k, max_dist,
+                               workspace, workspace_bytes, true, out_idx, out_dist, stats, stream);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -861,7 +932,8 @@ MPB_API int mpb_knn_f32filter_static(const double *samples, int64_t n_samples, c
     int rc = check_common("mpb_knn_f32filter_static", samples, n_samples, queries, n_queries, dim, k, out_idx);
     if (rc != MPB_OK) return rc;
     MPB_REQUIRE(max_dist >= 0., "mpb_knn_f32filter_static: max_dist must be >= 0");
-    const size_t need = ws_layout(n_samples, n_queries, dim).total;
+    // sized without the tensor-core tiles (96 bytes per sample would not leave room for much in this array)
+    const size_t need = ws_layout(n_samples, n_queries, dim, false).total;
     if (need > (size_t)MPB_KNN_STATIC_BYTES) {
         mpb_set_error("mpb_knn_f32filter_static: %lld samples x %lld queries at dim %d need %zu bytes of scratch, "
                       "the built-in array holds %zu; use mpb_knn_f32filter with a caller-owned workspace",
@@ -884,6 +956,6 @@ MPB_API int mpb_knn_f32filter_static(const double *samples, int64_t n_samples, c
     }
     // prepare re-initialises the header (bounding box, fallback counter) and rewrites every tile slot it
     // will read, so nothing left behind by an earlier call is ever consumed
-    return mpb_knn_f32filter(samples, n_samples, queries, n_queries, dim, weights, k, max_dist, scratch,
-                             (size_t)MPB_KNN_STATIC_BYTES, out_idx, out_dist, stats, stream);
+    return filter_on_workspace("mpb_knn_f32filter_static", samples, n_samples, queries, n_queries, dim, weights, k,
+                               max_dist, scratch, (size_t)MPB_KNN_STATIC_BYTES, false, out_idx, out_dist, stats, stream);
 }
