@@ -446,10 +446,39 @@ def main():
         "fp64_fma_peak_tflops": fp64_peak / 1e12,
     }
 
+    from motion_planners_b200 import _lib as _mplib
+    if _mplib.lib().mpb_knn_filter_kind(int(n), int(D), int(k) + 1) == 1:
+        # The kNN ran on the tensor-core scan: three tcgen05.mma kind::tf32 k-steps (K = 24 operand columns: every
+        # fp32 value enters as two TF32 parts) per 128-query x 256-candidate tile.  Executed tensor flops per
+        # (query, sample) pair = 2 * 24.  Peak: MEASURED_PEAKS.json has the dense bf16 rate (sustained figure: the
+        # kernel is timed inside a long step); TF32 runs at half of it.
+        tc_flops = 2.0 * 24 * float(m["n_local"]) * n
+        bf16_peak = peaks_file.get("bf16_tflops_sustained") or peaks_file.get("bf16_tflops")
+        tf32_peak = (bf16_peak / 2.0) if bf16_peak else 1130.0
+        tc_achieved = tc_flops / (knn_ms * 1e-3) / 1e12
+        fp32_view = dict(roofline)
+        for key in ("kernel", "bound", "traffic", "hbm", "kernel_ms"):
+            fp32_view.pop(key, None)
+        roofline = {
+            "kernel": "knn_tc_kernel", "bound": "tensor", "achieved": tc_achieved, "peak": tf32_peak,
+            "unit": "TFLOP/s", "frac": tc_achieved / tf32_peak,
+            "peak_source": ("MEASURED_PEAKS.json bf16_tflops_sustained / 2 (TF32 is half the bf16 rate)" if bf16_peak
+                            else "fallback: nominal dense TF32, 1130 TFLOP/s"),
+            "flops_per_pair": 48, "survey_flops_per_pair": 3 * D,
+            "note": "the MMAs occupy about a quarter of the kernel; what bounds it is the CUDA-core epilogue that "
+                    "reads every key out of tensor memory (tcgen05.ld), takes a min-tree per 32 keys and inserts the "
+                    "takers (profiles/r1_summary.md, r1h)",
+            "traffic": None, "kernel_ms": knn_ms, "hbm": roofline["hbm"],
+            # the same time expressed on the fp32 formulation's count (2*D flop per pair) against the FFMA2 peak:
+            # above 1 means faster than a perfect FFMA2 kernel could be
+            "as_fp32_filter": fp32_view,
+        }
+
     line = {
         "metric": METRIC, "value": m["value"], "unit": UNIT, "n_gpus": world_size, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": m["ms_step"], "higher_is_better": True, "scaling": "strong",
-        "vs_baseline": None, "dtype": "f64 (fp32 filter pass inside the kNN, results bit-exact to the fp64 reference)",
+        "vs_baseline": None,
+        "dtype": "f64 (fp32 / split-TF32 filter pass inside the kNN, results bit-exact to the fp64 reference)",
         "data": "synthetic", "knn_queries_per_s": m["qps"],
         "config": {"workload": args.workload, "description": m["desc"], "n_samples": n, "dim": D, "k": k,
                    "n_box": m["world"].n_box, "n_sph": m["world"].n_sph, "edges_per_step": m["edges"],

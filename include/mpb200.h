@@ -298,6 +298,16 @@ int mpb_roadmap_parents(const int64_t *nbr, const double *nbr_dist, const int32_
                         const uint8_t *vertex_hit, int64_t n_rows, int row_len, int64_t row_offset,
                         const double *dist, int64_t source, int64_t *parent, void *stream);
 
+/* Which filter mpb_knn_search / mpb_knn_f32filter run for a sample set of this size and dimension at this k
+ * (for reporting; results are identical): the packed-fp32 FFMA2 scan, the tensor-core scan (tcgen05.mma
+ * kind::tf32 on operands split into two TF32 parts, accumulator in tensor memory), or the exact fp64 scan alone.
+ * The tensor-core scan is chosen for 6- and 7-dimensional sets of at least 300 000 samples and k <= 12;
+ * MPB200_KNN_TC=0 / =1 in the environment (read once) switches it off / forces it wherever it applies. */
+#define MPB_KNN_KIND_FP32 0
+#define MPB_KNN_KIND_TENSOR 1
+#define MPB_KNN_KIND_EXACT 2
+int mpb_knn_filter_kind(int64_t n_samples, int dim, int k);
+
 /* ---- measurement helpers (not part of the planner path) ---------------------------------
  * Issue-rate micro-benchmarks used by bench.py for the roofline denominators: each thread
  * runs `iters` rounds of 8 independent dependent-FMA chains.  flops = 2 * 8 * iters *

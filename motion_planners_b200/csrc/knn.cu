@@ -592,23 +592,44 @@ __global__ void __launch_bounds__(kWarps * 32, kBlocksPerSM)
 // ------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------
-// The tensor-core scan (knn_tc.cuh) is an opt-in alternative for sample sets of up to seven dimensions: set
-// MPB200_KNN_TC=1 in the environment before the library is first used.  It is bit-exact like the default path but
-// slower on B200 (341 vs 245 ms at 1M x 7-DoF): every key has to be read out of tensor memory, and that read-out
-// runs at about 64 bytes per clock per SM.  It stays in the tree, tested, for hardware with a fused min on that
-// read-out.
-constexpr int64_t kTcMinSamples = 8192;
+// Which filter serves a search.  The tensor-core scan (knn_tc.cuh) costs the same for every dimension up to 7
+// (its operand is always 24 columns wide) and has a heavier insertion path than the FFMA2 kernel, so it wins where
+// the scan is long and the dimension high: measured on B200 at 7-DoF, 162 vs 245 ms at 1M samples, 26.4 vs 28.4 ms
+// at 300k, 6.7 vs 3.8 ms at 100k.  Default: 6 or 7 dimensions and at least kTcAutoMinSamples samples.
+// MPB200_KNN_TC=0 switches it off, MPB200_KNN_TC=1 forces it for every set it can serve (dimension <= 7, at least
+// MPB200_KNN_TC_MIN samples, default 8192); both are read once, when the library is first used.
+constexpr int64_t kTcAutoMinSamples = 300000;
+constexpr int kTcAutoMinDim = 6;
 
-bool tc_enabled()
+struct TcPolicy {
+    int mode;            // 0 off, 1 forced, 2 automatic
+    int64_t forced_min;
+};
+
+const TcPolicy &tc_policy()
 {
-    static const bool on = [] {
+    static const TcPolicy p = [] {
+        TcPolicy q = {2, 8192};
         const char *e = getenv("MPB200_KNN_TC");
-        return e && e[0] == '1';
+        if (e && e[0] == '0') q.mode = 0;
+        if (e && e[0] == '1') q.mode = 1;
+        const char *m = getenv("MPB200_KNN_TC_MIN");
+        if (m) {
+            const long long v = atoll(m);
+            if (v >= kTcTile) q.forced_min = v;
+        }
+        return q;
     }();
-    return on;
+    return p;
 }
 
-bool use_tc(int64_t N, int D) { return tc_enabled() && D <= kTcMaxDim && N >= kTcMinSamples; }
+bool use_tc(int64_t N, int D)
+{
+    const TcPolicy &p = tc_policy();
+    if (p.mode == 0 || D > kTcMaxDim) return false;
+    if (p.mode == 1) return N >= p.forced_min;
+    return D >= kTcAutoMinDim && N >= kTcAutoMinSamples;
+}
 
 struct WsLayout {
     size_t packed_off, packed_bytes, tc_off, tc_bytes, fb_off, fb_bytes, surv_off, surv_bytes, thr_off, thr_bytes, total;
@@ -757,7 +778,7 @@ int launch_search(const double *x, int64_t N, const double *qs, int64_t M, const
     MPB_CUDA_CHECK(cudaMemsetAsync(&h->fb_count, 0, sizeof(int), st));
     if constexpr (D <= kTcMaxDim) {
         if (L.tc_tiles > 0 && k <= kSmallListMaxK) {
-            // tensor-core scan -> 4 x 16 survivors per query -> exact re-rank + certificate -> exact re-do of the rest
+            // tensor-core scan -> kTcParts x 16 survivors per query -> exact re-rank + certificate -> exact re-do of the rest
             char *base = reinterpret_cast<char *>(ws);
             const unsigned char *tiles = reinterpret_cast<const unsigned char *>(base + L.tc_off);
             int *surv = reinterpret_cast<int *>(base + L.surv_off);
@@ -834,6 +855,14 @@ MPB_API int mpb_knn_f64_metric(const double *samples, int64_t n_samples, const d
     const double lim = (metric == MPB_METRIC_KDTREE) ? max_dist * max_dist : max_dist;
     return dispatch_exact(dim, samples, n_samples, queries, n_queries, make_weights(weights, dim), metric, k, lim,
                           out_idx, out_dist, (cudaStream_t)stream);
+}
+
+MPB_API int mpb_knn_filter_kind(int64_t n_samples, int dim, int k)
+{
+    if (dim < 1 || dim > MPB_MAX_DIM || n_samples < 0 || k < 1 || k > MPB_MAX_K) return MPB_EINVAL;
+    if (k > kFilterMaxK) return MPB_KNN_KIND_EXACT;
+    if (k <= kSmallListMaxK && use_tc(n_samples, dim)) return MPB_KNN_KIND_TENSOR;
+    return MPB_KNN_KIND_FP32;
 }
 
 MPB_API size_t mpb_knn_workspace_bytes(int64_t n_samples, int64_t n_queries, int dim)

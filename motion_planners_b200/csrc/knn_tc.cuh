@@ -20,10 +20,16 @@
 constexpr int kTcK = 24;                       // operand columns (D <= 7)
 constexpr int kTcTile = 256;                   // candidates per tile = MMA N
 constexpr int kTcQueries = 128;                // queries per CTA = MMA M = TMEM lanes
-constexpr int kTcStages = 4;                   // shared-memory ring depth
+#ifndef MPB_TC_PARTS
+#define MPB_TC_PARTS 4
+#endif
+#ifndef MPB_TC_STAGES
+#define MPB_TC_STAGES 3
+#endif
+constexpr int kTcStages = MPB_TC_STAGES;       // shared-memory ring depth
 constexpr int kTcKeep = 16;                    // survivors per list
-constexpr int kTcParts = 4;                    // epilogue warps per TMEM lane quarter = lists per query
-constexpr int kTcEpiWarps = 4 * kTcParts;      // warp w: lane quarter w & 3, part w >> 2 (two 32-key chunks per tile)
+constexpr int kTcParts = MPB_TC_PARTS;          // epilogue warps per TMEM lane quarter = lists per query
+constexpr int kTcEpiWarps = 4 * kTcParts;      // warp w: lane quarter w & 3, part w >> 2 (8 / kTcParts chunks of 32 keys per tile)
 constexpr int kTcThreads = 32 * (kTcEpiWarps + 2);
 constexpr int kTcSurvivors = kTcKeep * kTcParts;   // survivors per query handed to the exact re-rank
 constexpr uint32_t kTcLbo = 128;               // bytes between the two 16-byte k-chunks of a k-step
@@ -69,6 +75,16 @@ __device__ __forceinline__ void mbar_wait_backoff(uint64_t *bar, uint32_t parity
 {
     for (uint32_t spins = 0; !mbar_try_wait(bar, parity); ++spins) {
         __nanosleep(40);
+        if (spins > (1u << 24)) __trap();
+    }
+}
+
+// the same for a whole converged warp (the vote keeps the code after it warp-uniform); sixteen warps polling
+// without a pause took a third of the SM's issue slots
+__device__ __forceinline__ void mbar_wait_warp_backoff(uint64_t *bar, uint32_t parity)
+{
+    for (uint32_t spins = 0; !__all_sync(0xffffffffu, mbar_try_wait(bar, parity)); ++spins) {
+        __nanosleep(32);
         if (spins > (1u << 24)) __trap();
     }
 }
@@ -132,7 +148,9 @@ struct TcSmem {
     static constexpr int B_OFF = A_OFF + kTcQueryBytes;
     static constexpr int LK_OFF = B_OFF + kTcStages * kTcTileBytes;
     static constexpr int LI_OFF = LK_OFF + kTcSurvivors * kTcQueries * 4;
-    static constexpr int BAR_OFF = LI_OFF + kTcSurvivors * kTcQueries * 4;
+    static constexpr int SCR_OFF = LI_OFF + kTcSurvivors * kTcQueries * 4;   // [epilogue warp][32 lanes][33]
+    static constexpr int THR_OFF = SCR_OFF + kTcEpiWarps * 32 * 33 * 4;        // [part][128] published thresholds
+    static constexpr int BAR_OFF = THR_OFF + kTcParts * kTcQueries * 4;
     static constexpr int BYTES = BAR_OFF + 256;
 };
 
@@ -150,6 +168,8 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     unsigned char *sB = smem + TcSmem::B_OFF;
     float *lk = reinterpret_cast<float *>(smem + TcSmem::LK_OFF);      // [part][128][kTcKeep] sorted keys per query
     int *li = reinterpret_cast<int *>(smem + TcSmem::LI_OFF);          // [part][128][kTcKeep] their candidate indices
+    float *scr = reinterpret_cast<float *>(smem + TcSmem::SCR_OFF);
+    float *sthr = reinterpret_cast<float *>(smem + TcSmem::THR_OFF);
     uint64_t *full = reinterpret_cast<uint64_t *>(smem + TcSmem::BAR_OFF);
     uint64_t *empty = full + kTcStages;
     uint64_t *tfull = empty + kTcStages;
@@ -184,6 +204,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         lk[i] = INFINITY;
         li[i] = -1;
     }
+    for (int i = tid; i < kTcParts * kTcQueries; i += kTcThreads) sthr[i] = INFINITY;
     if (tid == 0) {
         for (int s = 0; s < kTcStages; ++s) {
             mbar_init(&full[s], 1);
@@ -255,27 +276,50 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
         float *lkp = lk + part * kTcKeep * kTcQueries;
         int *lip = li + part * kTcKeep * kTcQueries;
-        // The 32 keys a lane just received are examined with one min-tree; a lane whose minimum beats its
-        // threshold is served by the WHOLE warp: its keys are spread over the lanes (key j to lane j), the takers
-        // are found with one ballot, and each taker is inserted into that query's shared-memory list by lanes
-        // 0..15 side by side.  A lane-private walk over the 32 keys made every lane of the warp wait for it,
-        // and one chunk in five has such a lane at 1M candidates (profiles/r1_summary.md).
+        // The 32 keys a lane just received are examined with one min-tree.  When some lane's minimum beats its
+        // threshold, the flagged lanes park their keys in the warp's scratch rows, and each flagged lane is then
+        // served by the WHOLE warp: lane j reads key j of that row, one ballot finds the takers, and each taker is
+        // inserted into the query's shared-memory list by lanes 0..15 side by side.  (A lane-private walk over
+        // the 32 keys makes every lane of the warp wait for it, and at 1M candidates one chunk in five has a
+        // flagged lane: profiles/r1_summary.md.)
+        float *rows = scr + warp * 32 * 33;
         auto examine = [&](const uint32_t (&v)[32], int cbase) {
-            float m = __uint_as_float(v[0]);
+            float g[4];        // minima of the four groups of eight keys
 #pragma unroll
-            for (int j = 1; j < 32; ++j) m = fminf(m, __uint_as_float(v[j]));
+            for (int gi = 0; gi < 4; ++gi) {
+                g[gi] = __uint_as_float(v[8 * gi]);
+#pragma unroll
+                for (int j = 1; j < 8; ++j) g[gi] = fminf(g[gi], __uint_as_float(v[8 * gi + j]));
+            }
+            const float m = fminf(fminf(g[0], g[1]), fminf(g[2], g[3]));
             unsigned flagged = __ballot_sync(FULL_MASK, m < thr);
+            if (flagged == 0) return;
+            // A list that already holds 16 keys below t proves that nothing at or above t is among the query's
+            // 16 best, whichever list it would go to: before any work is spent on a flagged chunk, every lane
+            // lowers its threshold to the smallest one published for its query (read without synchronisation:
+            // a stale value is only a larger one) and the chunk is tested again.
+#pragma unroll
+            for (int pp = 0; pp < kTcParts; ++pp) thr = fminf(thr, sthr[pp * kTcQueries + q]);
+            flagged = __ballot_sync(FULL_MASK, m < thr);
+            if (flagged == 0) return;
+            // only the groups of eight that hold a key below the threshold are parked
+            unsigned gm = 0;
+#pragma unroll
+            for (int gi = 0; gi < 4; ++gi) {
+                if (g[gi] < thr) {
+                    gm |= 1u << gi;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) rows[lane * 33 + 8 * gi + j] = __uint_as_float(v[8 * gi + j]);
+                }
+            }
+            __syncwarp();
             while (flagged) {
                 const int L = __ffs(flagged) - 1;
                 flagged &= flagged - 1;
                 float thrL = __shfl_sync(FULL_MASK, thr, L);
-                float mine = 0.f;
-#pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    const float t = __uint_as_float(__shfl_sync(FULL_MASK, v[j], L));
-                    if (lane == j) mine = t;
-                }
-                unsigned takers = __ballot_sync(FULL_MASK, mine < thrL);
+                const unsigned gmL = __shfl_sync(FULL_MASK, gm, L);
+                const float mine = rows[L * 33 + lane];      // stale where the group was not parked: masked out
+                unsigned takers = __ballot_sync(FULL_MASK, ((gmL >> (lane >> 3)) & 1u) && mine < thrL);
                 const int qL = quarter * 32 + L;
                 while (takers) {
                     const int j = __ffs(takers) - 1;
@@ -299,28 +343,56 @@ __global__ void __launch_bounds__(kTcThreads, 1)
                         thrL = lkp[qL * kTcKeep + kTcKeep - 1];
                     }
                 }
-                if (lane == L) thr = thrL;
+                if (lane == L) {
+                    thr = thrL;
+                    sthr[part * kTcQueries + q] = thrL;
+                }
             }
+            __syncwarp();
         };
         for (int i = 0; i < n_tiles; ++i) {
             const int b = i & 1;
-            mbar_wait_warp(&tfull[b], (uint32_t)((i / 2) & 1));
+            mbar_wait_warp_backoff(&tfull[b], (uint32_t)((i / 2) & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            // two register sets: the second chunk's load is in flight while the first chunk is examined
+            constexpr int CH = (kTcTile / 32) / kTcParts;      // chunks per warp per tile
+            static_assert(CH % 2 == 0, "chunks are processed in pairs");
             uint32_t va[32], vb[32];
-            const int c0 = 2 * part;
-            __syncwarp();
-            tmem_ld32(va, lane_base + (uint32_t)(b * kTcTile + c0 * 32));
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-            __syncwarp();
-            tmem_ld32(vb, lane_base + (uint32_t)(b * kTcTile + (c0 + 1) * 32));
-            examine(va, i * kTcTile + c0 * 32);
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-            __syncwarp();
-            // both chunks are in registers: the accumulator can be handed back before the second is examined
-            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-            if (lane == 0) mbar_arrive(&tempty[b]);
-            examine(vb, i * kTcTile + (c0 + 1) * 32);
+            const int c0 = CH * part;
+            const uint32_t tile_base = lane_base + (uint32_t)(b * kTcTile + c0 * 32);
+            if constexpr (CH == 2) {
+                // both chunks go to registers first and the accumulator is handed back at once: the next MMAs
+                // never wait for a warp that is busy inserting
+                __syncwarp();
+                tmem_ld32(va, tile_base);
+                tmem_ld32(vb, tile_base + 32u);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tempty[b]);
+                examine(va, i * kTcTile + c0 * 32);
+                examine(vb, i * kTcTile + (c0 + 1) * 32);
+            } else {
+                // two register sets: the next chunk's load is in flight while the current chunk is examined; the
+                // accumulator is handed back as soon as this warp's last chunk is in registers
+                __syncwarp();
+                tmem_ld32(va, tile_base);
+#pragma unroll 1
+                for (int c = 0; c < CH; c += 2) {
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    __syncwarp();
+                    tmem_ld32(vb, tile_base + (uint32_t)((c + 1) * 32));
+                    examine(va, i * kTcTile + (c0 + c) * 32);
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    __syncwarp();
+                    if (c + 2 < CH) {
+                        tmem_ld32(va, tile_base + (uint32_t)((c + 2) * 32));
+                    } else {
+                        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                        if (lane == 0) mbar_arrive(&tempty[b]);
+                    }
+                    examine(vb, i * kTcTile + (c0 + c + 1) * 32);
+                }
+            }
         }
         // this part's survivors of the query (ascending fp32 key) and its final threshold
         const int64_t qq = q0 + q;
@@ -336,7 +408,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
 }
 
 // ---- exact re-rank of the survivors of every query, and the certificate ---------------------------------
-// One warp per query, two survivors per lane (kTcParts lists of kTcKeep).  Same argument as in
+// One warp per query, kTcSurvivors / 32 survivors per lane (kTcParts lists of kTcKeep).  Same argument as in
 // knn_filter_kernel: every sample outside list p has computed key >= T_p, so every sample outside all lists has
 // computed key >= T = min_p T_p, hence exact squared distance >= (sqrt(T - eta + |q^|^2) - delta)^2; here eta also
 // covers the TF32 split (three dropped or rounded 2^-22 terms) and the tensor core's accumulation, budgeted at
@@ -348,7 +420,8 @@ __global__ void __launch_bounds__(256)
                          const float *__restrict__ surv_thr, int *__restrict__ fb_list, int64_t *__restrict__ out_idx,
                          double *__restrict__ out_dist)
 {
-    static_assert(kTcSurvivors == 64, "two survivors per lane");
+    constexpr int NU = kTcSurvivors / 32;       // survivors per lane
+    static_assert(kTcSurvivors % 32 == 0, "whole survivors per lane");
     const int lane = threadIdx.x & 31;
     const int64_t q = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (q >= M) return;                         // whole warps leave together
@@ -360,10 +433,10 @@ __global__ void __launch_bounds__(256)
         const double qh = (double)(float)d_sub(eq[d], h->center[d]);
         nq2 += qh * qh;
     }
-    int ci[2];
-    double S[2];
+    int ci[NU];
+    double S[NU];
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
+    for (int u = 0; u < NU; ++u) {
         ci[u] = surv_idx[q * kTcSurvivors + u * 32 + lane];
         if (ci[u] >= N) ci[u] = -1;             // a padding slot (only when a part saw fewer than 16 real candidates)
         S[u] = INFINITY;
@@ -374,25 +447,29 @@ __global__ void __launch_bounds__(256)
             S[u] = sqdist_kdtree<D>(eq, ex);
         }
     }
-    int rank[2] = {0, 0};
+    int rank[NU];
+#pragma unroll
+    for (int u = 0; u < NU; ++u) rank[u] = 0;
     for (int o = 0; o < 32; ++o) {
 #pragma unroll
-        for (int w = 0; w < 2; ++w) {
+        for (int w = 0; w < NU; ++w) {
             const double So = __shfl_sync(FULL_MASK, S[w], o);
             const int io = __shfl_sync(FULL_MASK, ci[w], o);
 #pragma unroll
-            for (int u = 0; u < 2; ++u) rank[u] += ((So < S[u]) || (So == S[u] && io < ci[u])) ? 1 : 0;
+            for (int u = 0; u < NU; ++u) rank[u] += ((So < S[u]) || (So == S[u] && io < ci[u])) ? 1 : 0;
         }
     }
     // k-th smallest exact key among the survivors (inf when fewer than k exist)
     double Sk = INFINITY;
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
+    for (int u = 0; u < NU; ++u) {
         const unsigned mk = __ballot_sync(FULL_MASK, ci[u] >= 0 && rank[u] == k - 1);
         const double cand = __shfl_sync(FULL_MASK, S[u], mk ? (__ffs(mk) - 1) : 0);
         if (mk) Sk = cand;
     }
-    const int nvalid = __popc(__ballot_sync(FULL_MASK, ci[0] >= 0)) + __popc(__ballot_sync(FULL_MASK, ci[1] >= 0));
+    int nvalid = 0;
+#pragma unroll
+    for (int u = 0; u < NU; ++u) nvalid += __popc(__ballot_sync(FULL_MASK, ci[u] >= 0));
     float T32 = INFINITY;
 #pragma unroll
     for (int p = 0; p < kTcParts; ++p) {
@@ -419,7 +496,7 @@ __global__ void __launch_bounds__(256)
     }
     if (ok) {
 #pragma unroll
-        for (int u = 0; u < 2; ++u) {
+        for (int u = 0; u < NU; ++u) {
             if (ci[u] >= 0 && rank[u] < k) {
                 const bool keep = S[u] < r2;
                 out_idx[q * k + rank[u]] = keep ? (int64_t)ci[u] : -1;

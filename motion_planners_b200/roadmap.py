@@ -20,7 +20,7 @@ import math
 import numpy as np
 import torch
 
-from . import ops
+from . import _lib, ops
 from .geometry import STEP_SIZE
 
 
@@ -125,7 +125,8 @@ class DeviceRoadmap(object):
             self._index = ops.KnnIndex(samples, self.weights)
         self._index._prepared = False
         self._index.prepare(n_local)
-        launches += 4                               # init, minmax, finalize, pack
+        tensor = _lib.lib().mpb_knn_filter_kind(int(samples.shape[0]), int(samples.shape[1]), int(self.kk)) == 1
+        launches += 5 if tensor else 4              # init, minmax, finalize, pack (+ the tensor-core operand tiles)
         mark("packed")
         if getattr(self, "nbr_idx", None) is None or self.nbr_idx.shape != (n_local, self.kk):
             self.nbr_idx = torch.empty((n_local, self.kk), dtype=torch.int64, device=samples.device)
@@ -133,7 +134,7 @@ class DeviceRoadmap(object):
             self.stats = torch.zeros(2, dtype=torch.int64, device=samples.device)
         self._index.search(queries, self.kk, self.max_distance, stats=self.stats, out_idx=self.nbr_idx,
                            out_dist=self.nbr_dist)
-        launches += 2                               # filter + exact re-do of uncertified queries
+        launches += 3 if tensor else 2              # filter (+ its re-rank kernel) + exact re-do of uncertified queries
         mark("knn")
 
         if check:
