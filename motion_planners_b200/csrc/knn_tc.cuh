@@ -20,6 +20,12 @@
 constexpr int kTcK = 24;                       // operand columns (D <= 7)
 constexpr int kTcTile = 256;                   // candidates per tile = MMA N
 constexpr int kTcQueries = 128;                // queries per CTA = MMA M = TMEM lanes
+#ifndef MPB_TC_SLEEP_ROLE
+#define MPB_TC_SLEEP_ROLE 40      // ns between polls of the producer / MMA threads
+#endif
+#ifndef MPB_TC_SLEEP_EPI
+#define MPB_TC_SLEEP_EPI 32       // ns between polls of an epilogue warp
+#endif
 #ifndef MPB_TC_PARTS
 #define MPB_TC_PARTS 4
 #endif
@@ -74,7 +80,7 @@ __device__ __forceinline__ void mbar_arrive(uint64_t *bar)
 __device__ __forceinline__ void mbar_wait_backoff(uint64_t *bar, uint32_t parity)
 {
     for (uint32_t spins = 0; !mbar_try_wait(bar, parity); ++spins) {
-        __nanosleep(40);
+        __nanosleep(MPB_TC_SLEEP_ROLE);
         if (spins > (1u << 24)) __trap();
     }
 }
@@ -84,7 +90,7 @@ __device__ __forceinline__ void mbar_wait_backoff(uint64_t *bar, uint32_t parity
 __device__ __forceinline__ void mbar_wait_warp_backoff(uint64_t *bar, uint32_t parity)
 {
     for (uint32_t spins = 0; !__all_sync(0xffffffffu, mbar_try_wait(bar, parity)); ++spins) {
-        __nanosleep(32);
+        __nanosleep(MPB_TC_SLEEP_EPI);
         if (spins > (1u << 24)) __trap();
     }
 }
