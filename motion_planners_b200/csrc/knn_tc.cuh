@@ -81,7 +81,7 @@ __device__ __forceinline__ void mbar_wait_backoff(uint64_t *bar, uint32_t parity
 {
     for (uint32_t spins = 0; !mbar_try_wait(bar, parity); ++spins) {
         __nanosleep(MPB_TC_SLEEP_ROLE);
-        if (spins > (1u << 24)) __trap();
+        if (spins > (1u << 26)) __trap();
     }
 }
 
@@ -91,7 +91,7 @@ __device__ __forceinline__ void mbar_wait_warp_backoff(uint64_t *bar, uint32_t p
 {
     for (uint32_t spins = 0; !__all_sync(0xffffffffu, mbar_try_wait(bar, parity)); ++spins) {
         __nanosleep(MPB_TC_SLEEP_EPI);
-        if (spins > (1u << 24)) __trap();
+        if (spins > (1u << 26)) __trap();
     }
 }
 
