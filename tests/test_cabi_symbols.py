@@ -57,3 +57,23 @@ def test_product_never_imports_the_oracle():
                 src = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), f
                 assert "mp_oracle" not in src, f
+
+
+def test_knn_filter_kind_policy_is_a_pure_host_query():
+    """mpb_knn_filter_kind touches no device: which filter a search gets depends on size, dimension and k only."""
+    import ctypes
+    import os
+    if os.environ.get("MPB200_KNN_TC") is not None:
+        import pytest
+        pytest.skip("the policy is overridden through the environment")
+    from motion_planners_b200 import _lib
+    lib = _lib.lib()
+    kind = lambda n, d, k: lib.mpb_knn_filter_kind(ctypes.c_int64(n), d, k)
+    FP32, TENSOR, EXACT = 0, 1, 2
+    assert kind(1000000, 7, 11) == TENSOR and kind(300000, 6, 11) == TENSOR
+    assert kind(299999, 7, 11) == FP32 and kind(100000, 6, 11) == FP32
+    assert kind(1000000, 5, 11) == TENSOR and kind(500000, 5, 11) == FP32
+    assert kind(1000000, 3, 11) == FP32 and kind(1000000, 8, 11) == FP32
+    assert kind(1000000, 7, 13) == FP32          # 32-entry lists: packed-fp32 kernel
+    assert kind(1000000, 7, 29) == EXACT and kind(1000, 2, 32) == EXACT
+    assert kind(1000, 0, 3) < 0 and kind(1000, 3, 0) < 0 and kind(1000, 3, 33) < 0
