@@ -594,14 +594,14 @@ __global__ void __launch_bounds__(kWarps * 32, kBlocksPerSM)
 // ------------------------------------------------------------------------------------------
 // Which filter serves a search.  The tensor-core scan (knn_tc.cuh) costs the same for every dimension up to 7
 // (its operand is always 24 columns wide) and has a heavier insertion path than the FFMA2 kernel, so it wins where
-// the scan is long and the dimension high: measured on B200 at 7-DoF, 162 vs 245 ms at 1M samples, 26.4 vs 28.4 ms
-// at 300k, 6.7 vs 3.8 ms at 100k; the FFMA2 kernel at 1M samples takes 158 / 180 / 206 / 226 ms at 3 / 4 / 5 / 6
-// dimensions.  Default: 6 or 7 dimensions from kTcAutoMinSamples samples on, 4 or 5 dimensions from
-// kTcAutoMinSamplesLowDim on.
-// MPB200_KNN_TC=0 switches it off, MPB200_KNN_TC=1 forces it for every set it can serve (dimension <= 7, at least
-// MPB200_KNN_TC_MIN samples, default 8192); both are read once, when the library is first used.
-constexpr int64_t kTcAutoMinSamples = 300000;
-constexpr int64_t kTcAutoMinSamplesLowDim = 700000;
+// the scan is long and the dimension high.  Measured on B200, k = 11, tensor-core vs FFMA2 kernel: 7-DoF 1M samples
+// 140 vs 245 ms, 300k 20.7 vs 28.4, 200k 11.7 vs 13.8, 150k 7.5 vs 8.0, 100k 5.0 vs 4.1; 6-DoF 100k 4.9 vs 3.8;
+// the FFMA2 kernel at 1M samples takes 158 / 180 / 206 / 226 ms at 3 / 4 / 5 / 6 dimensions.  Default: from
+// kTcAutoMin[dim] samples on.  MPB200_KNN_TC=0 switches the tensor-core scan off, MPB200_KNN_TC=1 forces it for
+// every set it can serve (dimension <= 7, at least MPB200_KNN_TC_MIN samples, default 8192); both are read once,
+// when the library is first used.
+constexpr int64_t kTcNever = INT64_MAX;
+constexpr int64_t kTcAutoMin[kTcMaxDim + 1] = {kTcNever, kTcNever, kTcNever, kTcNever, 500000, 300000, 180000, 160000};
 
 struct TcPolicy {
     int mode;            // 0 off, 1 forced, 2 automatic
@@ -630,7 +630,7 @@ bool use_tc(int64_t N, int D)
     const TcPolicy &p = tc_policy();
     if (p.mode == 0 || D > kTcMaxDim) return false;
     if (p.mode == 1) return N >= p.forced_min;
-    return (D >= 6 && N >= kTcAutoMinSamples) || (D >= 4 && N >= kTcAutoMinSamplesLowDim);
+    return N >= kTcAutoMin[D];
 }
 
 struct WsLayout {
@@ -656,7 +656,7 @@ WsLayout ws_layout(int64_t N, int64_t M, int D, bool allow_tc = true)
     L.surv_off = L.fb_off + L.fb_bytes;
     L.surv_bytes = tc ? ((m * kTcSurvivors * sizeof(int) + 255) & ~(size_t)255) : 0;
     L.thr_off = L.surv_off + L.surv_bytes;
-    L.thr_bytes = tc ? ((m * kTcParts * sizeof(float) + 255) & ~(size_t)255) : 0;
+    L.thr_bytes = tc ? ((m * kTcLists * sizeof(float) + 255) & ~(size_t)255) : 0;
     L.total = L.thr_off + L.thr_bytes;
     return L;
 }

@@ -30,14 +30,18 @@ constexpr int kTcQueries = 128;                // queries per CTA = MMA M = TMEM
 #define MPB_TC_PARTS 4
 #endif
 #ifndef MPB_TC_STAGES
-#define MPB_TC_STAGES 3
+#define MPB_TC_STAGES 4
 #endif
 constexpr int kTcStages = MPB_TC_STAGES;       // shared-memory ring depth
 constexpr int kTcKeep = 16;                    // survivors per list
 constexpr int kTcParts = MPB_TC_PARTS;          // epilogue warps per TMEM lane quarter = lists per query
 constexpr int kTcEpiWarps = 4 * kTcParts;      // warp w: lane quarter w & 3, part w >> 2 (8 / kTcParts chunks of 32 keys per tile)
 constexpr int kTcThreads = 32 * (kTcEpiWarps + 2);
-constexpr int kTcSurvivors = kTcKeep * kTcParts;   // survivors per query handed to the exact re-rank
+#ifndef MPB_TC_SHARED_LIST
+#define MPB_TC_SHARED_LIST 1      // 1: the warps of a lane quarter share one list per query (per-query lock)
+#endif
+constexpr int kTcLists = MPB_TC_SHARED_LIST ? 1 : kTcParts;   // lists per query
+constexpr int kTcSurvivors = kTcKeep * kTcLists;   // survivors per query handed to the exact re-rank
 constexpr uint32_t kTcLbo = 128;               // bytes between the two 16-byte k-chunks of a k-step
 constexpr uint32_t kTcSbo = (kTcK / 4) * 128;  // bytes between 8-row groups
 constexpr int kTcTileBytes = (kTcTile / 8) * (int)kTcSbo;      // 24576
@@ -156,7 +160,8 @@ struct TcSmem {
     static constexpr int LI_OFF = LK_OFF + kTcSurvivors * kTcQueries * 4;
     static constexpr int SCR_OFF = LI_OFF + kTcSurvivors * kTcQueries * 4;   // [epilogue warp][32 lanes][33]
     static constexpr int THR_OFF = SCR_OFF + kTcEpiWarps * 32 * 33 * 4;        // [part][128] published thresholds
-    static constexpr int BAR_OFF = THR_OFF + kTcParts * kTcQueries * 4;
+    static constexpr int LOCK_OFF = THR_OFF + kTcLists * kTcQueries * 4;       // [128] list locks (shared-list build)
+    static constexpr int BAR_OFF = LOCK_OFF + kTcQueries * 4;
     static constexpr int BYTES = BAR_OFF + 256;
 };
 
@@ -176,6 +181,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     int *li = reinterpret_cast<int *>(smem + TcSmem::LI_OFF);          // [part][128][kTcKeep] their candidate indices
     float *scr = reinterpret_cast<float *>(smem + TcSmem::SCR_OFF);
     float *sthr = reinterpret_cast<float *>(smem + TcSmem::THR_OFF);
+    int *locks = reinterpret_cast<int *>(smem + TcSmem::LOCK_OFF);
     uint64_t *full = reinterpret_cast<uint64_t *>(smem + TcSmem::BAR_OFF);
     uint64_t *empty = full + kTcStages;
     uint64_t *tfull = empty + kTcStages;
@@ -210,7 +216,8 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         lk[i] = INFINITY;
         li[i] = -1;
     }
-    for (int i = tid; i < kTcParts * kTcQueries; i += kTcThreads) sthr[i] = INFINITY;
+    for (int i = tid; i < kTcLists * kTcQueries; i += kTcThreads) sthr[i] = INFINITY;
+    for (int i = tid; i < kTcQueries; i += kTcThreads) locks[i] = 0;
     if (tid == 0) {
         for (int s = 0; s < kTcStages; ++s) {
             mbar_init(&full[s], 1);
@@ -280,8 +287,9 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         const int q = quarter * 32 + lane;
         float thr = INFINITY;
         const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
-        float *lkp = lk + part * kTcKeep * kTcQueries;
-        int *lip = li + part * kTcKeep * kTcQueries;
+        const int my_list = MPB_TC_SHARED_LIST ? 0 : part;
+        float *lkp = lk + my_list * kTcKeep * kTcQueries;
+        int *lip = li + my_list * kTcKeep * kTcQueries;
         // The 32 keys a lane just received are examined with one min-tree.  When some lane's minimum beats its
         // threshold, the flagged lanes park their keys in the warp's scratch rows, and each flagged lane is then
         // served by the WHOLE warp: lane j reads key j of that row, one ballot finds the takers, and each taker is
@@ -305,7 +313,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
             // lowers its threshold to the smallest one published for its query (read without synchronisation:
             // a stale value is only a larger one) and the chunk is tested again.
 #pragma unroll
-            for (int pp = 0; pp < kTcParts; ++pp) thr = fminf(thr, sthr[pp * kTcQueries + q]);
+            for (int pp = 0; pp < kTcLists; ++pp) thr = fminf(thr, sthr[pp * kTcQueries + q]);
             flagged = __ballot_sync(FULL_MASK, m < thr);
             if (flagged == 0) return;
             // only the groups of eight that hold a key below the threshold are parked
@@ -323,10 +331,20 @@ __global__ void __launch_bounds__(kTcThreads, 1)
                 const int L = __ffs(flagged) - 1;
                 flagged &= flagged - 1;
                 float thrL = __shfl_sync(FULL_MASK, thr, L);
+                const int qL = quarter * 32 + L;
+#if MPB_TC_SHARED_LIST
+                // the four warps of this lane quarter insert into the same list: one warp at a time per query
+                if (lane == 0) {
+                    for (uint32_t spins = 0; atomicCAS(&locks[qL], 0, 1) != 0; ++spins)
+                        if (spins > (1u << 24)) __trap();
+                }
+                __syncwarp();
+                __threadfence_block();
+                thrL = fminf(thrL, lkp[qL * kTcKeep + kTcKeep - 1]);
+#endif
                 const unsigned gmL = __shfl_sync(FULL_MASK, gm, L);
                 const float mine = rows[L * 33 + lane];      // stale where the group was not parked: masked out
                 unsigned takers = __ballot_sync(FULL_MASK, ((gmL >> (lane >> 3)) & 1u) && mine < thrL);
-                const int qL = quarter * 32 + L;
                 while (takers) {
                     const int j = __ffs(takers) - 1;
                     takers &= takers - 1;
@@ -351,8 +369,13 @@ __global__ void __launch_bounds__(kTcThreads, 1)
                 }
                 if (lane == L) {
                     thr = thrL;
-                    sthr[part * kTcQueries + q] = thrL;
+                    sthr[my_list * kTcQueries + q] = thrL;
                 }
+#if MPB_TC_SHARED_LIST
+                __syncwarp();
+                __threadfence_block();
+                if (lane == 0) atomicExch(&locks[qL], 0);
+#endif
             }
             __syncwarp();
         };
@@ -400,12 +423,15 @@ __global__ void __launch_bounds__(kTcThreads, 1)
                 }
             }
         }
+#if MPB_TC_SHARED_LIST
+        asm volatile("bar.sync 1, %0;" ::"r"(kTcEpiWarps * 32) : "memory");
+#endif
         // this part's survivors of the query (ascending fp32 key) and its final threshold
         const int64_t qq = q0 + q;
-        if (qq < M) {
+        if (qq < M && (!MPB_TC_SHARED_LIST || part == 0)) {
 #pragma unroll
-            for (int p = 0; p < kTcKeep; ++p) surv_idx[qq * kTcSurvivors + part * kTcKeep + p] = lip[q * kTcKeep + p];
-            surv_thr[qq * kTcParts + part] = thr;
+            for (int p = 0; p < kTcKeep; ++p) surv_idx[qq * kTcSurvivors + my_list * kTcKeep + p] = lip[q * kTcKeep + p];
+            surv_thr[qq * kTcLists + my_list] = MPB_TC_SHARED_LIST ? lkp[q * kTcKeep + kTcKeep - 1] : thr;
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -426,8 +452,7 @@ __global__ void __launch_bounds__(256)
                          const float *__restrict__ surv_thr, int *__restrict__ fb_list, int64_t *__restrict__ out_idx,
                          double *__restrict__ out_dist)
 {
-    constexpr int NU = kTcSurvivors / 32;       // survivors per lane
-    static_assert(kTcSurvivors % 32 == 0, "whole survivors per lane");
+    constexpr int NU = (kTcSurvivors + 31) / 32;   // survivors per lane
     const int lane = threadIdx.x & 31;
     const int64_t q = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (q >= M) return;                         // whole warps leave together
@@ -443,7 +468,7 @@ __global__ void __launch_bounds__(256)
     double S[NU];
 #pragma unroll
     for (int u = 0; u < NU; ++u) {
-        ci[u] = surv_idx[q * kTcSurvivors + u * 32 + lane];
+        ci[u] = (u * 32 + lane < kTcSurvivors) ? surv_idx[q * kTcSurvivors + u * 32 + lane] : -1;
         if (ci[u] >= N) ci[u] = -1;             // a padding slot (only when a part saw fewer than 16 real candidates)
         S[u] = INFINITY;
         if (ci[u] >= 0) {
@@ -478,8 +503,8 @@ __global__ void __launch_bounds__(256)
     for (int u = 0; u < NU; ++u) nvalid += __popc(__ballot_sync(FULL_MASK, ci[u] >= 0));
     float T32 = INFINITY;
 #pragma unroll
-    for (int p = 0; p < kTcParts; ++p) {
-        const float tp = surv_thr[q * kTcParts + p];
+    for (int p = 0; p < kTcLists; ++p) {
+        const float tp = surv_thr[q * kTcLists + p];
         if (tp < 1.0e38f) T32 = fminf(T32, tp);  // a list that never filled (or filled with padding) excludes nothing
     }
     const double T = (double)T32;
