@@ -32,7 +32,7 @@ if ROOT not in sys.path:
 import numpy as np  # noqa: E402
 
 NCU_DRAM_BYTES_PER_LAUNCH = {"c4lite": 978.515968e6 + 182.364672e6}          # knn_filter_kernel (FFMA2 scan)
-NCU_DRAM_BYTES_PER_LAUNCH_TC = {"c4lite": 5.137574e9 + 277.608704e6}       # knn_tc_kernel (tensor-core scan)
+NCU_DRAM_BYTES_PER_LAUNCH_TC = {"c4lite": 5.530121e9 + 75.893248e6}        # knn_tc_kernel (tensor-core scan)
 
 METRIC = "PRM edges collision-checked/sec (kNN k=10 + vertex + edge checks per roadmap build step)"
 UNIT = "edges/s"
@@ -469,7 +469,7 @@ def main():
             "note": "the MMAs occupy about a quarter of the kernel; what bounds it is the CUDA-core epilogue that "
                     "reads every key out of tensor memory (tcgen05.ld), takes a min-tree per 32 keys and inserts the "
                     "takers (profiles/r1_summary.md, r1h)",
-            # dram__bytes_read.sum + dram__bytes_write.sum of one launch (profiles/r1i_ncu_full_knn_tc_raw.csv)
+            # dram__bytes_read.sum + dram__bytes_write.sum of one launch (profiles/r1j_ncu_full_knn_tc_raw.csv)
             "traffic": NCU_DRAM_BYTES_PER_LAUNCH_TC.get(args.workload) if world_size == 1 else None,
             "kernel_ms": knn_ms, "hbm": roofline["hbm"],
             # the same time expressed on the fp32 formulation's count (2*D flop per pair) against the FFMA2 peak:
