@@ -34,7 +34,7 @@ constexpr int kTcQueries = 128;                // queries per CTA = MMA M = TMEM
 #endif
 constexpr int kTcStages = MPB_TC_STAGES;       // shared-memory ring depth
 constexpr int kTcKeep = 16;                    // survivors per list
-constexpr int kTcParts = MPB_TC_PARTS;          // epilogue warps per TMEM lane quarter = lists per query
+constexpr int kTcParts = MPB_TC_PARTS;          // epilogue warps per TMEM lane quarter
 constexpr int kTcEpiWarps = 4 * kTcParts;      // warp w: lane quarter w & 3, part w >> 2 (8 / kTcParts chunks of 32 keys per tile)
 constexpr int kTcThreads = 32 * (kTcEpiWarps + 2);
 #ifndef MPB_TC_SHARED_LIST
@@ -167,7 +167,7 @@ struct TcSmem {
 
 // ---- the scan: 128 queries per CTA against every candidate tile --------------------------------------
 // Warps 0..15: epilogue (lane = query of TMEM lane quarter w & 3; part w >> 2 takes two of a tile's eight 32-key
-// chunks and keeps its own 16-entry list per query, so the four warps of a quarter never touch the same list).
+// chunks; the four warps of a quarter insert into one 16-entry list per query, one warp at a time per query).
 // Warp 16, one lane: MMA issue.  Warp 17, one lane: tile producer.
 template <int D>
 __global__ void __launch_bounds__(kTcThreads, 1)
