@@ -1,6 +1,8 @@
-"""The opt-in tensor-core form of the kNN filter (MPB200_KNN_TC=1; tcgen05.mma kind::tf32 on three-way split
-operands, accumulator in tensor memory) returns the same neighbours and bit-identical distances as the exact
-fp64 scan.  The switch is read once per process, so the check runs in a child process."""
+"""The tensor-core form of the kNN filter (tcgen05.mma kind::tf32 on split operands, accumulator in tensor
+memory) forced onto small sets with MPB200_KNN_TC=1, against the CPU oracle (nearest.py:74-85 restated in
+oracle/mp_oracle.c): same neighbours, bit-identical distances.  Includes inputs built to defeat an fp32 /
+TF32 filter, where the exactness certificate has to FAIL and the exact kernel has to take the query over.
+The switch is read once per process, so the checks run in a child process."""
 import os
 import subprocess
 import sys
@@ -15,32 +17,77 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CHILD = r"""
 import sys, numpy as np, torch
 sys.path.insert(0, %r)
+import oracle
 from motion_planners_b200 import _lib, ops
-# the switch took: the workspace now has room for the 96-byte-per-sample operand tiles
-assert _lib.lib().mpb_knn_workspace_bytes(30000, 3000, 7) > 30000 * 96
-for N, M, D, k, seed in [(30000, 3000, 7, 11, 0), (20011, 2500, 6, 11, 1), (9000, 1500, 3, 5, 2), (8192, 130, 2, 12, 3)]:
+oracle.use_all_cores()
+lib = _lib.lib()
+host = lambda t: t.cpu().numpy()
+
+for N, M, D, k, seed in [(30000, 3000, 7, 11, 0), (20011, 2500, 6, 11, 1), (9000, 1500, 3, 5, 2),
+                         (8192, 130, 2, 12, 3), (8193, 129, 7, 1, 4), (9000, 700, 5, 8, 5)]:
+    assert lib.mpb_knn_filter_kind(N, D, k) == 1, (N, D, k)
     rs = np.random.RandomState(seed)
-    x = torch.from_numpy(rs.uniform(size=(N, D))).cuda()
-    q = torch.cat([x[: M // 2], torch.from_numpy(rs.uniform(-0.1, 1.1, size=(M - M // 2, D))).cuda()])
+    X = rs.uniform(size=(N, D))
+    Q = np.concatenate([X[: M // 2], rs.uniform(-0.1, 1.1, size=(M - M // 2, D))])
     w = rs.uniform(0.5, 2.0, size=D)
+    x, q = torch.from_numpy(X).cuda(), torch.from_numpy(Q).cuda()
     stats = torch.zeros(2, dtype=torch.int64, device="cuda")
     index = ops.KnnIndex(x, w)
     idx, dist = index.search(q, k, float("inf"), stats=stats)
-    ref_idx, ref_dist = ops.knn(x, q, k, weights=w, method="f64")
-    assert torch.equal(idx, ref_idx) and torch.equal(dist, ref_dist), (N, D)
+    o_idx, o_dist = oracle.knn(X, Q, k, w)
+    assert (host(idx) == o_idx).all() and (host(dist) == o_dist).all(), (N, D)
     assert int(stats[0]) < M // 50, int(stats[0])        # the certificate holds for (almost) every query
     r = float(dist[:, k // 2].median())
     idx_r, dist_r = index.search(q, k, r)
-    ref_idx_r, ref_dist_r = ops.knn(x, q, k, weights=w, max_dist=r, method="f64")
-    assert torch.equal(idx_r, ref_idx_r) and torch.equal(dist_r, ref_dist_r), (N, D, "bounded")
+    o_idx_r, o_dist_r = oracle.knn(X, Q, k, w, r)
+    assert (host(idx_r) == o_idx_r).all() and (host(dist_r) == o_dist_r).all(), (N, D, "bounded")
+
+# -- the certificate's failing branch on the tensor path
+# (a) a cluster 1e-9 wide, off centre, inside a unit cloud: fp32 coordinates cannot tell its members apart
+rs = np.random.RandomState(5)
+N, D, k = 12000, 7, 11
+X = rs.uniform(size=(N, D))
+X[:4000] = 0.9 + 1e-9 * rs.uniform(size=(4000, D))
+assert lib.mpb_knn_filter_kind(N, D, k) == 1
+stats = torch.zeros(2, dtype=torch.int64, device="cuda")
+x = torch.from_numpy(X).cuda()
+idx, dist = ops.knn(x, x, k, stats=stats)
+o_idx, o_dist = oracle.knn(X, X, k)
+assert (host(idx) == o_idx).all() and (host(dist) == o_dist).all()
+assert int(stats[0]) >= 3000, int(stats[0])
+
+# (b) two groups 2e3 apart: the bounding-box centre sits 1e3 away from every sample, so the centred fp32
+# coordinates carry an absolute error near 6e-5 while neighbours are about 1e-4..1e-3 apart
+rs = np.random.RandomState(6)
+N, D, k = 16384, 6, 11
+X = 0.02 * rs.uniform(size=(N, D))
+X[N // 2:, 0] += 2000.0
+assert lib.mpb_knn_filter_kind(N, D, k) == 1
+stats = torch.zeros(2, dtype=torch.int64, device="cuda")
+x = torch.from_numpy(X).cuda()
+idx, dist = ops.knn(x, x, k, stats=stats)
+o_idx, o_dist = oracle.knn(X, X, k)
+assert (host(idx) == o_idx).all() and (host(dist) == o_dist).all()
+assert int(stats[0]) > 0, int(stats[0])
+
+# (c) mixed magnitudes per coordinate (weights 1e3 and 1e-3) and a bounded search
+rs = np.random.RandomState(7)
+N, D, k = 10000, 7, 12
+X = rs.uniform(size=(N, D))
+w = np.array([1e3, 1.0, 1e-3, 1.0, 30.0, 1.0, 0.1])
+x = torch.from_numpy(X).cuda()
+stats = torch.zeros(2, dtype=torch.int64, device="cuda")
+idx, dist = ops.knn(x, x[:3000], k, weights=w, stats=stats)
+o_idx, o_dist = oracle.knn(X, X[:3000], k, w)
+assert (host(idx) == o_idx).all() and (host(dist) == o_dist).all()
 print("TC_OK")
 """
 
 
-def test_tensor_core_filter_matches_exact_scan():
+def test_tensor_core_filter_matches_oracle():
     if not torch.cuda.is_available():
         pytest.skip("no CUDA device")
     env = dict(os.environ, MPB200_KNN_TC="1")
-    out = subprocess.run([sys.executable, "-c", CHILD % ROOT], env=env, capture_output=True, text=True, timeout=600)
+    out = subprocess.run([sys.executable, "-c", CHILD % ROOT], env=env, capture_output=True, text=True, timeout=900)
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
     assert "TC_OK" in out.stdout
