@@ -309,6 +309,23 @@ int mpb_roadmap_parents(const int64_t *nbr, const double *nbr_dist, const int32_
 #define MPB_KNN_KIND_EXACT 2
 int mpb_knn_filter_kind(int64_t n_samples, int dim, int k);
 
+/* Diagnostic for the tensor-core filter (no counterpart in the reference; scipy's cKDTree, nearest.py:81, has
+ * no filter pass).  The exactness certificate of mpb_knn_search budgets the rounding of a filter key --
+ * the TF32 split of the operands plus whatever tcgen05.mma kind::tf32 does inside its accumulator -- at
+ * 32 * 2^-22 * (R^2 + 2 |q^| R) (R: radius of the centred sample set, q^: centred query).  This call measures it:
+ * it prepares the workspace for `samples`, runs the scan's measuring build for `queries` against EVERY tile and
+ * compares each key read from tensor memory with the same expression evaluated in fp64 on the same fp32
+ * operands.  out (dev, 2 x u64): [0] = bit pattern of the double max |key_tc - key_fp64| / (R^2 + 2 |q^| R),
+ * [1] = pairs measured.  The budget holds iff out[0] <= 32 * 2^-22.  Cost: one fp64 key per pair.
+ * Needs a set the tensor-core scan serves (mpb_knn_filter_kind == MPB_KNN_KIND_TENSOR at k <= 12). */
+int mpb_knn_tc_key_error(const double *samples, int64_t n_samples, const double *queries, int64_t n_queries,
+                         int dim, const double *weights, void *workspace, size_t workspace_bytes,
+                         unsigned long long *out, void *stream);
+
+/* Kernels launched so far by the mpb_knn_* entry points on the calling host thread (a monotone counter;
+ * callers report differences).  No counterpart in the reference. */
+int mpb_knn_launch_count(void);
+
 /* ---- measurement helpers (not part of the planner path) ---------------------------------
  * Issue-rate micro-benchmarks used by bench.py for the roofline denominators: each thread
  * runs `iters` rounds of 8 independent dependent-FMA chains.  flops = 2 * 8 * iters *

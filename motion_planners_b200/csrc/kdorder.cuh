@@ -1,0 +1,305 @@
+// Spatial ordering of a point set for the tensor-core kNN scan (included by knn.cu, inside its anonymous
+// namespace, after KnnHeader).
+//
+// The scan of knn_tc.cuh skips every candidate tile whose bounding box is provably farther from a block of
+// queries than the block's current k-th distances.  That only pays when a tile (256 consecutive candidates)
+// and a query block (128 consecutive queries) are compact in space, so both sets are first brought into the
+// leaf order of a balanced k-d partition: `leaves` cells of floor/ceil(n / leaves) points each, obtained level
+// by level -- every level sorts the points of each current cell along one coordinate and cuts the cell into
+// 2^bits parts of equal leaf counts.  One level = one stable LSD radix sort of (cell id, coordinate) keys over
+// the whole array, so cells stay where they are and only their contents are reordered.  Everything is
+// stream-ordered device work on caller-provided scratch: no host round trip, no allocation, deterministic.
+//
+// The reference has no counterpart (scipy's cKDTree builds its own tree inside nearest.py:59-61); the order
+// only decides which tiles are visited, never what the search returns.
+#pragma once
+
+constexpr int kRsThreads = 256;                    // threads per block of the radix passes
+constexpr int kRsItems = 16;                       // keys per thread
+constexpr int kRsChunk = kRsThreads * kRsItems;    // keys per block
+constexpr int kKdMaxLevels = 8;
+constexpr int kKdCoordBits = 24;                   // leading bits of the order-preserving fp32 image kept in a key
+
+struct KdPlan {
+    int64_t n;            // points
+    int64_t leaves;       // cells at the end (each holds floor or ceil of n / leaves points)
+    int levels;           // sorts
+    int bits[kKdMaxLevels];   // level l cuts every cell 2^bits[l] ways along coordinate dim_order[l]
+    int leaf_bits;        // bits needed for a cell id
+};
+
+inline int ceil_log2_i64(int64_t v)
+{
+    int b = 0;
+    while (((int64_t)1 << b) < v) ++b;
+    return b;
+}
+
+inline KdPlan kd_plan(int64_t n, int64_t leaves, int D)
+{
+    KdPlan p;
+    p.n = n;
+    p.leaves = leaves < 1 ? 1 : leaves;
+    const int T = ceil_log2_i64(p.leaves);
+    int levels = T < D ? T : D;
+    if (levels > kKdMaxLevels) levels = kKdMaxLevels;
+    p.levels = levels;
+    for (int l = 0; l < kKdMaxLevels; ++l) p.bits[l] = 0;
+    for (int l = 0; l < levels; ++l) p.bits[l] = T / levels + (l < T % levels ? 1 : 0);
+    p.leaf_bits = T;
+    return p;
+}
+
+// first position of leaf j, and the leaf that holds position pos (leaf j = positions [floor(j n / L), floor((j+1) n / L)))
+__host__ __device__ inline int64_t kd_leaf_start(int64_t j, int64_t n, int64_t L) { return (j * n) / L; }
+__host__ __device__ inline int64_t kd_leaf_of(int64_t pos, int64_t n, int64_t L) { return ((pos + 1) * L - 1) / n; }
+
+// first leaf of the cell that holds leaf j after `depth` levels of cuts
+__device__ inline int64_t kd_cell_start(const KdPlan &p, int64_t j, int depth)
+{
+    int64_t s = 0, c = p.leaves;
+    for (int l = 0; l < depth; ++l) {
+        const int64_t w = (int64_t)1 << p.bits[l];
+        const int64_t r = j - s;
+        const int64_t i = ((r + 1) * w - 1) / c;          // child i covers leaves [floor(i c / w), floor((i+1) c / w))
+        const int64_t a = (i * c) / w, b = ((i + 1) * c) / w;
+        s += a;
+        c = b - a;
+    }
+    return s;
+}
+
+__device__ __forceinline__ uint32_t ord_f32(float f)
+{
+    const uint32_t u = __float_as_uint(f);
+    return (u >> 31) ? ~u : (u | 0x80000000u);
+}
+
+// coordinates ranked by extent of the sample set's bounding box, widest first (ties: lower coordinate)
+__global__ void kd_dim_order_kernel(KnnHeader *h, int D)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    double ext[MPB_MAX_DIM];
+    for (int d = 0; d < D; ++d) {
+        const double e = dec_f64(h->mm[MPB_MAX_DIM + d]) - dec_f64(h->mm[d]);
+        ext[d] = (e == e) ? e : 0.;
+    }
+    bool used[MPB_MAX_DIM];
+    for (int d = 0; d < D; ++d) used[d] = false;
+    for (int r = 0; r < D; ++r) {
+        int best = -1;
+        for (int d = 0; d < D; ++d)
+            if (!used[d] && (best < 0 || ext[d] > ext[best])) best = d;
+        used[best] = true;
+        h->dim_order[r] = best;
+    }
+}
+
+// keys of one level: (first leaf of the point's current cell) << 24 | leading bits of its centred coordinate
+template <int D>
+__global__ void __launch_bounds__(256)
+    kd_key_kernel(const double *__restrict__ x, Weights wt, const KnnHeader *__restrict__ h, KdPlan p, int level,
+                  const uint32_t *__restrict__ perm_in, uint64_t *__restrict__ keys, uint32_t *__restrict__ vals)
+{
+    const int64_t pos = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (pos >= p.n) return;
+    const uint32_t j = perm_in ? perm_in[pos] : (uint32_t)pos;
+    const int d = h->dim_order[level];
+    // dim_order is data; the coordinate is fetched by a runtime index from global memory, the weight from a
+    // small switch (wt lives in the kernel's parameter space)
+    double w = wt.w[0];
+#pragma unroll
+    for (int dd = 1; dd < D; ++dd)
+        if (dd == d) w = wt.w[dd];
+    const float f = (float)d_sub(d_mul(w, x[(int64_t)j * D + d]), h->center[d]);
+    const uint64_t cell = (uint64_t)kd_cell_start(p, kd_leaf_of(pos, p.n, p.leaves), level);
+    keys[pos] = (cell << kKdCoordBits) | (uint64_t)(ord_f32(f) >> (32 - kKdCoordBits));
+    vals[pos] = j;
+}
+
+// ---- stable LSD radix sort of (64-bit key, 32-bit value) pairs, one 8-bit digit per pass -----------------
+// Pass = digit histogram per block -> exclusive scan over (digit, block) -> stable scatter.  A block owns
+// kRsChunk consecutive keys; inside it warp w owns a contiguous run of them and walks it 32 keys at a time, so
+// "earlier in the array" is "earlier warp, earlier step, lower lane" and the rank of a key among the equal
+// digits before it comes from match.any + popcount.
+__global__ void __launch_bounds__(kRsThreads)
+    rs_hist_kernel(const uint64_t *__restrict__ keys, int64_t n, int shift, uint32_t *__restrict__ hist, int nblocks)
+{
+    __shared__ uint32_t h[256];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    const int64_t base = (int64_t)blockIdx.x * kRsChunk;
+#pragma unroll 4
+    for (int i = 0; i < kRsItems; ++i) {
+        const int64_t idx = base + (int64_t)i * kRsThreads + threadIdx.x;
+        if (idx < n) atomicAdd(&h[(uint32_t)(keys[idx] >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    hist[(size_t)threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];
+}
+
+// exclusive scan of hist[256 * nblocks] (digit-major), one block
+__global__ void __launch_bounds__(1024) rs_scan_kernel(uint32_t *__restrict__ hist, int total)
+{
+    __shared__ uint32_t warp_sums[32];
+    const int per = (total + 1023) / 1024;
+    const int lo = threadIdx.x * per;
+    const int hi = min(lo + per, total);
+    uint32_t s = 0;
+    for (int i = lo; i < hi; ++i) s += hist[i];
+    // block-wide exclusive scan of the per-thread sums
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t inc = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += v;
+    }
+    if (lane == 31) warp_sums[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t w = warp_sums[lane];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t v = __shfl_up_sync(0xffffffffu, w, o);
+            if (lane >= o) w += v;
+        }
+        warp_sums[lane] = w;
+    }
+    __syncthreads();
+    uint32_t run = inc - s + (warp > 0 ? warp_sums[warp - 1] : 0u);
+    for (int i = lo; i < hi; ++i) {
+        const uint32_t v = hist[i];
+        hist[i] = run;
+        run += v;
+    }
+}
+
+__global__ void __launch_bounds__(kRsThreads)
+    rs_scatter_kernel(const uint64_t *__restrict__ keys, const uint32_t *__restrict__ vals, int64_t n, int shift,
+                      const uint32_t *__restrict__ hist, int nblocks, uint64_t *__restrict__ out_keys,
+                      uint32_t *__restrict__ out_vals)
+{
+    constexpr int W = kRsThreads / 32;
+    constexpr int STEPS = kRsChunk / kRsThreads;           // 32-key steps per warp
+    __shared__ uint32_t wh[W][256];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < W * 256; i += kRsThreads) (&wh[0][0])[i] = 0;
+    __syncthreads();
+    const int64_t base = (int64_t)blockIdx.x * kRsChunk + (int64_t)warp * (STEPS * 32);
+    uint64_t k[STEPS];
+    uint32_t v[STEPS];
+#pragma unroll
+    for (int s = 0; s < STEPS; ++s) {
+        const int64_t idx = base + s * 32 + lane;
+        const bool in = idx < n;
+        k[s] = in ? keys[idx] : 0ull;
+        v[s] = in ? vals[idx] : 0u;
+        const uint32_t dg = in ? ((uint32_t)(k[s] >> shift) & 255u) : 256u;
+        const unsigned m = __match_any_sync(0xffffffffu, dg);
+        if (in && lane == __ffs(m) - 1) wh[warp][dg] += __popc(m);
+        __syncwarp();
+    }
+    __syncthreads();
+    {
+        const int d = threadIdx.x;                        // kRsThreads == 256 digits
+        uint32_t run = hist[(size_t)d * nblocks + blockIdx.x];
+#pragma unroll
+        for (int w = 0; w < W; ++w) {
+            const uint32_t t = wh[w][d];
+            wh[w][d] = run;
+            run += t;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int s = 0; s < STEPS; ++s) {
+        const int64_t idx = base + s * 32 + lane;
+        const bool in = idx < n;
+        const uint32_t dg = in ? ((uint32_t)(k[s] >> shift) & 255u) : 256u;
+        const unsigned m = __match_any_sync(0xffffffffu, dg);
+        if (in) {
+            const uint32_t pos = wh[warp][dg] + __popc(m & ((1u << lane) - 1u));
+            out_keys[pos] = k[s];
+            out_vals[pos] = v[s];
+        }
+        __syncwarp();
+        if (in && lane == __ffs(m) - 1) wh[warp][dg] += __popc(m);
+        __syncwarp();
+    }
+}
+static_assert(kRsThreads == 256, "one thread per digit in the scatter kernel");
+
+struct KdScratch {
+    uint64_t *keys[2];
+    uint32_t *vals[2];
+    uint32_t *hist;
+};
+
+inline size_t kd_scratch_bytes(int64_t n)
+{
+    const size_t nn = (size_t)(n > 0 ? n : 1);
+    const size_t nblocks = (nn + kRsChunk - 1) / kRsChunk;
+    return 2 * ((nn * 8 + 255) & ~(size_t)255) + 2 * ((nn * 4 + 255) & ~(size_t)255) + ((nblocks * 256 * 4 + 255) & ~(size_t)255);
+}
+
+inline KdScratch kd_scratch_at(void *base, int64_t n)
+{
+    const size_t nn = (size_t)(n > 0 ? n : 1);
+    const size_t kb = (nn * 8 + 255) & ~(size_t)255, vb = (nn * 4 + 255) & ~(size_t)255;
+    char *p = reinterpret_cast<char *>(base);
+    KdScratch s;
+    s.keys[0] = reinterpret_cast<uint64_t *>(p);
+    s.keys[1] = reinterpret_cast<uint64_t *>(p + kb);
+    s.vals[0] = reinterpret_cast<uint32_t *>(p + 2 * kb);
+    s.vals[1] = reinterpret_cast<uint32_t *>(p + 2 * kb + vb);
+    s.hist = reinterpret_cast<uint32_t *>(p + 2 * kb + 2 * vb);
+    return s;
+}
+
+// Sorts in place of the scratch: the pairs start in buffer `cur` and end in the returned buffer index.
+inline int rs_sort(const KdScratch &s, int cur, int64_t n, int key_bits, cudaStream_t st, int *launches)
+{
+    const int nblocks = (int)((n + kRsChunk - 1) / kRsChunk);
+    for (int shift = 0; shift < key_bits; shift += 8) {
+        rs_hist_kernel<<<nblocks, kRsThreads, 0, st>>>(s.keys[cur], n, shift, s.hist, nblocks);
+        rs_scan_kernel<<<1, 1024, 0, st>>>(s.hist, 256 * nblocks);
+        rs_scatter_kernel<<<nblocks, kRsThreads, 0, st>>>(s.keys[cur], s.vals[cur], n, shift, s.hist, nblocks,
+                                                          s.keys[cur ^ 1], s.vals[cur ^ 1]);
+        cur ^= 1;
+        if (launches) *launches += 3;
+    }
+    return cur;
+}
+
+// The whole ordering: after the call, *perm_out (one of the scratch value buffers) lists the point indices in
+// leaf order.  n >= 1.
+template <int D>
+int kd_order(const double *x, int64_t n, const Weights &wt, const KnnHeader *h, const KdPlan &plan, const KdScratch &s,
+             const uint32_t **perm_out, cudaStream_t st, int *launches)
+{
+    int cur = 0;
+    const unsigned blocks = (unsigned)((n + 255) / 256);
+    if (plan.levels == 0) {
+        // a single leaf: the identity order (written through the same kernel for uniformity)
+        KdPlan p1 = plan;
+        kd_key_kernel<D><<<blocks, 256, 0, st>>>(x, wt, h, p1, 0, nullptr, s.keys[0], s.vals[0]);
+        MPB_LAUNCH_CHECK();
+        if (launches) *launches += 1;
+        *perm_out = s.vals[0];
+        return MPB_OK;
+    }
+    for (int l = 0; l < plan.levels; ++l) {
+        const uint32_t *perm_in = (l == 0) ? nullptr : s.vals[cur];
+        // the keys are written into the buffer the sort will read; the values ride along
+        kd_key_kernel<D><<<blocks, 256, 0, st>>>(x, wt, h, plan, l, perm_in, s.keys[cur ^ 1], s.vals[cur ^ 1]);
+        MPB_LAUNCH_CHECK();
+        if (launches) *launches += 1;
+        cur ^= 1;
+        const int bits = kKdCoordBits + (l == 0 ? 0 : plan.leaf_bits);
+        cur = rs_sort(s, cur, n, bits, st, launches);
+        MPB_LAUNCH_CHECK();
+    }
+    *perm_out = s.vals[cur];
+    return MPB_OK;
+}

@@ -68,6 +68,7 @@ struct KnnHeader {
     double R;                                 // >= ||e - c|| and >= ||fl32(e - c)|| for every sample
     int fb_count;                             // queries queued for the exact kernel
     int pad;
+    int dim_order[MPB_MAX_DIM];               // coordinates by extent, widest first (kdorder.cuh)
 };
 static_assert(sizeof(KnnHeader) <= kHeaderBytes, "header overflows its slot");
 
@@ -132,6 +133,8 @@ __global__ void __launch_bounds__(256) knn_minmax_kernel(const double *__restric
         }
     }
 }
+
+__global__ void knn_set_stat_kernel(int64_t *stats, int64_t v) { stats[0] = v; }
 
 __global__ void knn_finalize_kernel(KnnHeader *h, int D)
 {
@@ -587,6 +590,10 @@ __global__ void __launch_bounds__(kWarps * 32, kBlocksPerSM)
     }
 }
 
+// kernels launched by the kNN entry points on this host thread (bench.py reports the count it claims)
+static thread_local int g_last_launches = 0;
+
+#include "kdorder.cuh"
 #include "knn_tc.cuh"
 
 // ------------------------------------------------------------------------------------------
@@ -634,16 +641,22 @@ bool use_tc(int64_t N, int D)
 }
 
 struct WsLayout {
-    size_t packed_off, packed_bytes, tc_off, tc_bytes, fb_off, fb_bytes, surv_off, surv_bytes, thr_off, thr_bytes, total;
-    int64_t n_tiles, n_pad, tc_tiles;
+    size_t packed_off, packed_bytes, tc_off, tc_bytes, slot_off, slot_bytes, box_off, box_bytes, fb_off, fb_bytes, surv_off,
+        surv_bytes, thr_off, thr_bytes, qord_off, qord_bytes, sort_off, sort_bytes, total;
+    int64_t n_tiles, n_pad, tc_tiles, tc_slots;
+    int box_stride;
 };
 
+// Workspace: [header][packed fp32 tiles][tensor-core tiles][tile slot -> sample index][tile boxes] -- written by
+// prepare, their offsets depend on the sample set only -- then [fallback list][survivors][thresholds][query
+// order][sort scratch], which belong to one search (prepare uses the sort scratch too, at its M = 0 offset).
 WsLayout ws_layout(int64_t N, int64_t M, int D, bool allow_tc = true)
 {
     WsLayout L;
     const int P = planes_for(D), TILE = tile_for(D);
     const bool tc = allow_tc && use_tc(N, D);
     const size_t m = (size_t)(M > 0 ? M : 1);
+    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
     L.n_tiles = (N + TILE - 1) / TILE;
     L.n_pad = L.n_tiles * TILE;
     L.packed_off = kHeaderBytes;
@@ -651,13 +664,26 @@ WsLayout ws_layout(int64_t N, int64_t M, int D, bool allow_tc = true)
     L.tc_tiles = tc ? (N + kTcTile - 1) / kTcTile : 0;
     L.tc_off = (L.packed_off + L.packed_bytes + 1023) & ~(size_t)1023;
     L.tc_bytes = (size_t)L.tc_tiles * kTcTileBytes;
-    L.fb_off = (L.tc_off + L.tc_bytes + 255) & ~(size_t)255;
-    L.fb_bytes = (m * sizeof(int) + 255) & ~(size_t)255;
+    L.slot_off = up(L.tc_off + L.tc_bytes);
+    L.slot_bytes = up((size_t)L.tc_tiles * kTcTile * sizeof(int));
+    L.box_stride = (int)((L.tc_tiles + 31) & ~(int64_t)31);
+    L.box_off = L.slot_off + L.slot_bytes;
+    L.box_bytes = up((size_t)16 * L.box_stride * sizeof(float));
+    L.fb_off = L.box_off + L.box_bytes;
+    L.fb_bytes = up(m * sizeof(int));
+    // query slots: blocks of 128; the sample set as its own query set uses the tiles' own slots
+    const int64_t own = (M == N) ? L.tc_tiles * kTcTile : 0;
+    const int64_t other = ((M + kTcQueries - 1) / kTcQueries) * kTcQueries;
+    L.tc_slots = tc ? (own > other ? own : other) : 0;
     L.surv_off = L.fb_off + L.fb_bytes;
-    L.surv_bytes = tc ? ((m * kTcSurvivors * sizeof(int) + 255) & ~(size_t)255) : 0;
+    L.surv_bytes = tc ? up((size_t)L.tc_slots * kTcSurvivors * sizeof(int)) : 0;
     L.thr_off = L.surv_off + L.surv_bytes;
-    L.thr_bytes = tc ? ((m * kTcLists * sizeof(float) + 255) & ~(size_t)255) : 0;
-    L.total = L.thr_off + L.thr_bytes;
+    L.thr_bytes = tc ? up((size_t)L.tc_slots * kTcLists * sizeof(float)) : 0;
+    L.qord_off = L.thr_off + L.thr_bytes;
+    L.qord_bytes = tc ? up((size_t)(other > 0 ? other : kTcQueries) * sizeof(int)) : 0;
+    L.sort_off = L.qord_off + L.qord_bytes;
+    L.sort_bytes = tc ? kd_scratch_bytes(N > M ? N : M) : 0;
+    L.total = L.sort_off + L.sort_bytes;
     return L;
 }
 
@@ -715,12 +741,27 @@ int launch_prepare(const double *x, int64_t N, const Weights &wt, void *ws, bool
         knn_pack_kernel<D><<<(unsigned)((L.n_pad + 255) / 256), 256, 0, st>>>(x, N, L.n_pad, wt, h, packed);
         MPB_LAUNCH_CHECK();
     }
+    g_last_launches += 2 + (N > 0 ? 1 : 0) + (L.n_pad > 0 ? 1 : 0);
     if constexpr (D <= kTcMaxDim) {
         if (L.tc_tiles > 0) {
-            unsigned char *tiles = reinterpret_cast<unsigned char *>(ws) + L.tc_off;
-            const int64_t npad = L.tc_tiles * kTcTile;
-            knn_tc_pack_kernel<D><<<(unsigned)((npad + 255) / 256), 256, 0, st>>>(x, N, npad, wt, h, tiles);
+            // k-d leaf order of the samples (two leaves of at most 128 per tile), then the operand tiles, the
+            // slot -> sample table and the tile boxes in that order
+            char *base = reinterpret_cast<char *>(ws);
+            unsigned char *tiles = reinterpret_cast<unsigned char *>(base + L.tc_off);
+            int *slot_idx = reinterpret_cast<int *>(base + L.slot_off);
+            float *boxes = reinterpret_cast<float *>(base + L.box_off);
+            kd_dim_order_kernel<<<1, 32, 0, st>>>(h, D);
             MPB_LAUNCH_CHECK();
+            const int64_t leaves = 2 * L.tc_tiles;
+            const KdPlan plan = kd_plan(N, leaves, D);
+            const KdScratch scratch = kd_scratch_at(base + L.sort_off, N);
+            const uint32_t *perm = nullptr;
+            int rc = kd_order<D>(x, N, wt, h, plan, scratch, &perm, st, &g_last_launches);
+            if (rc != MPB_OK) return rc;
+            knn_tc_pack_kernel<D><<<(unsigned)L.tc_tiles, kTcTile, 0, st>>>(x, N, leaves, perm, wt, h, tiles, slot_idx,
+                                                                         boxes, L.box_stride);
+            MPB_LAUNCH_CHECK();
+            g_last_launches += 2;
         }
     }
     return MPB_OK;
@@ -772,39 +813,95 @@ int launch_search(const double *x, int64_t N, const double *qs, int64_t M, const
                                   nullptr, st);
         if (rc0 != MPB_OK) return rc0;
         if (stats) {
-            const int64_t all = M;
-            MPB_CUDA_CHECK(cudaMemcpyAsync(stats, &all, sizeof(all), cudaMemcpyHostToDevice, st));
+            knn_set_stat_kernel<<<1, 1, 0, st>>>(stats, M);      // every query went to the exact scan
+            MPB_LAUNCH_CHECK();
         }
+        g_last_launches += 2;
         return MPB_OK;
     }
     MPB_CUDA_CHECK(cudaMemsetAsync(&h->fb_count, 0, sizeof(int), st));
     if constexpr (D <= kTcMaxDim) {
         if (L.tc_tiles > 0 && k <= kSmallListMaxK) {
-            // tensor-core scan -> kTcParts x 16 survivors per query -> exact re-rank + certificate -> exact re-do of the rest
+            // tensor-core scan over the tiles near each query block -> 16 survivors per query -> exact re-rank +
+            // certificate -> exact re-do of the rest
             char *base = reinterpret_cast<char *>(ws);
             const unsigned char *tiles = reinterpret_cast<const unsigned char *>(base + L.tc_off);
+            const int *slot_idx = reinterpret_cast<const int *>(base + L.slot_off);
+            const float *boxes = reinterpret_cast<const float *>(base + L.box_off);
             int *surv = reinterpret_cast<int *>(base + L.surv_off);
             float *sthr = reinterpret_cast<float *>(base + L.thr_off);
-            MPB_CUDA_CHECK(cudaFuncSetAttribute(knn_tc_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+            const int *qorder = slot_idx;                  // the sample set queried against itself: block = half tile
+            int64_t blocks = 2 * L.tc_tiles;
+            if (!(qs == x && M == N)) {
+                // any other query set gets its own k-d order, one leaf of at most 128 queries per block
+                blocks = (M + kTcQueries - 1) / kTcQueries;
+                const KdPlan plan = kd_plan(M, blocks, D);
+                const KdScratch scratch = kd_scratch_at(base + L.sort_off, N > M ? N : M);
+                const uint32_t *perm = nullptr;
+                int rc = kd_order<D>(qs, M, wt, h, plan, scratch, &perm, st, &g_last_launches);
+                if (rc != MPB_OK) return rc;
+                int *qo = reinterpret_cast<int *>(base + L.qord_off);
+                knn_tc_qorder_kernel<<<(unsigned)blocks, kTcQueries, 0, st>>>(M, blocks, perm, qo);
+                MPB_LAUNCH_CHECK();
+                g_last_launches += 1;
+                qorder = qo;
+            }
+            MPB_CUDA_CHECK(cudaFuncSetAttribute(knn_tc_kernel<D, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                 (int)TcSmem::BYTES));
-            const int64_t ctas = (M + kTcQueries - 1) / kTcQueries;
-            knn_tc_kernel<D><<<(unsigned)ctas, kTcThreads, TcSmem::BYTES, st>>>(qs, M, wt, tiles, (int)L.tc_tiles, h, surv, sthr);
+            knn_tc_kernel<D, false><<<(unsigned)blocks, kTcThreads, TcSmem::BYTES, st>>>(
+                qs, qorder, wt, tiles, (int)L.tc_tiles, boxes, L.box_stride, h, surv, sthr, nullptr, nullptr, nullptr);
             MPB_LAUNCH_CHECK();
-            const int64_t rthreads = M * 32;
-            knn_tc_rerank_kernel<D><<<(unsigned)((rthreads + 255) / 256), 256, 0, st>>>(x, N, qs, M, wt, k, r2, h, surv,
-                                                                                        sthr, fb, out_idx, out_dist);
+            const int64_t n_slots = blocks * kTcQueries;
+            const int64_t rthreads = n_slots * 32;
+            knn_tc_rerank_kernel<D><<<(unsigned)((rthreads + 255) / 256), 256, 0, st>>>(
+                x, N, qs, M, wt, k, r2, h, qorder, n_slots, slot_idx, surv, sthr, fb, out_idx, out_dist);
             MPB_LAUNCH_CHECK();
+            g_last_launches += 3;
             return launch_exact<D>(x, N, qs, M, wt, MPB_METRIC_KDTREE, k, r2, fb, &h->fb_count, out_idx, out_dist, stats,
                                    st);
         }
     }
     // 16 survivors per query leave a comfortable certificate margin up to k = 12 (a PRM's k + 1 = 11) and
     // halve the insertion work; larger k keeps 32
+    g_last_launches += 2;
     int rc = (k <= kSmallListMaxK)
                  ? launch_filter<D, Q, 16>(x, N, qs, M, wt, k, r2, packed, (int)L.n_tiles, h, fb, out_idx, out_dist, st)
                  : launch_filter<D, Q, 32>(x, N, qs, M, wt, k, r2, packed, (int)L.n_tiles, h, fb, out_idx, out_dist, st);
     if (rc != MPB_OK) return rc;
     return launch_exact<D>(x, N, qs, M, wt, MPB_METRIC_KDTREE, k, r2, fb, &h->fb_count, out_idx, out_dist, stats, st);
+}
+
+// measuring build of the tensor-core scan (mpb_knn_tc_key_error): prepared workspace in, two counters out
+template <int D>
+int launch_tc_diag(const double *x, int64_t N, const double *qs, int64_t M, const Weights &wt, void *ws,
+                   unsigned long long *out, cudaStream_t st)
+{
+    if constexpr (D <= kTcMaxDim) {
+        const WsLayout L = ws_layout(N, M, D, true);
+        if (L.tc_tiles == 0) return MPB_EINVAL;
+        KnnHeader *h = reinterpret_cast<KnnHeader *>(ws);
+        char *base = reinterpret_cast<char *>(ws);
+        const int64_t blocks = (M + kTcQueries - 1) / kTcQueries;
+        const KdPlan plan = kd_plan(M, blocks, D);
+        const KdScratch scratch = kd_scratch_at(base + L.sort_off, N > M ? N : M);
+        const uint32_t *perm = nullptr;
+        int rc = kd_order<D>(qs, M, wt, h, plan, scratch, &perm, st, &g_last_launches);
+        if (rc != MPB_OK) return rc;
+        int *qo = reinterpret_cast<int *>(base + L.qord_off);
+        knn_tc_qorder_kernel<<<(unsigned)blocks, kTcQueries, 0, st>>>(M, blocks, perm, qo);
+        MPB_LAUNCH_CHECK();
+        MPB_CUDA_CHECK(cudaMemsetAsync(out, 0, 2 * sizeof(unsigned long long), st));
+        MPB_CUDA_CHECK(cudaFuncSetAttribute(knn_tc_kernel<D, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)TcSmem::BYTES));
+        knn_tc_kernel<D, true><<<(unsigned)blocks, kTcThreads, TcSmem::BYTES, st>>>(
+            qs, qo, wt, reinterpret_cast<const unsigned char *>(base + L.tc_off), (int)L.tc_tiles,
+            reinterpret_cast<const float *>(base + L.box_off), L.box_stride, h, nullptr, nullptr, x,
+            reinterpret_cast<const int *>(base + L.slot_off), out);
+        MPB_LAUNCH_CHECK();
+        return MPB_OK;
+    } else {
+        return MPB_EINVAL;
+    }
 }
 
 int dispatch_exact(int D, const double *x, int64_t N, const double *qs, int64_t M, const Weights &wt, int metric, int k,
@@ -909,6 +1006,28 @@ MPB_API int mpb_knn_search(const double *samples, int64_t n_samples, const doubl
     return dispatch_search(dim, samples, n_samples, queries, n_queries, make_weights(weights, dim), k,
                            max_dist * max_dist, workspace, true, out_idx, out_dist, stats, (cudaStream_t)stream);
 }
+
+MPB_API int mpb_knn_tc_key_error(const double *samples, int64_t n_samples, const double *queries, int64_t n_queries,
+                                 int dim, const double *weights, void *workspace, size_t workspace_bytes,
+                                 unsigned long long *out, void *stream)
+{
+    MPB_REQUIRE(dim >= 1 && dim <= kTcMaxDim, "mpb_knn_tc_key_error: the tensor-core scan serves dim 1..%d", kTcMaxDim);
+    MPB_REQUIRE(samples && queries && out && n_samples > 0 && n_queries > 0, "mpb_knn_tc_key_error: empty input");
+    MPB_REQUIRE(n_samples < 2147483647LL && n_queries < 2147483647LL, "mpb_knn_tc_key_error: too many points");
+    MPB_REQUIRE(use_tc(n_samples, dim), "mpb_knn_tc_key_error: the tensor-core scan does not serve %lld samples at "
+                "dim %d under the current policy (MPB200_KNN_TC)", (long long)n_samples, dim);
+    int rc = check_ws("mpb_knn_tc_key_error", workspace, workspace_bytes, n_samples, n_queries, dim);
+    if (rc != MPB_OK) return rc;
+    const Weights wt = make_weights(weights, dim);
+    rc = dispatch_prepare(dim, samples, n_samples, wt, workspace, true, (cudaStream_t)stream);
+    if (rc != MPB_OK) return rc;
+#define CALL(DD) launch_tc_diag<DD>(samples, n_samples, queries, n_queries, wt, workspace, out, (cudaStream_t)stream)
+    MPB_DISPATCH_DIM(dim, CALL)
+#undef CALL
+    return MPB_EINVAL;
+}
+
+MPB_API int mpb_knn_launch_count(void) { return g_last_launches; }
 
 // prepare + search on one workspace; `allow_tc` = the workspace was sized with room for the tensor-core tiles
 static int filter_on_workspace(const char *who, const double *samples, int64_t n_samples, const double *queries,

@@ -15,6 +15,14 @@
 // plain register and the 256 keys of a tile come to it through tcgen05.ld; a producer thread streams candidate
 // tiles (prepared in the operand's canonical shared-memory image, so a tile is one 1-D bulk copy) through a
 // ring, one thread issues the MMAs into a double-buffered TMEM accumulator (2 x 256 columns).
+//
+// Which tiles a CTA scans: samples and queries are first brought into the leaf order of a balanced k-d partition
+// (kdorder.cuh), so a tile is a compact cell with a known fp32 bounding box and the 128 queries of a CTA are
+// neighbours in space.  A CTA visits its nearest tile first, then, in rounds, the tiles whose box lies closer to
+// the block of queries than the largest current k-th distance in the block -- nearest box first, re-checked
+// against the shrinking distances just before each copy is issued.  A skipped tile cannot hold a neighbour of any
+// query of the block, and the exactness certificate (knn_tc_rerank_kernel) is unchanged: the results stay bit
+// for bit those of the full scan.  At 1M uniform 7-DoF samples a CTA reads about 6 % of the tiles.
 #pragma once
 
 constexpr int kTcK = 24;                       // operand columns (D <= 7)
@@ -47,6 +55,9 @@ constexpr uint32_t kTcSbo = (kTcK / 4) * 128;  // bytes between 8-row groups
 constexpr int kTcTileBytes = (kTcTile / 8) * (int)kTcSbo;      // 24576
 constexpr int kTcQueryBytes = (kTcQueries / 8) * (int)kTcSbo;  // 12288
 constexpr int kTcMaxDim = 7;
+constexpr int kTcListCap = 2048;                // candidate tiles planned per round (shared-memory list)
+constexpr int kTcHalf = kTcTile / 2;            // points per k-d leaf: a tile is two leaves, a query block one
+static_assert(kTcHalf == kTcQueries, "a query block of the sample set itself is one half tile");
 
 // byte offset of (row r, column kk) in an operand image: K-major, no swizzle (8 x 16-byte core matrices)
 __host__ __device__ inline uint32_t tc_offset(int r, int kk)
@@ -113,28 +124,45 @@ __device__ __forceinline__ void tmem_ld32(uint32_t (&v)[32], uint32_t taddr)
         : "r"(taddr));
 }
 
+
 // ---- candidate tiles in the operand image ------------------------------------------------------------
+// One block per tile.  Tile t holds k-d leaves 2t and 2t+1 of the sample order (at most 128 points each, slot
+// 128 * half + i); unused slots carry a huge norm and slot_idx = -1.  The block also writes the tile's bounding
+// box over the centred fp32 coordinates it packs (exactly the values the scan multiplies), plane-major:
+// tile_box[d * stride + t] = min, tile_box[(8 + d) * stride + t] = max.
 template <int D>
-__global__ void __launch_bounds__(256)
-    knn_tc_pack_kernel(const double *__restrict__ x, int64_t N, int64_t Npad, Weights wt, const KnnHeader *__restrict__ h,
-                       unsigned char *__restrict__ tiles)
+__global__ void __launch_bounds__(kTcTile)
+    knn_tc_pack_kernel(const double *__restrict__ x, int64_t N, int64_t leaves, const uint32_t *__restrict__ perm,
+                       Weights wt, const KnnHeader *__restrict__ h, unsigned char *__restrict__ tiles,
+                       int *__restrict__ slot_idx, float *__restrict__ tile_box, int box_stride)
 {
     static_assert(D <= kTcMaxDim, "three k-steps hold up to seven coordinates");
-    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= Npad) return;
-    float row[kTcK];
+    __shared__ float red[kTcTile / 32][2][8];
+    const int64_t t = blockIdx.x;
+    const int r = threadIdx.x, lane = r & 31, warp = r >> 5;
+    const int64_t leaf = 2 * t + (r >> 7);
+    const int i = r & (kTcHalf - 1);
+    int64_t j = -1;
+    if (leaf < leaves) {
+        const int64_t start = kd_leaf_start(leaf, N, leaves);
+        const int64_t cnt = kd_leaf_start(leaf + 1, N, leaves) - start;
+        if (i < cnt) j = (int64_t)perm[start + i];
+    }
+    float row[kTcK], f[D];
 #pragma unroll
-    for (int i = 0; i < kTcK; ++i) row[i] = 0.f;
-    if (j < N) {
+    for (int c = 0; c < kTcK; ++c) row[c] = 0.f;
+#pragma unroll
+    for (int d = 0; d < D; ++d) f[d] = 0.f;
+    if (j >= 0) {
         double n2 = 0.;
 #pragma unroll
         for (int d = 0; d < D; ++d) {
             const double e = d_mul(wt.w[d], x[j * D + d]);
-            const float f = (float)d_sub(e, h->center[d]);
-            n2 += (double)f * (double)f;
-            const float hi = tf32_rn(f);
+            f[d] = (float)d_sub(e, h->center[d]);
+            n2 += (double)f[d] * (double)f[d];
+            const float hi = tf32_rn(f[d]);
             row[d] = hi;
-            row[8 + d] = tf32_rn(f - hi);      // f - hi is exact in fp32
+            row[8 + d] = tf32_rn(f[d] - hi);      // f - hi is exact in fp32
             row[16 + d] = hi;
         }
         const float n = (float)n2;
@@ -142,16 +170,63 @@ __global__ void __launch_bounds__(256)
         row[7] = nh;
         row[15] = tf32_rn(n - nh);
     } else {
-        row[7] = 3.0e38f;                      // padding never qualifies (finite: no inf - inf inside the MMA)
+        row[7] = 3.0e38f;                          // padding never qualifies (finite: no inf - inf inside the MMA)
     }
-    const int64_t t = j / kTcTile;
-    const int r = (int)(j - t * kTcTile);
     unsigned char *base = tiles + (size_t)t * kTcTileBytes;
 #pragma unroll
     for (int c = 0; c < kTcK / 4; ++c)
         *reinterpret_cast<float4 *>(base + tc_offset(r, 4 * c)) =
             make_float4(row[4 * c], row[4 * c + 1], row[4 * c + 2], row[4 * c + 3]);
+    slot_idx[t * kTcTile + r] = (int)j;
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        float lo = (j >= 0) ? f[d] : INFINITY, hi = (j >= 0) ? f[d] : -INFINITY;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            lo = fminf(lo, __shfl_xor_sync(FULL_MASK, lo, o));
+            hi = fmaxf(hi, __shfl_xor_sync(FULL_MASK, hi, o));
+        }
+        if (lane == 0) {
+            red[warp][0][d] = lo;
+            red[warp][1][d] = hi;
+        }
+    }
+    __syncthreads();
+    if (r < 16 && (r & 7) < D) {
+        const int side = r >> 3, d = r & 7;
+        float v = red[0][side][d];
+#pragma unroll
+        for (int w = 1; w < kTcTile / 32; ++w) v = side ? fmaxf(v, red[w][1][d]) : fminf(v, red[w][0][d]);
+        tile_box[(size_t)r * box_stride + t] = v;
+    }
 }
+
+// query blocks of a query set that is not the sample set: block g = leaf g of the queries' own k-d order
+__global__ void __launch_bounds__(kTcQueries)
+    knn_tc_qorder_kernel(int64_t M, int64_t leaves, const uint32_t *__restrict__ perm, int *__restrict__ qorder)
+{
+    const int64_t g = blockIdx.x;
+    const int64_t start = kd_leaf_start(g, M, leaves);
+    const int64_t cnt = kd_leaf_start(g + 1, M, leaves) - start;
+    const int i = threadIdx.x;
+    qorder[g * kTcQueries + i] = (i < cnt) ? (int)perm[start + i] : -1;
+}
+
+struct TcCtl {                 // per-CTA control block in shared memory
+    float qlo[8], qhi[8];      // bounding box of the block's centred fp32 queries
+    float red_f[32];
+    unsigned long long red_u[32];
+    unsigned long long lo_key; // every tile with (lower bound, index) <= lo_key has been handled
+    int slot_tile[kTcStages];  // tile in each ring slot (-1: end of round)
+    int acc_tile[2];           // tile in each accumulator (-1: end of round)
+    int list_n;                // tiles planned for the coming round
+    int list_all;              // candidates counted by the last collection pass (may exceed the list)
+    int home;                  // the tile nearest to the block
+    int cursor;                // tiles below this index were all visited (rounds before any threshold existed)
+    int has_lo;
+    int final_round;           // the planned round covers everything that is left
+    float rmax2;
+};
 
 struct TcSmem {
     static constexpr int A_OFF = 0;
@@ -161,27 +236,62 @@ struct TcSmem {
     static constexpr int SCR_OFF = LI_OFF + kTcSurvivors * kTcQueries * 4;   // [epilogue warp][32 lanes][33]
     static constexpr int THR_OFF = SCR_OFF + kTcEpiWarps * 32 * 33 * 4;        // [part][128] published thresholds
     static constexpr int LOCK_OFF = THR_OFF + kTcLists * kTcQueries * 4;       // [128] list locks (shared-list build)
-    static constexpr int BAR_OFF = LOCK_OFF + kTcQueries * 4;
+    static constexpr int NQ_OFF = LOCK_OFF + kTcQueries * 4;                   // [128] |q^|^2, rounded up
+    static constexpr int LIST_OFF = NQ_OFF + kTcQueries * 4;                   // [kTcListCap] (lower bound, tile) keys
+    static constexpr int CTL_OFF = LIST_OFF + kTcListCap * 8;
+    static constexpr int BAR_OFF = CTL_OFF + 640;
     static constexpr int BYTES = BAR_OFF + 256;
 };
+static_assert(sizeof(TcCtl) <= 640, "control block overflows its slot");
+static_assert(TcSmem::LIST_OFF % 8 == 0 && TcSmem::CTL_OFF % 8 == 0 && TcSmem::BAR_OFF % 8 == 0, "alignment");
+static_assert(TcSmem::BYTES <= 227 * 1024, "shared memory per CTA");
+static_assert(MPB_TC_SHARED_LIST == 1, "the pruned scan reads the block's thresholds from the shared lists");
 
-// ---- the scan: 128 queries per CTA against every candidate tile --------------------------------------
+// squared k-th distance implied by a list threshold (a key is d^2 - |q^|^2), rounded up; +inf stays +inf
+__device__ __forceinline__ float tc_r2_of(float thr, float nq2_up)
+{
+    return fmaxf(thr + nq2_up, 0.f) * 1.000001f + 1e-37f;
+}
+
+// centred fp32 image of query slot `slot` (an unused slot of the block repeats the block's first query)
+template <int D>
+__device__ __forceinline__ bool tc_query_hat(const double *__restrict__ qs, const int *__restrict__ qorder, int64_t slot0,
+                                             int q, const Weights &wt, const KnnHeader *__restrict__ h, float (&f)[D])
+{
+    int qi = qorder[slot0 + q];
+    const bool valid = qi >= 0;
+    if (!valid) qi = qorder[slot0];
+#pragma unroll
+    for (int d = 0; d < D; ++d) f[d] = (float)d_sub(d_mul(wt.w[d], qs[(int64_t)qi * D + d]), h->center[d]);
+    return valid;
+}
+
+// ---- the scan: one block of (at most) 128 queries per CTA against the tiles that can matter to it ------------
 // Warps 0..15: epilogue (lane = query of TMEM lane quarter w & 3; part w >> 2 takes two of a tile's eight 32-key
 // chunks; the four warps of a quarter insert into one 16-entry list per query, one warp at a time per query).
-// Warp 16, one lane: MMA issue.  Warp 17, one lane: tile producer.
-template <int D>
+// Warp 16, one lane: MMA issue.  Warp 17: tile producer (all lanes follow the list, lane 0 issues the copies).
+// Between rounds every warp of the CTA plans the next round together.
+// DIAG = true is the measuring build behind mpb_knn_tc_key_error: every tile is visited, nothing is inserted,
+// and each key read from tensor memory is compared with the same expression evaluated in fp64.
+template <int D, bool DIAG>
 __global__ void __launch_bounds__(kTcThreads, 1)
-    knn_tc_kernel(const double *__restrict__ qs, int64_t M, Weights wt, const unsigned char *__restrict__ tiles,
-                  int n_tiles, const KnnHeader *__restrict__ h, int *__restrict__ surv_idx, float *__restrict__ surv_thr)
+    knn_tc_kernel(const double *__restrict__ qs, const int *__restrict__ qorder, Weights wt,
+                  const unsigned char *__restrict__ tiles, int n_tiles, const float *__restrict__ tile_box,
+                  int box_stride, const KnnHeader *__restrict__ h, int *__restrict__ surv_idx,
+                  float *__restrict__ surv_thr, const double *__restrict__ x, const int *__restrict__ slot_idx,
+                  unsigned long long *__restrict__ diag)
 {
     extern __shared__ __align__(1024) unsigned char smem[];
     unsigned char *sA = smem + TcSmem::A_OFF;
     unsigned char *sB = smem + TcSmem::B_OFF;
-    float *lk = reinterpret_cast<float *>(smem + TcSmem::LK_OFF);      // [part][128][kTcKeep] sorted keys per query
-    int *li = reinterpret_cast<int *>(smem + TcSmem::LI_OFF);          // [part][128][kTcKeep] their candidate indices
+    float *lk = reinterpret_cast<float *>(smem + TcSmem::LK_OFF);      // [128][kTcKeep] sorted keys per query
+    int *li = reinterpret_cast<int *>(smem + TcSmem::LI_OFF);          // [128][kTcKeep] their candidate slots
     float *scr = reinterpret_cast<float *>(smem + TcSmem::SCR_OFF);
     float *sthr = reinterpret_cast<float *>(smem + TcSmem::THR_OFF);
     int *locks = reinterpret_cast<int *>(smem + TcSmem::LOCK_OFF);
+    float *nq2s = reinterpret_cast<float *>(smem + TcSmem::NQ_OFF);
+    unsigned long long *list = reinterpret_cast<unsigned long long *>(smem + TcSmem::LIST_OFF);
+    TcCtl *ctl = reinterpret_cast<TcCtl *>(smem + TcSmem::CTL_OFF);
     uint64_t *full = reinterpret_cast<uint64_t *>(smem + TcSmem::BAR_OFF);
     uint64_t *empty = full + kTcStages;
     uint64_t *tfull = empty + kTcStages;
@@ -189,21 +299,23 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty + 2);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int64_t q0 = (int64_t)blockIdx.x * kTcQueries;
+    const int64_t slot0 = (int64_t)blockIdx.x * kTcQueries;
 
-    if (tid < kTcQueries) {            // this thread's query row of the A operand, and its empty list
-        int64_t q = q0 + tid;
-        if (q >= M) q = M - 1;
+    if (tid < kTcQueries) {            // this thread's query row of the A operand, its norm, the block's box
+        float f[D];
+        tc_query_hat<D>(qs, qorder, slot0, tid, wt, h, f);
         float row[kTcK];
 #pragma unroll
         for (int i = 0; i < kTcK; ++i) row[i] = 0.f;
+        double n2 = 0.;
 #pragma unroll
         for (int d = 0; d < D; ++d) {
-            const float f = -2.f * (float)d_sub(d_mul(wt.w[d], qs[q * D + d]), h->center[d]);
-            const float hi = tf32_rn(f);
+            n2 += (double)f[d] * (double)f[d];
+            const float m2 = -2.f * f[d];
+            const float hi = tf32_rn(m2);
             row[d] = hi;
             row[8 + d] = hi;
-            row[16 + d] = tf32_rn(f - hi);
+            row[16 + d] = tf32_rn(m2 - hi);
         }
         row[7] = 1.f;
         row[15] = 1.f;
@@ -211,6 +323,20 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         for (int c = 0; c < kTcK / 4; ++c)
             *reinterpret_cast<float4 *>(sA + tc_offset(tid, 4 * c)) =
                 make_float4(row[4 * c], row[4 * c + 1], row[4 * c + 2], row[4 * c + 3]);
+        nq2s[tid] = (float)n2 * 1.000001f;
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            float lo = f[d], hi = f[d];            // an unused slot repeats a real query: the box is unchanged
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                lo = fminf(lo, __shfl_xor_sync(FULL_MASK, lo, o));
+                hi = fmaxf(hi, __shfl_xor_sync(FULL_MASK, hi, o));
+            }
+            if (lane == 0) {
+                scr[warp * 16 + d] = lo;
+                scr[warp * 16 + 8 + d] = hi;
+            }
+        }
     }
     for (int i = tid; i < kTcSurvivors * kTcQueries; i += kTcThreads) {
         lk[i] = INFINITY;
@@ -224,10 +350,14 @@ __global__ void __launch_bounds__(kTcThreads, 1)
             mbar_init(&empty[s], 1);
         }
         for (int b = 0; b < 2; ++b) {
-            mbar_init(&tfull[b], 1);
+            mbar_init(&tfull[b], 2);               // the MMAs' commit + the issuing thread's own arrival
             mbar_init(&tempty[b], kTcEpiWarps);
         }
         mbar_fence_init();
+        ctl->cursor = 0;
+        ctl->has_lo = 0;
+        ctl->lo_key = 0ull;
+        ctl->final_round = 0;
     }
     if (warp == kTcEpiWarps) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
@@ -240,155 +370,368 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem = *tmem_slot;
 
-    if (warp == kTcEpiWarps + 1) {
-        // ---- producer: one bulk copy per tile
-        if (lane == 0) {
-            for (int i = 0; i < n_tiles; ++i) {
-                const int s = i % kTcStages;
-                if (i >= kTcStages) mbar_wait_backoff(&empty[s], (uint32_t)((i / kTcStages - 1) & 1));
-                mbar_arrive_expect_tx(&full[s], kTcTileBytes);
-                bulk_copy_g2s(sB + (size_t)s * kTcTileBytes, tiles + (size_t)i * kTcTileBytes, kTcTileBytes, &full[s]);
-            }
+    // ---- the block's box, and the lower bound of the squared distance from it to a tile's box
+    float qlo[D], qhi[D];
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        qlo[d] = fminf(fminf(scr[d], scr[16 + d]), fminf(scr[32 + d], scr[48 + d]));
+        qhi[d] = fmaxf(fmaxf(scr[8 + d], scr[24 + d]), fmaxf(scr[40 + d], scr[56 + d]));
+    }
+    // computed in fp32 and scaled down past its own rounding (D + 3 operations of 2^-24 each), so it never
+    // exceeds the true box-to-box distance; the boxes are exact (min / max of the very values the MMA reads)
+    auto tile_lb = [&](int t) -> float {
+        float s = 0.f;
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            const float blo = tile_box[(size_t)d * box_stride + t], bhi = tile_box[(size_t)(8 + d) * box_stride + t];
+            const float gap = fmaxf(fmaxf(blo - qhi[d], qlo[d] - bhi), 0.f);
+            s = __fmaf_rn(gap, gap, s);
         }
-    } else if (warp == kTcEpiWarps) {
-        // ---- MMA issue: three k-steps per tile into accumulator i & 1
-        if (lane == 0) {
-            // D = f32, A = B = tf32, both K-major, N = 256, M = 128
-            constexpr uint32_t idesc =
-                (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kTcTile >> 3) << 17) | ((uint32_t)(kTcQueries >> 4) << 24);
-            const uint32_t a_addr = smem_u32(sA);
-            for (int i = 0; i < n_tiles; ++i) {
-                const int s = i % kTcStages, b = i & 1;
-                mbar_wait_backoff(&full[s], (uint32_t)((i / kTcStages) & 1));
-                if (i >= 2) mbar_wait_backoff(&tempty[b], (uint32_t)((i / 2 - 1) & 1));
-                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t b_addr = smem_u32(sB + (size_t)s * kTcTileBytes);
-                const uint32_t d_addr = tmem + (uint32_t)(b * kTcTile);
+        return s * 0.999998f;
+    };
+    auto key_of = [](float lb, int t) -> unsigned long long {
+        return ((unsigned long long)__float_as_uint(lb) << 32) | (unsigned long long)(uint32_t)t;
+    };
+
+    // ---- round 0: the nearest tile alone (ties: lowest index); it gives every query of the block a first list
+    {
+        unsigned long long best = ~0ull;
+        for (int t = tid; t < n_tiles; t += kTcThreads) best = min(best, key_of(tile_lb(t), t));
 #pragma unroll
-                for (int ks = 0; ks < kTcK / 8; ++ks) {
-                    const uint64_t da = tc_desc(a_addr + ks * 2 * kTcLbo);
-                    const uint64_t db = tc_desc(b_addr + ks * 2 * kTcLbo);
-                    const uint32_t acc = ks > 0 ? 1u : 0u;
-                    asm volatile(
-                        "{\n .reg .pred p;\n setp.ne.b32 p, %4, 0;\n"
-                        " tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n}"
-                        ::"r"(d_addr), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
-                }
-                // both commits track every MMA issued so far: the ring slot is free, the accumulator is ready
-                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
-                             ::"r"(smem_u32(&empty[s])) : "memory");
-                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
-                             ::"r"(smem_u32(&tfull[b])) : "memory");
-            }
+        for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(FULL_MASK, best, o));
+        if (lane == 0) ctl->red_u[warp] = best;
+        __syncthreads();
+        if (tid == 0) {
+            unsigned long long b = ctl->red_u[0];
+            for (int w = 1; w < kTcThreads / 32; ++w) b = min(b, ctl->red_u[w]);
+            ctl->home = (int)(uint32_t)b;
+            list[0] = b;
+            ctl->list_n = 1;
         }
-    } else {
-        // ---- epilogue: lane = query; this warp's part of every tile is two chunks of 32 keys
-        const int quarter = warp & 3, part = warp >> 2;
-        const int q = quarter * 32 + lane;
-        float thr = INFINITY;
-        const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
-        const int my_list = MPB_TC_SHARED_LIST ? 0 : part;
-        float *lkp = lk + my_list * kTcKeep * kTcQueries;
-        int *lip = li + my_list * kTcKeep * kTcQueries;
-        // The 32 keys a lane just received are examined with one min-tree.  When some lane's minimum beats its
-        // threshold, the flagged lanes park their keys in the warp's scratch rows, and each flagged lane is then
-        // served by the WHOLE warp: lane j reads key j of that row, one ballot finds the takers, and each taker is
-        // inserted into the query's shared-memory list by lanes 0..15 side by side.  (A lane-private walk over
-        // the 32 keys makes every lane of the warp wait for it, and at 1M candidates one chunk in five has a
-        // flagged lane: profiles/r1_summary.md.)
-        float *rows = scr + warp * 32 * 33;
-        auto examine = [&](const uint32_t (&v)[32], int cbase) {
-            float g[4];        // minima of the four groups of eight keys
+        __syncthreads();
+    }
+    const int home = ctl->home;
+
+    // ---- planning of the next round, by the whole CTA (uniform control flow; ends with list / list_n ready)
+    auto plan_round = [&]() {
+        // largest squared k-th distance in the block right now
+        if (tid < kTcQueries) {
+            float r = tc_r2_of(lk[tid * kTcKeep + kTcKeep - 1], nq2s[tid]);
 #pragma unroll
-            for (int gi = 0; gi < 4; ++gi) {
-                g[gi] = __uint_as_float(v[8 * gi]);
-#pragma unroll
-                for (int j = 1; j < 8; ++j) g[gi] = fminf(g[gi], __uint_as_float(v[8 * gi + j]));
+            for (int o = 16; o > 0; o >>= 1) r = fmaxf(r, __shfl_xor_sync(FULL_MASK, r, o));
+            if (lane == 0) ctl->red_f[warp] = r;
+        }
+        __syncthreads();
+        const float rmax2 = fmaxf(fmaxf(ctl->red_f[0], ctl->red_f[1]), fmaxf(ctl->red_f[2], ctl->red_f[3]));
+        const int cursor = ctl->cursor;
+        const bool has_lo = ctl->has_lo != 0;
+        const unsigned long long lo_key = ctl->lo_key;
+        int n = 0;
+        if (!(rmax2 < 3.0e38f)) {
+            // some list is not full yet (or holds padding): no bound to prune with; take the next tiles by index
+            const int end = min(n_tiles, cursor + kTcListCap);
+            if (tid == 0) ctl->list_all = 0;
+            __syncthreads();
+            for (int t = cursor + tid; t < end; t += kTcThreads)
+                if (t != home) list[atomicAdd(&ctl->list_all, 1)] = key_of(0.f, t);
+            __syncthreads();
+            n = ctl->list_all;
+            if (tid == 0) {
+                ctl->cursor = end;
+                ctl->final_round = (end >= n_tiles) ? 1 : 0;
+                ctl->red_f[4] = 1.f;
             }
-            const float m = fminf(fminf(g[0], g[1]), fminf(g[2], g[3]));
-            unsigned flagged = __ballot_sync(FULL_MASK, m < thr);
-            if (flagged == 0) return;
-            // A list that already holds 16 keys below t proves that nothing at or above t is among the query's
-            // 16 best, whichever list it would go to: before any work is spent on a flagged chunk, every lane
-            // lowers its threshold to the smallest one published for its query (read without synchronisation:
-            // a stale value is only a larger one) and the chunk is tested again.
-#pragma unroll
-            for (int pp = 0; pp < kTcLists; ++pp) thr = fminf(thr, sthr[pp * kTcQueries + q]);
-            flagged = __ballot_sync(FULL_MASK, m < thr);
-            if (flagged == 0) return;
-            // only the groups of eight that hold a key below the threshold are parked
-            unsigned gm = 0;
-#pragma unroll
-            for (int gi = 0; gi < 4; ++gi) {
-                if (g[gi] < thr) {
-                    gm |= 1u << gi;
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) rows[lane * 33 + 8 * gi + j] = __uint_as_float(v[8 * gi + j]);
-                }
-            }
-            __syncwarp();
-            while (flagged) {
-                const int L = __ffs(flagged) - 1;
-                flagged &= flagged - 1;
-                float thrL = __shfl_sync(FULL_MASK, thr, L);
-                const int qL = quarter * 32 + L;
-#if MPB_TC_SHARED_LIST
-                // the four warps of this lane quarter insert into the same list: one warp at a time per query
-                if (lane == 0) {
-                    for (uint32_t spins = 0; atomicCAS(&locks[qL], 0, 1) != 0; ++spins)
-                        if (spins > (1u << 24)) __trap();
-                }
-                __syncwarp();
-                __threadfence_block();
-                thrL = fminf(thrL, lkp[qL * kTcKeep + kTcKeep - 1]);
-#endif
-                const unsigned gmL = __shfl_sync(FULL_MASK, gm, L);
-                const float mine = rows[L * 33 + lane];      // stale where the group was not parked: masked out
-                unsigned takers = __ballot_sync(FULL_MASK, ((gmL >> (lane >> 3)) & 1u) && mine < thrL);
-                while (takers) {
-                    const int j = __ffs(takers) - 1;
-                    takers &= takers - 1;
-                    const float key = __shfl_sync(FULL_MASK, mine, j);
-                    if (key < thrL) {
-                        const bool in_list = lane < kTcKeep;
-                        const float e = in_list ? lkp[qL * kTcKeep + lane] : INFINITY;
-                        const int ei = in_list ? lip[qL * kTcKeep + lane] : -1;
-                        // equal keys: the newcomer goes after the incumbents
-                        const int pos = __popc(__ballot_sync(FULL_MASK, in_list && e <= key));
-                        if (lane >= pos && lane < kTcKeep - 1) {
-                            lkp[qL * kTcKeep + lane + 1] = e;
-                            lip[qL * kTcKeep + lane + 1] = ei;
-                        }
-                        if (lane == pos) {
-                            lkp[qL * kTcKeep + pos] = key;
-                            lip[qL * kTcKeep + pos] = cbase + j;
-                        }
-                        __syncwarp();
-                        thrL = lkp[qL * kTcKeep + kTcKeep - 1];
+        } else {
+            // tiles whose box is closer than that, not handled yet.  More than the list holds (a block whose
+            // first tile gave loose distances, or a box that touches thousands of tiles): the nearer ones first,
+            // by shrinking the bound; if that does not separate them, the next kTcListCap tiles by index.
+            float bound = rmax2;
+            int tries = 0, end = n_tiles;
+            bool window = false;
+            for (;;) {
+                if (tid == 0) ctl->list_all = 0;
+                __syncthreads();
+                for (int t = cursor + tid; t < end; t += kTcThreads) {
+                    if (t == home) continue;
+                    const float lb = tile_lb(t);
+                    const unsigned long long key = key_of(lb, t);
+                    if (lb < bound && (!has_lo || key > lo_key)) {
+                        const int pos = atomicAdd(&ctl->list_all, 1);
+                        if (pos < kTcListCap) list[pos] = key;
                     }
                 }
-                if (lane == L) {
-                    thr = thrL;
-                    sthr[my_list * kTcQueries + q] = thrL;
+                __syncthreads();
+                n = ctl->list_all;
+                if (n <= kTcListCap && (n > 0 || window || bound == rmax2)) break;
+                if (n > kTcListCap && !window && ++tries <= 3) {
+                    bound *= 0.25f;
+                } else {
+                    window = true;
+                    bound = rmax2;
+                    end = min(n_tiles, cursor + kTcListCap);
                 }
-#if MPB_TC_SHARED_LIST
-                __syncwarp();
-                __threadfence_block();
-                if (lane == 0) atomicExch(&locks[qL], 0);
-#endif
+                __syncthreads();
+            }
+            if (tid == 0) {
+                ctl->final_round = (bound == rmax2 && end == n_tiles) ? 1 : 0;
+                if (window) ctl->cursor = end;
+                ctl->red_f[4] = window ? 1.f : 0.f;
+            }
+        }
+        // nearest box first (bitonic sort of the keys; the pad sorts to the end)
+        int n2 = 2;
+        while (n2 < n) n2 <<= 1;
+        if (n > 1) {
+            for (int i = n + tid; i < n2; i += kTcThreads) list[i] = ~0ull;
+            __syncthreads();
+            for (int k2 = 2; k2 <= n2; k2 <<= 1) {
+                for (int j = k2 >> 1; j > 0; j >>= 1) {
+                    for (int i = tid; i < n2; i += kTcThreads) {
+                        const int p = i ^ j;
+                        if (p > i) {
+                            const unsigned long long a = list[i], b = list[p];
+                            if ((a > b) == ((i & k2) == 0)) {
+                                list[i] = b;
+                                list[p] = a;
+                            }
+                        }
+                    }
+                    __syncthreads();
+                }
+            }
+        }
+        if (tid == 0) {
+            ctl->list_n = n;
+            if (n > 0 && rmax2 < 3.0e38f && ctl->red_f[4] == 0.f) {     // a round ordered by distance, not by index
+                ctl->lo_key = list[n - 1];
+                ctl->has_lo = 1;
+            }
+        }
+        __syncthreads();
+    };
+
+    // ---- epilogue state (warps 0..15)
+    const int quarter = warp & 3, part = warp >> 2;
+    const int q = quarter * 32 + lane;             // this thread's query (epilogue warps only)
+    float thr = INFINITY;
+    const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
+    float *rows = scr + (warp < kTcEpiWarps ? warp : 0) * 32 * 33;
+    // The 32 keys a lane just received are examined with one min-tree.  When some lane's minimum beats its
+    // threshold, the flagged lanes park their keys in the warp's scratch rows, and each flagged lane is then
+    // served by the WHOLE warp: lane j reads key j of that row, one ballot finds the takers, and each taker is
+    // inserted into the query's shared-memory list by lanes 0..15 side by side.  (A lane-private walk over
+    // the 32 keys makes every lane of the warp wait for it: profiles/r1_summary.md.)
+    auto examine = [&](const uint32_t (&v)[32], int cbase) {
+        float g[4];        // minima of the four groups of eight keys
+#pragma unroll
+        for (int gi = 0; gi < 4; ++gi) {
+            g[gi] = __uint_as_float(v[8 * gi]);
+#pragma unroll
+            for (int j = 1; j < 8; ++j) g[gi] = fminf(g[gi], __uint_as_float(v[8 * gi + j]));
+        }
+        const float m = fminf(fminf(g[0], g[1]), fminf(g[2], g[3]));
+        unsigned flagged = __ballot_sync(FULL_MASK, m < thr);
+        if (flagged == 0) return;
+        // A list that already holds 16 keys below t proves that nothing at or above t is among the query's
+        // 16 best: before any work is spent on a flagged chunk, every lane lowers its threshold to the one
+        // published for its query (read without synchronisation: a stale value is only a larger one) and the
+        // chunk is tested again.
+        thr = fminf(thr, sthr[q]);
+        flagged = __ballot_sync(FULL_MASK, m < thr);
+        if (flagged == 0) return;
+        // only the groups of eight that hold a key below the threshold are parked
+        unsigned gm = 0;
+#pragma unroll
+        for (int gi = 0; gi < 4; ++gi) {
+            if (g[gi] < thr) {
+                gm |= 1u << gi;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) rows[lane * 33 + 8 * gi + j] = __uint_as_float(v[8 * gi + j]);
+            }
+        }
+        __syncwarp();
+        while (flagged) {
+            const int L = __ffs(flagged) - 1;
+            flagged &= flagged - 1;
+            float thrL = __shfl_sync(FULL_MASK, thr, L);
+            const int qL = quarter * 32 + L;
+            // the four warps of this lane quarter insert into the same list: one warp at a time per query
+            if (lane == 0) {
+                for (uint32_t spins = 0; atomicCAS(&locks[qL], 0, 1) != 0; ++spins)
+                    if (spins > (1u << 24)) __trap();
             }
             __syncwarp();
-        };
-        for (int i = 0; i < n_tiles; ++i) {
-            const int b = i & 1;
-            mbar_wait_warp_backoff(&tfull[b], (uint32_t)((i / 2) & 1));
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            constexpr int CH = (kTcTile / 32) / kTcParts;      // chunks per warp per tile
-            static_assert(CH % 2 == 0, "chunks are processed in pairs");
-            uint32_t va[32], vb[32];
-            const int c0 = CH * part;
-            const uint32_t tile_base = lane_base + (uint32_t)(b * kTcTile + c0 * 32);
-            if constexpr (CH == 2) {
+            __threadfence_block();
+            thrL = fminf(thrL, lk[qL * kTcKeep + kTcKeep - 1]);
+            const unsigned gmL = __shfl_sync(FULL_MASK, gm, L);
+            const float mine = rows[L * 33 + lane];      // stale where the group was not parked: masked out
+            unsigned takers = __ballot_sync(FULL_MASK, ((gmL >> (lane >> 3)) & 1u) && mine < thrL);
+            while (takers) {
+                const int j = __ffs(takers) - 1;
+                takers &= takers - 1;
+                const float key = __shfl_sync(FULL_MASK, mine, j);
+                if (key < thrL) {
+                    const bool in_list = lane < kTcKeep;
+                    const float e = in_list ? lk[qL * kTcKeep + lane] : INFINITY;
+                    const int ei = in_list ? li[qL * kTcKeep + lane] : -1;
+                    // equal keys: the newcomer goes after the incumbents
+                    const int pos = __popc(__ballot_sync(FULL_MASK, in_list && e <= key));
+                    if (lane >= pos && lane < kTcKeep - 1) {
+                        lk[qL * kTcKeep + lane + 1] = e;
+                        li[qL * kTcKeep + lane + 1] = ei;
+                    }
+                    if (lane == pos) {
+                        lk[qL * kTcKeep + pos] = key;
+                        li[qL * kTcKeep + pos] = cbase + j;
+                    }
+                    __syncwarp();
+                    thrL = lk[qL * kTcKeep + kTcKeep - 1];
+                }
+            }
+            if (lane == L) {
+                thr = thrL;
+                sthr[q] = thrL;
+            }
+            __syncwarp();
+            __threadfence_block();
+            if (lane == 0) atomicExch(&locks[qL], 0);
+        }
+        __syncwarp();
+    };
+
+    // DIAG: this thread's query in fp32 and fp64 terms, and the running maxima of the key error
+    float dq[D];
+    double d_scale = 1., d_max = 0.;
+    unsigned long long d_pairs = 0;
+    bool d_valid = false;
+    if constexpr (DIAG) {
+        if (warp < kTcEpiWarps) {
+            d_valid = tc_query_hat<D>(qs, qorder, slot0, q, wt, h, dq);
+            double n2 = 0.;
+#pragma unroll
+            for (int d = 0; d < D; ++d) n2 += (double)dq[d] * (double)dq[d];
+            d_scale = h->R * h->R + 2.0 * sqrt(n2) * h->R;
+        }
+    }
+    // every key of the chunk against the same expression in fp64: n + sum_d (-2 q^_d) x^_d over the fp32 values
+    auto measure = [&](const uint32_t (&v)[32], int cbase) {
+        if constexpr (DIAG) {
+            for (int i = 0; i < 32; ++i) {
+                const int j = slot_idx[cbase + i];
+                if (j < 0 || !d_valid) continue;
+                double n2 = 0., dot = 0.;
+#pragma unroll
+                for (int d = 0; d < D; ++d) {
+                    const float f = (float)d_sub(d_mul(wt.w[d], x[(int64_t)j * D + d]), h->center[d]);
+                    n2 += (double)f * (double)f;
+                    dot += (double)(-2.f * dq[d]) * (double)f;
+                }
+                const double exact = (double)(float)n2 + dot;
+                const double err = fabs((double)__uint_as_float(v[i]) - exact) / d_scale;
+                d_max = fmax(d_max, err);
+                ++d_pairs;
+            }
+        }
+    };
+
+    // ---- rounds: scan the planned tiles, then plan again, until a round has covered everything that is left
+    uint32_t it = 0;                               // tiles and end-of-round marks this thread's role has handled
+    for (;;) {
+        if (warp == kTcEpiWarps + 1) {
+            // ---- producer: follows the list; a tile is dropped (and with it the rest of the round: the list is
+            // sorted) when its box is no longer closer than the block's largest k-th distance
+            const int n = ctl->list_n;
+            for (int i = 0; i <= n; ++i) {
+                int t = -1;
+                if (i < n) {
+                    const unsigned long long e = list[i];
+                    const float lb = __uint_as_float((uint32_t)(e >> 32));
+                    float r = 0.f;
+#pragma unroll
+                    for (int u = 0; u < kTcQueries / 32; ++u) {
+                        const int qq = lane + 32 * u;
+                        r = fmaxf(r, tc_r2_of(*(volatile float *)&lk[qq * kTcKeep + kTcKeep - 1], nq2s[qq]));
+                    }
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) r = fmaxf(r, __shfl_xor_sync(FULL_MASK, r, o));
+                    if (lb >= r) i = n;            // -> the end-of-round mark
+                    else t = (int)(uint32_t)e;
+                }
+                const int s = it % kTcStages;
+                if (lane == 0) {
+                    if (it >= kTcStages) mbar_wait_backoff(&empty[s], (uint32_t)((it / kTcStages - 1) & 1));
+                    *(volatile int *)&ctl->slot_tile[s] = t;
+                    if (t >= 0) {
+                        mbar_arrive_expect_tx(&full[s], kTcTileBytes);
+                        bulk_copy_g2s(sB + (size_t)s * kTcTileBytes, tiles + (size_t)t * kTcTileBytes, kTcTileBytes, &full[s]);
+                    } else {
+                        mbar_arrive(&full[s]);
+                    }
+                }
+                ++it;
+                __syncwarp();
+            }
+        } else if (warp == kTcEpiWarps) {
+            // ---- MMA issue: three k-steps per tile into accumulator it & 1
+            if (lane == 0) {
+                // D = f32, A = B = tf32, both K-major, N = 256, M = 128
+                constexpr uint32_t idesc =
+                    (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kTcTile >> 3) << 17) | ((uint32_t)(kTcQueries >> 4) << 24);
+                const uint32_t a_addr = smem_u32(sA);
+                for (;;) {
+                    const int s = it % kTcStages, b = it & 1;
+                    mbar_wait_backoff(&full[s], (uint32_t)((it / kTcStages) & 1));
+                    const int t = *(volatile int *)&ctl->slot_tile[s];
+                    if (it >= 2) mbar_wait_backoff(&tempty[b], (uint32_t)((it / 2 - 1) & 1));
+                    ++it;
+                    *(volatile int *)&ctl->acc_tile[b] = t;
+                    if (t < 0) {
+                        mbar_arrive(&empty[s]);
+                        mbar_arrive(&tfull[b]);
+                        mbar_arrive(&tfull[b]);
+                        break;
+                    }
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t b_addr = smem_u32(sB + (size_t)s * kTcTileBytes);
+                    const uint32_t d_addr = tmem + (uint32_t)(b * kTcTile);
+#pragma unroll
+                    for (int ks = 0; ks < kTcK / 8; ++ks) {
+                        const uint64_t da = tc_desc(a_addr + ks * 2 * kTcLbo);
+                        const uint64_t db = tc_desc(b_addr + ks * 2 * kTcLbo);
+                        const uint32_t acc = ks > 0 ? 1u : 0u;
+                        asm volatile(
+                            "{\n .reg .pred p;\n setp.ne.b32 p, %4, 0;\n"
+                            " tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n}"
+                            ::"r"(d_addr), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
+                    }
+                    // both commits track every MMA issued so far: the ring slot is free, the accumulator is ready;
+                    // the plain arrival publishes acc_tile[b] to the epilogue warps
+                    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
+                                 ::"r"(smem_u32(&empty[s])) : "memory");
+                    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
+                                 ::"r"(smem_u32(&tfull[b])) : "memory");
+                    mbar_arrive(&tfull[b]);
+                }
+            }
+            __syncwarp();
+        } else {
+            // ---- epilogue: lane = query; this warp's part of every tile is two chunks of 32 keys
+            for (;;) {
+                const int b = it & 1;
+                mbar_wait_warp_backoff(&tfull[b], (uint32_t)((it / 2) & 1));
+                ++it;
+                const int t = *(volatile int *)&ctl->acc_tile[b];
+                if (t < 0) {
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&tempty[b]);
+                    break;
+                }
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                constexpr int CH = (kTcTile / 32) / kTcParts;      // chunks per warp per tile
+                static_assert(CH == 2, "both chunks of a warp go to registers at once");
+                uint32_t va[32], vb[32];
+                const int c0 = CH * part;
+                const uint32_t tile_base = lane_base + (uint32_t)(b * kTcTile + c0 * 32);
                 // both chunks go to registers first and the accumulator is handed back at once: the next MMAs
                 // never wait for a warp that is busy inserting
                 __syncwarp();
@@ -398,40 +741,31 @@ __global__ void __launch_bounds__(kTcThreads, 1)
                 asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&tempty[b]);
-                examine(va, i * kTcTile + c0 * 32);
-                examine(vb, i * kTcTile + (c0 + 1) * 32);
-            } else {
-                // two register sets: the next chunk's load is in flight while the current chunk is examined; the
-                // accumulator is handed back as soon as this warp's last chunk is in registers
-                __syncwarp();
-                tmem_ld32(va, tile_base);
-#pragma unroll 1
-                for (int c = 0; c < CH; c += 2) {
-                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                    __syncwarp();
-                    tmem_ld32(vb, tile_base + (uint32_t)((c + 1) * 32));
-                    examine(va, i * kTcTile + (c0 + c) * 32);
-                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                    __syncwarp();
-                    if (c + 2 < CH) {
-                        tmem_ld32(va, tile_base + (uint32_t)((c + 2) * 32));
-                    } else {
-                        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-                        if (lane == 0) mbar_arrive(&tempty[b]);
-                    }
-                    examine(vb, i * kTcTile + (c0 + c + 1) * 32);
+                if constexpr (DIAG) {
+                    measure(va, t * kTcTile + c0 * 32);
+                    measure(vb, t * kTcTile + (c0 + 1) * 32);
+                } else {
+                    examine(va, t * kTcTile + c0 * 32);
+                    examine(vb, t * kTcTile + (c0 + 1) * 32);
                 }
             }
         }
-#if MPB_TC_SHARED_LIST
-        asm volatile("bar.sync 1, %0;" ::"r"(kTcEpiWarps * 32) : "memory");
-#endif
-        // this part's survivors of the query (ascending fp32 key) and its final threshold
-        const int64_t qq = q0 + q;
-        if (qq < M && (!MPB_TC_SHARED_LIST || part == 0)) {
+        __syncwarp();
+        __syncthreads();
+        if (ctl->final_round) break;
+        plan_round();
+    }
+
+    // the survivors of every query (ascending fp32 key) and its final threshold
+    if (!DIAG && warp < 4) {
 #pragma unroll
-            for (int p = 0; p < kTcKeep; ++p) surv_idx[qq * kTcSurvivors + my_list * kTcKeep + p] = lip[q * kTcKeep + p];
-            surv_thr[qq * kTcLists + my_list] = MPB_TC_SHARED_LIST ? lkp[q * kTcKeep + kTcKeep - 1] : thr;
+        for (int p = 0; p < kTcKeep; ++p) surv_idx[(slot0 + q) * kTcKeep + p] = li[q * kTcKeep + p];
+        surv_thr[slot0 + q] = lk[q * kTcKeep + kTcKeep - 1];
+    }
+    if constexpr (DIAG) {
+        if (warp < kTcEpiWarps && d_pairs > 0) {
+            atomicMax(&diag[0], (unsigned long long)__double_as_longlong(d_max));   // non-negative doubles order as integers
+            atomicAdd(&diag[1], d_pairs);
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -440,22 +774,27 @@ __global__ void __launch_bounds__(kTcThreads, 1)
 }
 
 // ---- exact re-rank of the survivors of every query, and the certificate ---------------------------------
-// One warp per query, kTcSurvivors / 32 survivors per lane (kTcParts lists of kTcKeep).  Same argument as in
-// knn_filter_kernel: every sample outside list p has computed key >= T_p, so every sample outside all lists has
-// computed key >= T = min_p T_p, hence exact squared distance >= (sqrt(T - eta + |q^|^2) - delta)^2; here eta also
-// covers the TF32 split (three dropped or rounded 2^-22 terms) and the tensor core's accumulation, budgeted at
-// 2^-22 per term.
+// One warp per query slot.  Same argument as in knn_filter_kernel: every sample of a VISITED tile that is not in
+// the list has computed key >= T (the list's final threshold), hence exact squared distance
+// >= (sqrt(T - eta + |q^|^2) - delta)^2; here eta also covers the TF32 split (three dropped or rounded 2^-22
+// terms) and the tensor core's accumulation, budgeted at 2^-22 per term (measured: mpb_knn_tc_key_error).
+// Every sample of a SKIPPED tile lies in a box whose squared distance to the block's box, rounded down, was at
+// least the block's largest T_q + |q^|^2, rounded up, when the tile was dropped -- and thresholds only fall --
+// so its fp32-space squared distance is >= T + |q^|^2 and the same bound holds for it a fortiori.
 template <int D>
 __global__ void __launch_bounds__(256)
     knn_tc_rerank_kernel(const double *__restrict__ x, int64_t N, const double *__restrict__ qs, int64_t M, Weights wt,
-                         int k, double r2, KnnHeader *__restrict__ h, const int *__restrict__ surv_idx,
+                         int k, double r2, KnnHeader *__restrict__ h, const int *__restrict__ qorder, int64_t n_slots,
+                         const int *__restrict__ slot_idx, const int *__restrict__ surv_idx,
                          const float *__restrict__ surv_thr, int *__restrict__ fb_list, int64_t *__restrict__ out_idx,
                          double *__restrict__ out_dist)
 {
     constexpr int NU = (kTcSurvivors + 31) / 32;   // survivors per lane
     const int lane = threadIdx.x & 31;
-    const int64_t q = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (q >= M) return;                         // whole warps leave together
+    const int64_t slot = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (slot >= n_slots) return;                // whole warps leave together
+    const int64_t q = qorder[slot];
+    if (q < 0 || q >= M) return;                // an unused slot of a query block
     double eq[D];
     double nq2 = 0.;
 #pragma unroll
@@ -468,8 +807,8 @@ __global__ void __launch_bounds__(256)
     double S[NU];
 #pragma unroll
     for (int u = 0; u < NU; ++u) {
-        ci[u] = (u * 32 + lane < kTcSurvivors) ? surv_idx[q * kTcSurvivors + u * 32 + lane] : -1;
-        if (ci[u] >= N) ci[u] = -1;             // a padding slot (only when a part saw fewer than 16 real candidates)
+        ci[u] = (u * 32 + lane < kTcSurvivors) ? surv_idx[slot * kTcSurvivors + u * 32 + lane] : -1;
+        if (ci[u] >= 0) ci[u] = slot_idx[ci[u]];   // tile slot -> sample index (-1: a padding slot)
         S[u] = INFINITY;
         if (ci[u] >= 0) {
             double ex[D];
@@ -504,11 +843,13 @@ __global__ void __launch_bounds__(256)
     float T32 = INFINITY;
 #pragma unroll
     for (int p = 0; p < kTcLists; ++p) {
-        const float tp = surv_thr[q * kTcLists + p];
+        const float tp = surv_thr[slot * kTcLists + p];
         if (tp < 1.0e38f) T32 = fminf(T32, tp);  // a list that never filled (or filled with padding) excludes nothing
     }
     const double T = (double)T32;
-    bool ok = isinf(T) && T > 0;                 // no list ever filled: every sample is a survivor
+    // A list that never filled saw every tile (nothing is skipped without a threshold), so all N samples should
+    // be among the survivors; fewer means that some key was not comparable (overflow, NaN): not certified.
+    bool ok = isinf(T) && T > 0 && (int64_t)nvalid >= N;
     if (!ok) {
         const double R = h->R;
         constexpr double U24 = 5.9604644775390625e-08;   // 2^-24: rounding of the centred fp32 coordinates

@@ -301,6 +301,25 @@ def knn(samples, queries, k, weights=None, max_dist=math.inf, method="f32filter"
     return idx, dist
 
 
+def knn_tc_key_error(samples, queries, weights=None):
+    """Measured rounding of the tensor-core filter's keys (mpb_knn_tc_key_error): -> (max over pairs of
+    |key_tc - key_fp64| / (R^2 + 2 |q^| R), pairs measured).  The certificate budgets 32 * 2^-22 for it."""
+    samples = _f64(samples, "samples")
+    queries = _f64(queries, "queries", samples.shape[1])
+    N, D = samples.shape
+    M = queries.shape[0]
+    nbytes = _lib.lib().mpb_knn_workspace_bytes(N, M, D)
+    ws = torch.empty(nbytes + 256, dtype=torch.uint8, device=samples.device)
+    off = (-ws.data_ptr()) % 256
+    out = torch.zeros(2, dtype=torch.int64, device=samples.device)
+    _, wp = _host_weights(weights, D)
+    rc = _lib.lib().mpb_knn_tc_key_error(_ptr(samples), N, _ptr(queries), M, D, wp, ctypes.c_void_p(ws.data_ptr() + off),
+                                         ws.numel() - off, _ptr(out), _stream())
+    _lib.check(rc, "mpb_knn_tc_key_error")
+    host = out.cpu().numpy()
+    return float(host[:1].view(np.float64)[0]), int(host[1])
+
+
 def knn_static(samples, queries, k, weights=None, max_dist=math.inf, stats=None):
     """knn() on the library's built-in scratch array, for callers that must not allocate device memory
     (see mpb_knn_f32filter_static in include/mpb200.h for who those are and for the size limit).

@@ -123,10 +123,9 @@ class DeviceRoadmap(object):
         if self._index is None or self._index.samples.data_ptr() != samples.data_ptr() \
                 or self._index.n != samples.shape[0]:
             self._index = ops.KnnIndex(samples, self.weights)
+        count0 = _lib.lib().mpb_knn_launch_count()  # the library counts the kernels its kNN entry points launch
         self._index._prepared = False
         self._index.prepare(n_local)
-        tensor = _lib.lib().mpb_knn_filter_kind(int(samples.shape[0]), int(samples.shape[1]), int(self.kk)) == 1
-        launches += 5 if tensor else 4              # init, minmax, finalize, pack (+ the tensor-core operand tiles)
         mark("packed")
         if getattr(self, "nbr_idx", None) is None or self.nbr_idx.shape != (n_local, self.kk):
             self.nbr_idx = torch.empty((n_local, self.kk), dtype=torch.int64, device=samples.device)
@@ -134,7 +133,7 @@ class DeviceRoadmap(object):
             self.stats = torch.zeros(2, dtype=torch.int64, device=samples.device)
         self._index.search(queries, self.kk, self.max_distance, stats=self.stats, out_idx=self.nbr_idx,
                            out_dist=self.nbr_dist)
-        launches += 3 if tensor else 2              # filter (+ its re-rank kernel) + exact re-do of uncertified queries
+        launches += _lib.lib().mpb_knn_launch_count() - count0
         mark("knn")
 
         if check:

@@ -118,3 +118,31 @@ def test_clustered_samples(mp):
     stats = torch.zeros(2, dtype=torch.int64, device="cuda")
     idx, dist = mp.ops.knn(xs, xs, 11, stats=stats)
     check_knn_slices(X, idx, dist, 11, width=500)
+
+
+def test_tensor_core_key_error_within_certificate_budget(mp, capsys):
+    """What the certificate ASSUMES about tcgen05.mma kind::tf32 (its eta budgets 32 * 2^-22 of R^2 + 2|q^|R per key
+    for the TF32 split of the operands and the accumulation inside the tensor core) is measured here: every key
+    the scan reads from tensor memory against the same expression in fp64, over more than 1e7 pairs per set,
+    including sets that stress it (off-centre clusters, coordinates of mixed magnitude, far-away queries)."""
+    rs = np.random.RandomState(3)
+    N, D = 160_000, 7
+    budget = 32.0 * 2.0 ** -22
+    sets = {}
+    sets["uniform"] = (rs.uniform(size=(N, D)), None, rs.uniform(size=(256, D)))
+    X = rs.uniform(size=(N, D))
+    X[: N // 2] = 0.93 + 1e-3 * rs.uniform(size=(N // 2, D))
+    sets["off-centre cluster"] = (X, None, X[:256].copy())
+    sets["mixed magnitudes"] = (rs.uniform(size=(N, D)), np.array([1e3, 1.0, 1e-3, 1.0, 30.0, 1.0, 0.1]),
+                                rs.uniform(size=(256, D)))
+    X = rs.normal(size=(N, D)) * np.array([1, 10, 100, 1, 0.1, 5, 1.0])
+    sets["gaussian, far queries"] = (X, None, np.concatenate([X[:128], 50.0 + rs.uniform(size=(128, D))]))
+    worst = 0.0
+    for name, (X, w, Q) in sets.items():
+        err, pairs = mp.ops.knn_tc_key_error(torch.from_numpy(X).cuda(), torch.from_numpy(Q).cuda(), w)
+        assert pairs == N * Q.shape[0] and pairs > 10_000_000, (name, pairs)
+        assert 0.0 < err <= budget, (name, err / 2.0 ** -22)
+        worst = max(worst, err)
+        with capsys.disabled():
+            print("\n[tc key error] %-22s max = %.3f x 2^-22 over %d pairs (budget 32)" % (name, err / 2.0 ** -22, pairs))
+    assert worst <= budget
