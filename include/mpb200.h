@@ -167,7 +167,8 @@ int mpb_knn_f64_circular(const double *samples, int64_t n_samples, const double 
  * sample can belong to the answer; queries for which the proof fails are redone by the
  * exact kernel inside the same call.
  * workspace: dev, 256-byte aligned, at least mpb_knn_workspace_bytes(N, M, dim) bytes.
- * stats (dev [2] i64, may be NULL): [0] = queries re-done exactly, [1] = reserved. */
+ * stats (dev [2] i64, may be NULL): [0] = queries re-done exactly, [1] = candidate tiles read by the
+ * tensor-core scan, summed over its query blocks (0 on the other paths). */
 size_t mpb_knn_workspace_bytes(int64_t n_samples, int64_t n_queries, int dim);
 int mpb_knn_prepare(const double *samples, int64_t n_samples, int dim, const double *weights,
                     void *workspace, size_t workspace_bytes, void *stream);

@@ -60,7 +60,7 @@ constexpr int64_t kShortScanMax = MPB_KNN_SHORT_MAX;
 constexpr int kStages = MPB_KNN_STAGES;   // shared-memory ring depth
 constexpr int kSmallListMaxK = 12; // k up to which 16 survivors per query are kept (else 32)
 constexpr int kFilterMaxK = 28;    // beyond this the 32-entry lists cannot certify anything: exact scan directly
-constexpr int kHeaderBytes = 512;
+constexpr int kHeaderBytes = 1024;
 
 struct KnnHeader {
     unsigned long long mm[2 * MPB_MAX_DIM];   // order-encoded min [0,16) and max [16,32)
@@ -69,6 +69,8 @@ struct KnnHeader {
     int fb_count;                             // queries queued for the exact kernel
     int pad;
     int dim_order[MPB_MAX_DIM];               // coordinates by extent, widest first (kdorder.cuh)
+    unsigned long long tiles_visited;         // candidate tiles read by the tensor-core scan, summed over its CTAs
+    unsigned long long dbg[16];               // MPB_TC_STATS builds only
 };
 static_assert(sizeof(KnnHeader) <= kHeaderBytes, "header overflows its slot");
 
@@ -200,13 +202,16 @@ template <int D>
 __global__ void __launch_bounds__(256)
     knn_exact_kernel(const double *__restrict__ x, int64_t N, const double *__restrict__ qs, int64_t M, Weights wt,
                      int metric, int k, double lim, const int *__restrict__ list, const int *__restrict__ list_count,
-                     int64_t *__restrict__ out_idx, double *__restrict__ out_dist, int64_t *__restrict__ stats)
+                     const unsigned long long *__restrict__ visited, int64_t *__restrict__ out_idx, double *__restrict__ out_dist, int64_t *__restrict__ stats)
 {
     const int lane = threadIdx.x & 31;
     const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     const int64_t total = list ? (int64_t)*list_count : M;
-    if (stats && warp0 == 0 && lane == 0) stats[0] = list ? total : 0;
+    if (stats && warp0 == 0 && lane == 0) {
+        stats[0] = list ? total : 0;
+        stats[1] = visited ? (int64_t)*visited : 0;      // candidate tiles the tensor-core scan read
+    }
 
     for (int64_t it = warp0; it < total; it += nwarps) {
         const int64_t q = list ? (int64_t)list[it] : it;
@@ -709,14 +714,14 @@ int sm_count()
 template <int D>
 int launch_exact(const double *x, int64_t N, const double *qs, int64_t M, const Weights &wt, int metric, int k,
                  double lim, const int *list, const int *list_count, int64_t *out_idx, double *out_dist,
-                 int64_t *stats, cudaStream_t st)
+                 int64_t *stats, cudaStream_t st, const unsigned long long *visited = nullptr)
 {
     const int threads = 256;
     int64_t blocks = list ? (int64_t)sm_count() * 4 : (M * 32 + threads - 1) / threads;
     if (blocks > (int64_t)sm_count() * 32) blocks = (int64_t)sm_count() * 32;
     if (blocks < 1) blocks = 1;
     knn_exact_kernel<D><<<(unsigned)blocks, threads, 0, st>>>(x, N, qs, M, wt, metric, k, lim, list, list_count,
-                                                              out_idx, out_dist, stats);
+                                                              visited, out_idx, out_dist, stats);
     MPB_LAUNCH_CHECK();
     return MPB_OK;
 }
@@ -820,6 +825,7 @@ int launch_search(const double *x, int64_t N, const double *qs, int64_t M, const
         return MPB_OK;
     }
     MPB_CUDA_CHECK(cudaMemsetAsync(&h->fb_count, 0, sizeof(int), st));
+    MPB_CUDA_CHECK(cudaMemsetAsync(&h->tiles_visited, 0, 17 * sizeof(unsigned long long), st));
     if constexpr (D <= kTcMaxDim) {
         if (L.tc_tiles > 0 && k <= kSmallListMaxK) {
             // tensor-core scan over the tiles near each query block -> 16 survivors per query -> exact re-rank +
@@ -832,7 +838,8 @@ int launch_search(const double *x, int64_t N, const double *qs, int64_t M, const
             float *sthr = reinterpret_cast<float *>(base + L.thr_off);
             const int *qorder = slot_idx;                  // the sample set queried against itself: block = half tile
             int64_t blocks = 2 * L.tc_tiles;
-            if (!(qs == x && M == N)) {
+            const bool own = (qs == x && M == N);
+            if (!own) {
                 // any other query set gets its own k-d order, one leaf of at most 128 queries per block
                 blocks = (M + kTcQueries - 1) / kTcQueries;
                 const KdPlan plan = kd_plan(M, blocks, D);
@@ -849,7 +856,7 @@ int launch_search(const double *x, int64_t N, const double *qs, int64_t M, const
             MPB_CUDA_CHECK(cudaFuncSetAttribute(knn_tc_kernel<D, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                 (int)TcSmem::BYTES));
             knn_tc_kernel<D, false><<<(unsigned)blocks, kTcThreads, TcSmem::BYTES, st>>>(
-                qs, qorder, wt, tiles, (int)L.tc_tiles, boxes, L.box_stride, h, surv, sthr, nullptr, nullptr, nullptr);
+                qs, qorder, wt, tiles, (int)L.tc_tiles, boxes, L.box_stride, h, surv, sthr, nullptr, nullptr, nullptr, own ? 1 : 0);
             MPB_LAUNCH_CHECK();
             const int64_t n_slots = blocks * kTcQueries;
             const int64_t rthreads = n_slots * 32;
@@ -858,7 +865,7 @@ int launch_search(const double *x, int64_t N, const double *qs, int64_t M, const
             MPB_LAUNCH_CHECK();
             g_last_launches += 3;
             return launch_exact<D>(x, N, qs, M, wt, MPB_METRIC_KDTREE, k, r2, fb, &h->fb_count, out_idx, out_dist, stats,
-                                   st);
+                                   st, &h->tiles_visited);
         }
     }
     // 16 survivors per query leave a comfortable certificate margin up to k = 12 (a PRM's k + 1 = 11) and
@@ -896,7 +903,7 @@ int launch_tc_diag(const double *x, int64_t N, const double *qs, int64_t M, cons
         knn_tc_kernel<D, true><<<(unsigned)blocks, kTcThreads, TcSmem::BYTES, st>>>(
             qs, qo, wt, reinterpret_cast<const unsigned char *>(base + L.tc_off), (int)L.tc_tiles,
             reinterpret_cast<const float *>(base + L.box_off), L.box_stride, h, nullptr, nullptr, x,
-            reinterpret_cast<const int *>(base + L.slot_off), out);
+            reinterpret_cast<const int *>(base + L.slot_off), out, 0);
         MPB_LAUNCH_CHECK();
         return MPB_OK;
     } else {

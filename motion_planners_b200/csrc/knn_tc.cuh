@@ -25,6 +25,16 @@
 // for bit those of the full scan.  At 1M uniform 7-DoF samples a CTA reads about 6 % of the tiles.
 #pragma once
 
+#ifdef MPB_TC_STATS
+#define TC_STAT(i, v) atomicAdd(&const_cast<KnnHeader *>(h)->dbg[i], (unsigned long long)(v))
+#define TC_CLK(var) const long long var = clock64()
+#define TC_ACC(acc, since) acc += clock64() - (since)
+#else
+#define TC_CLK(var) ((void)0)
+#define TC_ACC(acc, since) ((void)0)
+#define TC_STAT(i, v) ((void)0)
+#endif
+
 constexpr int kTcK = 24;                       // operand columns (D <= 7)
 constexpr int kTcTile = 256;                   // candidates per tile = MMA N
 constexpr int kTcQueries = 128;                // queries per CTA = MMA M = TMEM lanes
@@ -34,6 +44,9 @@ constexpr int kTcQueries = 128;                // queries per CTA = MMA M = TMEM
 #ifndef MPB_TC_SLEEP_EPI
 #define MPB_TC_SLEEP_EPI 32       // ns between polls of an epilogue warp
 #endif
+#ifndef MPB_TC_FIRST_BOUND
+#define MPB_TC_FIRST_BOUND 0.5f
+#endif
 #ifndef MPB_TC_PARTS
 #define MPB_TC_PARTS 4
 #endif
@@ -42,6 +55,7 @@ constexpr int kTcQueries = 128;                // queries per CTA = MMA M = TMEM
 #endif
 constexpr int kTcStages = MPB_TC_STAGES;       // shared-memory ring depth
 constexpr int kTcKeep = 16;                    // survivors per list
+constexpr int kTcBuf = 32;                     // entries of a query's buffer: kTcKeep sorted survivors + appended takers
 constexpr int kTcParts = MPB_TC_PARTS;          // epilogue warps per TMEM lane quarter
 constexpr int kTcEpiWarps = 4 * kTcParts;      // warp w: lane quarter w & 3, part w >> 2 (8 / kTcParts chunks of 32 keys per tile)
 constexpr int kTcThreads = 32 * (kTcEpiWarps + 2);
@@ -232,11 +246,12 @@ struct TcSmem {
     static constexpr int A_OFF = 0;
     static constexpr int B_OFF = A_OFF + kTcQueryBytes;
     static constexpr int LK_OFF = B_OFF + kTcStages * kTcTileBytes;
-    static constexpr int LI_OFF = LK_OFF + kTcSurvivors * kTcQueries * 4;
-    static constexpr int SCR_OFF = LI_OFF + kTcSurvivors * kTcQueries * 4;   // [epilogue warp][32 lanes][33]
+    static constexpr int LI_OFF = LK_OFF + kTcBuf * kTcQueries * 4;
+    static constexpr int SCR_OFF = LI_OFF + kTcBuf * kTcQueries * 4;         // [epilogue warp][32 lanes][33]
     static constexpr int THR_OFF = SCR_OFF + kTcEpiWarps * 32 * 33 * 4;        // [part][128] published thresholds
     static constexpr int LOCK_OFF = THR_OFF + kTcLists * kTcQueries * 4;       // [128] list locks (shared-list build)
-    static constexpr int NQ_OFF = LOCK_OFF + kTcQueries * 4;                   // [128] |q^|^2, rounded up
+    static constexpr int CNT_OFF = LOCK_OFF + kTcQueries * 4;                  // [128] entries in each query's buffer
+    static constexpr int NQ_OFF = CNT_OFF + kTcQueries * 4;                    // [128] |q^|^2, rounded up
     static constexpr int LIST_OFF = NQ_OFF + kTcQueries * 4;                   // [kTcListCap] (lower bound, tile) keys
     static constexpr int CTL_OFF = LIST_OFF + kTcListCap * 8;
     static constexpr int BAR_OFF = CTL_OFF + 640;
@@ -279,13 +294,14 @@ __global__ void __launch_bounds__(kTcThreads, 1)
                   const unsigned char *__restrict__ tiles, int n_tiles, const float *__restrict__ tile_box,
                   int box_stride, const KnnHeader *__restrict__ h, int *__restrict__ surv_idx,
                   float *__restrict__ surv_thr, const double *__restrict__ x, const int *__restrict__ slot_idx,
-                  unsigned long long *__restrict__ diag)
+                  unsigned long long *__restrict__ diag, int own_blocks)
 {
     extern __shared__ __align__(1024) unsigned char smem[];
     unsigned char *sA = smem + TcSmem::A_OFF;
     unsigned char *sB = smem + TcSmem::B_OFF;
-    float *lk = reinterpret_cast<float *>(smem + TcSmem::LK_OFF);      // [128][kTcKeep] sorted keys per query
-    int *li = reinterpret_cast<int *>(smem + TcSmem::LI_OFF);          // [128][kTcKeep] their candidate slots
+    float *lk = reinterpret_cast<float *>(smem + TcSmem::LK_OFF);      // [128][kTcBuf] keys kept per query
+    int *li = reinterpret_cast<int *>(smem + TcSmem::LI_OFF);          // [128][kTcBuf] their candidate slots
+    int *cnts = reinterpret_cast<int *>(smem + TcSmem::CNT_OFF);
     float *scr = reinterpret_cast<float *>(smem + TcSmem::SCR_OFF);
     float *sthr = reinterpret_cast<float *>(smem + TcSmem::THR_OFF);
     int *locks = reinterpret_cast<int *>(smem + TcSmem::LOCK_OFF);
@@ -338,12 +354,15 @@ __global__ void __launch_bounds__(kTcThreads, 1)
             }
         }
     }
-    for (int i = tid; i < kTcSurvivors * kTcQueries; i += kTcThreads) {
+    for (int i = tid; i < kTcBuf * kTcQueries; i += kTcThreads) {
         lk[i] = INFINITY;
         li[i] = -1;
     }
-    for (int i = tid; i < kTcLists * kTcQueries; i += kTcThreads) sthr[i] = INFINITY;
-    for (int i = tid; i < kTcQueries; i += kTcThreads) locks[i] = 0;
+    for (int i = tid; i < kTcQueries; i += kTcThreads) {
+        sthr[i] = INFINITY;
+        locks[i] = 0;
+        cnts[i] = 0;
+    }
     if (tid == 0) {
         for (int s = 0; s < kTcStages; ++s) {
             mbar_init(&full[s], 1);
@@ -393,9 +412,18 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         return ((unsigned long long)__float_as_uint(lb) << 32) | (unsigned long long)(uint32_t)t;
     };
 
-    // ---- round 0: the nearest tile alone (ties: lowest index); it gives every query of the block a first list
-    {
+    // ---- round 0: the nearest tile alone (ties: lowest index); it gives every query of the block a first
+    // threshold.  own_blocks: the queries are the samples themselves, block b is one half of tile b / 2.
+    if (own_blocks) {
+        if (tid == 0) {
+            ctl->home = (int)(blockIdx.x >> 1);
+            list[0] = key_of(0.f, (int)(blockIdx.x >> 1));
+            ctl->list_n = 1;
+        }
+        __syncthreads();
+    } else {
         unsigned long long best = ~0ull;
+#pragma unroll 4
         for (int t = tid; t < n_tiles; t += kTcThreads) best = min(best, key_of(tile_lb(t), t));
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(FULL_MASK, best, o));
@@ -416,7 +444,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     auto plan_round = [&]() {
         // largest squared k-th distance in the block right now
         if (tid < kTcQueries) {
-            float r = tc_r2_of(lk[tid * kTcKeep + kTcKeep - 1], nq2s[tid]);
+            float r = tc_r2_of(sthr[tid], nq2s[tid]);
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) r = fmaxf(r, __shfl_xor_sync(FULL_MASK, r, o));
             if (lane == 0) ctl->red_f[warp] = r;
@@ -445,12 +473,16 @@ __global__ void __launch_bounds__(kTcThreads, 1)
             // tiles whose box is closer than that, not handled yet.  More than the list holds (a block whose
             // first tile gave loose distances, or a box that touches thousands of tiles): the nearer ones first,
             // by shrinking the bound; if that does not separate them, the next kTcListCap tiles by index.
-            float bound = rmax2;
+            // (the first such round stops at half the bound: the distances a block has after its own tile alone are
+            // loose, most of the tiles they admit are dropped again once the nearest ones have been read, and a
+            // short list is cheaper to sort; what is left is collected against the tightened bound afterwards)
+            float bound = has_lo ? rmax2 : rmax2 * MPB_TC_FIRST_BOUND;
             int tries = 0, end = n_tiles;
             bool window = false;
             for (;;) {
                 if (tid == 0) ctl->list_all = 0;
                 __syncthreads();
+#pragma unroll 4
                 for (int t = cursor + tid; t < end; t += kTcThreads) {
                     if (t == home) continue;
                     const float lb = tile_lb(t);
@@ -465,6 +497,8 @@ __global__ void __launch_bounds__(kTcThreads, 1)
                 if (n <= kTcListCap && (n > 0 || window || bound == rmax2)) break;
                 if (n > kTcListCap && !window && ++tries <= 3) {
                     bound *= 0.25f;
+                } else if (n == 0 && !window && bound < rmax2) {
+                    bound = rmax2;                 // nothing that near: everything below the real bound
                 } else {
                     window = true;
                     bound = rmax2;
@@ -518,9 +552,28 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     float *rows = scr + (warp < kTcEpiWarps ? warp : 0) * 32 * 33;
     // The 32 keys a lane just received are examined with one min-tree.  When some lane's minimum beats its
     // threshold, the flagged lanes park their keys in the warp's scratch rows, and each flagged lane is then
-    // served by the WHOLE warp: lane j reads key j of that row, one ballot finds the takers, and each taker is
-    // inserted into the query's shared-memory list by lanes 0..15 side by side.  (A lane-private walk over
-    // the 32 keys makes every lane of the warp wait for it: profiles/r1_summary.md.)
+    // served by the WHOLE warp: lane j reads key j of that row, one ballot finds the takers, and all takers are
+    // APPENDED side by side to the query's 32-entry buffer.  Only when the buffer is full is it sorted (a bitonic
+    // network over the 32 lanes) and cut back to its 16 smallest entries, whose largest becomes the query's new
+    // threshold.  A threshold is therefore up to 16 appends stale, which lets a few more keys in, but an append
+    // costs one store where a sorted insert cost a hundred instructions -- and with the nearest tiles first
+    // every query takes about 200 keys (measured), most of them from the first few tiles.
+    auto sort32 = [&](float &e, int &ei) {
+#pragma unroll
+        for (int k2 = 2; k2 <= 32; k2 <<= 1) {
+#pragma unroll
+            for (int j = k2 >> 1; j > 0; j >>= 1) {
+                const float ok = __shfl_xor_sync(FULL_MASK, e, j);
+                const int oi = __shfl_xor_sync(FULL_MASK, ei, j);
+                const bool other_less = (ok < e) || (ok == e && oi < ei);
+                const bool keep_min = ((lane & j) == 0) == ((lane & k2) == 0);
+                if (other_less == keep_min) {
+                    e = ok;
+                    ei = oi;
+                }
+            }
+        }
+    };
     auto examine = [&](const uint32_t (&v)[32], int cbase) {
         float g[4];        // minima of the four groups of eight keys
 #pragma unroll
@@ -532,11 +585,9 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         const float m = fminf(fminf(g[0], g[1]), fminf(g[2], g[3]));
         unsigned flagged = __ballot_sync(FULL_MASK, m < thr);
         if (flagged == 0) return;
-        // A list that already holds 16 keys below t proves that nothing at or above t is among the query's
-        // 16 best: before any work is spent on a flagged chunk, every lane lowers its threshold to the one
-        // published for its query (read without synchronisation: a stale value is only a larger one) and the
-        // chunk is tested again.
-        thr = fminf(thr, sthr[q]);
+        // the threshold published for the query by whichever warp cut its buffer last (read without
+        // synchronisation: a stale value is only a larger one); then the chunk is tested again
+        thr = fminf(thr, *(volatile float *)&sthr[q]);
         flagged = __ballot_sync(FULL_MASK, m < thr);
         if (flagged == 0) return;
         // only the groups of eight that hold a key below the threshold are parked
@@ -550,47 +601,54 @@ __global__ void __launch_bounds__(kTcThreads, 1)
             }
         }
         __syncwarp();
+        const unsigned lt = (1u << lane) - 1u;
         while (flagged) {
             const int L = __ffs(flagged) - 1;
             flagged &= flagged - 1;
-            float thrL = __shfl_sync(FULL_MASK, thr, L);
             const int qL = quarter * 32 + L;
-            // the four warps of this lane quarter insert into the same list: one warp at a time per query
+            if (lane == 0) TC_STAT(1, 1);
+            // the four warps of this lane quarter append to the same buffer: one warp at a time per query
             if (lane == 0) {
                 for (uint32_t spins = 0; atomicCAS(&locks[qL], 0, 1) != 0; ++spins)
                     if (spins > (1u << 24)) __trap();
             }
             __syncwarp();
             __threadfence_block();
-            thrL = fminf(thrL, lk[qL * kTcKeep + kTcKeep - 1]);
+            float thrL = *(volatile float *)&sthr[qL];
+            int c = *(volatile int *)&cnts[qL];
             const unsigned gmL = __shfl_sync(FULL_MASK, gm, L);
             const float mine = rows[L * 33 + lane];      // stale where the group was not parked: masked out
-            unsigned takers = __ballot_sync(FULL_MASK, ((gmL >> (lane >> 3)) & 1u) && mine < thrL);
-            while (takers) {
-                const int j = __ffs(takers) - 1;
-                takers &= takers - 1;
-                const float key = __shfl_sync(FULL_MASK, mine, j);
-                if (key < thrL) {
-                    const bool in_list = lane < kTcKeep;
-                    const float e = in_list ? lk[qL * kTcKeep + lane] : INFINITY;
-                    const int ei = in_list ? li[qL * kTcKeep + lane] : -1;
-                    // equal keys: the newcomer goes after the incumbents
-                    const int pos = __popc(__ballot_sync(FULL_MASK, in_list && e <= key));
-                    if (lane >= pos && lane < kTcKeep - 1) {
-                        lk[qL * kTcKeep + lane + 1] = e;
-                        li[qL * kTcKeep + lane + 1] = ei;
-                    }
-                    if (lane == pos) {
-                        lk[qL * kTcKeep + pos] = key;
-                        li[qL * kTcKeep + pos] = cbase + j;
-                    }
-                    __syncwarp();
-                    thrL = lk[qL * kTcKeep + kTcKeep - 1];
+            bool taker = ((gmL >> (lane >> 3)) & 1u) && mine < thrL;
+            float *bk = lk + qL * kTcBuf;
+            int *bi = li + qL * kTcBuf;
+            for (;;) {
+                const unsigned tk = __ballot_sync(FULL_MASK, taker);
+                if (tk == 0) break;
+                const int nt = __popc(tk), room = kTcBuf - c, rank = __popc(tk & lt);
+                if (lane == 0) TC_STAT(2, nt < room ? nt : room);
+                if (taker && rank < room) {
+                    bk[c + rank] = mine;
+                    bi[c + rank] = cbase + lane;
+                    taker = false;
                 }
+                c += nt < room ? nt : room;
+                if (nt < room) break;
+                // full: keep the 16 smallest (sorted), the 16th is the new threshold
+                __syncwarp();
+                float e = bk[lane];
+                int ei = bi[lane];
+                sort32(e, ei);
+                thrL = __shfl_sync(FULL_MASK, e, kTcKeep - 1);
+                bk[lane] = lane < kTcKeep ? e : INFINITY;
+                bi[lane] = lane < kTcKeep ? ei : -1;
+                c = kTcKeep;
+                taker = taker && mine < thrL;
+                __syncwarp();
             }
-            if (lane == L) {
-                thr = thrL;
-                sthr[q] = thrL;
+            if (lane == L) thr = thrL;
+            if (lane == 0) {
+                *(volatile int *)&cnts[qL] = c;
+                *(volatile float *)&sthr[qL] = thrL;
             }
             __syncwarp();
             __threadfence_block();
@@ -636,7 +694,16 @@ __global__ void __launch_bounds__(kTcThreads, 1)
 
     // ---- rounds: scan the planned tiles, then plan again, until a round has covered everything that is left
     uint32_t it = 0;                               // tiles and end-of-round marks this thread's role has handled
+    uint32_t visited = 0;
+#ifdef MPB_TC_STATS
+    long long c_start = clock64(), c_plan = 0, c_r0 = 0;
+    long long w_a = 0, w_b = 0, w_c = 0;
+    int round_no = 0;
+#endif
     for (;;) {
+#ifdef MPB_TC_STATS
+        const long long c_scan0 = clock64();
+#endif
         if (warp == kTcEpiWarps + 1) {
             // ---- producer: follows the list; a tile is dropped (and with it the rest of the round: the list is
             // sorted) when its box is no longer closer than the block's largest k-th distance
@@ -650,16 +717,19 @@ __global__ void __launch_bounds__(kTcThreads, 1)
 #pragma unroll
                     for (int u = 0; u < kTcQueries / 32; ++u) {
                         const int qq = lane + 32 * u;
-                        r = fmaxf(r, tc_r2_of(*(volatile float *)&lk[qq * kTcKeep + kTcKeep - 1], nq2s[qq]));
+                        r = fmaxf(r, tc_r2_of(*(volatile float *)&sthr[qq], nq2s[qq]));
                     }
 #pragma unroll
                     for (int o = 16; o > 0; o >>= 1) r = fmaxf(r, __shfl_xor_sync(FULL_MASK, r, o));
                     if (lb >= r) i = n;            // -> the end-of-round mark
                     else t = (int)(uint32_t)e;
+                    visited += (t >= 0);
                 }
                 const int s = it % kTcStages;
                 if (lane == 0) {
+                    TC_CLK(c0);
                     if (it >= kTcStages) mbar_wait_backoff(&empty[s], (uint32_t)((it / kTcStages - 1) & 1));
+                    TC_ACC(w_a, c0);
                     *(volatile int *)&ctl->slot_tile[s] = t;
                     if (t >= 0) {
                         mbar_arrive_expect_tx(&full[s], kTcTileBytes);
@@ -680,9 +750,13 @@ __global__ void __launch_bounds__(kTcThreads, 1)
                 const uint32_t a_addr = smem_u32(sA);
                 for (;;) {
                     const int s = it % kTcStages, b = it & 1;
+                    TC_CLK(c0);
                     mbar_wait_backoff(&full[s], (uint32_t)((it / kTcStages) & 1));
+                    TC_ACC(w_a, c0);
                     const int t = *(volatile int *)&ctl->slot_tile[s];
+                    TC_CLK(c1);
                     if (it >= 2) mbar_wait_backoff(&tempty[b], (uint32_t)((it / 2 - 1) & 1));
+                    TC_ACC(w_b, c1);
                     ++it;
                     *(volatile int *)&ctl->acc_tile[b] = t;
                     if (t < 0) {
@@ -718,7 +792,9 @@ __global__ void __launch_bounds__(kTcThreads, 1)
             // ---- epilogue: lane = query; this warp's part of every tile is two chunks of 32 keys
             for (;;) {
                 const int b = it & 1;
+                TC_CLK(cw0);
                 mbar_wait_warp_backoff(&tfull[b], (uint32_t)((it / 2) & 1));
+                TC_ACC(w_a, cw0);
                 ++it;
                 const int t = *(volatile int *)&ctl->acc_tile[b];
                 if (t < 0) {
@@ -745,22 +821,68 @@ __global__ void __launch_bounds__(kTcThreads, 1)
                     measure(va, t * kTcTile + c0 * 32);
                     measure(vb, t * kTcTile + (c0 + 1) * 32);
                 } else {
+                    TC_CLK(c2);
                     examine(va, t * kTcTile + c0 * 32);
                     examine(vb, t * kTcTile + (c0 + 1) * 32);
+                    TC_ACC(w_b, c2);
                 }
             }
         }
         __syncwarp();
         __syncthreads();
+#ifdef MPB_TC_STATS
+        if (round_no++ == 0) c_r0 = clock64() - c_scan0;
+        if (tid == 0) TC_STAT(3, 1);
+#endif
         if (ctl->final_round) break;
+#ifdef MPB_TC_STATS
+        const long long c_p0 = clock64();
+#endif
+        // fresh thresholds for the planning: every buffer that took keys since its last cut is cut now
+        if (!DIAG && warp < kTcEpiWarps) {
+            for (int qq = warp; qq < kTcQueries; qq += kTcEpiWarps) {
+                if (cnts[qq] > kTcKeep) {
+                    float e = lk[qq * kTcBuf + lane];
+                    int ei = li[qq * kTcBuf + lane];
+                    sort32(e, ei);
+                    lk[qq * kTcBuf + lane] = lane < kTcKeep ? e : INFINITY;
+                    li[qq * kTcBuf + lane] = lane < kTcKeep ? ei : -1;
+                    if (lane == kTcKeep - 1) sthr[qq] = e;
+                    if (lane == 0) cnts[qq] = kTcKeep;
+                }
+            }
+        }
+        __syncthreads();
         plan_round();
+#ifdef MPB_TC_STATS
+        c_plan += clock64() - c_p0;
+        if (tid == 0) TC_STAT(7, ctl->list_n);
+#endif
     }
+    if (warp == kTcEpiWarps + 1 && lane == 0) atomicAdd(&const_cast<KnnHeader *>(h)->tiles_visited, (unsigned long long)visited);
+#ifdef MPB_TC_STATS
+    if (tid == 0) {
+        TC_STAT(0, 1);
+        TC_STAT(4, clock64() - c_start);
+        TC_STAT(5, c_plan);
+        TC_STAT(6, c_r0);
+    }
+    if (lane == 0) {
+        if (warp == kTcEpiWarps + 1) TC_STAT(8, w_a);
+        else if (warp == kTcEpiWarps) { TC_STAT(9, w_a); TC_STAT(10, w_b); }
+        else { TC_STAT(11, w_a); TC_STAT(12, w_b); }
+    }
+#endif
 
-    // the survivors of every query (ascending fp32 key) and its final threshold
-    if (!DIAG && warp < 4) {
-#pragma unroll
-        for (int p = 0; p < kTcKeep; ++p) surv_idx[(slot0 + q) * kTcKeep + p] = li[q * kTcKeep + p];
-        surv_thr[slot0 + q] = lk[q * kTcKeep + kTcKeep - 1];
+    // the 16 survivors of every query (ascending fp32 key) and its final threshold
+    if (!DIAG && warp < kTcEpiWarps) {
+        for (int qq = warp; qq < kTcQueries; qq += kTcEpiWarps) {
+            float e = lk[qq * kTcBuf + lane];
+            int ei = li[qq * kTcBuf + lane];
+            sort32(e, ei);
+            if (lane < kTcKeep) surv_idx[(slot0 + qq) * kTcKeep + lane] = ei;
+            if (lane == kTcKeep - 1) surv_thr[slot0 + qq] = e;
+        }
     }
     if constexpr (DIAG) {
         if (warp < kTcEpiWarps && d_pairs > 0) {
