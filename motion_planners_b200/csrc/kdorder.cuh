@@ -138,40 +138,41 @@ __global__ void __launch_bounds__(kRsThreads)
     hist[(size_t)threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];
 }
 
-// exclusive scan of hist[256 * nblocks] (digit-major), one block
+// exclusive scan of hist[256 * nblocks] (digit-major), one block: 1024 consecutive entries per trip (coalesced),
+// a block-wide scan of them, and a running carry
 __global__ void __launch_bounds__(1024) rs_scan_kernel(uint32_t *__restrict__ hist, int total)
 {
     __shared__ uint32_t warp_sums[32];
-    const int per = (total + 1023) / 1024;
-    const int lo = threadIdx.x * per;
-    const int hi = min(lo + per, total);
-    uint32_t s = 0;
-    for (int i = lo; i < hi; ++i) s += hist[i];
-    // block-wide exclusive scan of the per-thread sums
+    __shared__ uint32_t carry_s;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint32_t inc = s;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += v;
-    }
-    if (lane == 31) warp_sums[warp] = inc;
+    if (threadIdx.x == 0) carry_s = 0;
     __syncthreads();
-    if (warp == 0) {
-        uint32_t w = warp_sums[lane];
+    for (int base = 0; base < total; base += 1024) {
+        const int i = base + threadIdx.x;
+        const uint32_t v = i < total ? hist[i] : 0u;
+        uint32_t inc = v;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t v = __shfl_up_sync(0xffffffffu, w, o);
-            if (lane >= o) w += v;
+            const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += u;
         }
-        warp_sums[lane] = w;
-    }
-    __syncthreads();
-    uint32_t run = inc - s + (warp > 0 ? warp_sums[warp - 1] : 0u);
-    for (int i = lo; i < hi; ++i) {
-        const uint32_t v = hist[i];
-        hist[i] = run;
-        run += v;
+        if (lane == 31) warp_sums[warp] = inc;
+        __syncthreads();
+        const uint32_t carry = carry_s;
+        if (warp == 0) {
+            uint32_t w = warp_sums[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t u = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += u;
+            }
+            warp_sums[lane] = w;
+        }
+        __syncthreads();
+        if (i < total) hist[i] = carry + (warp > 0 ? warp_sums[warp - 1] : 0u) + inc - v;
+        __syncthreads();
+        if (threadIdx.x == 0) carry_s = carry + warp_sums[31];
+        __syncthreads();
     }
 }
 

@@ -27,9 +27,11 @@
 
 #ifdef MPB_TC_STATS
 #define TC_STAT(i, v) atomicAdd(&const_cast<KnnHeader *>(h)->dbg[i], (unsigned long long)(v))
+#define TC_CNT(v) ++v
 #define TC_CLK(var) const long long var = clock64()
 #define TC_ACC(acc, since) acc += clock64() - (since)
 #else
+#define TC_CNT(v) ((void)0)
 #define TC_CLK(var) ((void)0)
 #define TC_ACC(acc, since) ((void)0)
 #define TC_STAT(i, v) ((void)0)
@@ -44,6 +46,12 @@ constexpr int kTcQueries = 128;                // queries per CTA = MMA M = TMEM
 #ifndef MPB_TC_SLEEP_EPI
 #define MPB_TC_SLEEP_EPI 32       // ns between polls of an epilogue warp
 #endif
+#ifndef MPB_TC_WAIT_HINT
+#define MPB_TC_WAIT_HINT 4000    // ns an epilogue warp may stay suspended inside one mbarrier.try_wait
+#endif
+#ifndef MPB_TC_BULK_MIN
+#define MPB_TC_BULK_MIN 5         // flagged lanes of a chunk from which the whole warp takes the sorting-network path
+#endif
 #ifndef MPB_TC_FIRST_BOUND
 #define MPB_TC_FIRST_BOUND 0.5f
 #endif
@@ -51,14 +59,13 @@ constexpr int kTcQueries = 128;                // queries per CTA = MMA M = TMEM
 #define MPB_TC_PARTS 4
 #endif
 #ifndef MPB_TC_STAGES
-#define MPB_TC_STAGES 4
+#define MPB_TC_STAGES 3
 #endif
 constexpr int kTcStages = MPB_TC_STAGES;       // shared-memory ring depth
 constexpr int kTcKeep = 16;                    // survivors per list
-constexpr int kTcBuf = 32;                     // entries of a query's buffer: kTcKeep sorted survivors + appended takers
 constexpr int kTcParts = MPB_TC_PARTS;          // epilogue warps per TMEM lane quarter
 constexpr int kTcEpiWarps = 4 * kTcParts;      // warp w: lane quarter w & 3, part w >> 2 (8 / kTcParts chunks of 32 keys per tile)
-constexpr int kTcThreads = 32 * (kTcEpiWarps + 2);
+constexpr int kTcThreads = 32 * (kTcEpiWarps + 3);   // + MMA issue, tile producer, threshold merger
 #ifndef MPB_TC_SHARED_LIST
 #define MPB_TC_SHARED_LIST 1      // 1: the warps of a lane quarter share one list per query (per-query lock)
 #endif
@@ -69,7 +76,7 @@ constexpr uint32_t kTcSbo = (kTcK / 4) * 128;  // bytes between 8-row groups
 constexpr int kTcTileBytes = (kTcTile / 8) * (int)kTcSbo;      // 24576
 constexpr int kTcQueryBytes = (kTcQueries / 8) * (int)kTcSbo;  // 12288
 constexpr int kTcMaxDim = 7;
-constexpr int kTcListCap = 2048;                // candidate tiles planned per round (shared-memory list)
+constexpr int kTcListCap = 512;                 // candidate tiles planned per round (shared-memory list)
 constexpr int kTcHalf = kTcTile / 2;            // points per k-d leaf: a tile is two leaves, a query block one
 static_assert(kTcHalf == kTcQueries, "a query block of the sample set itself is one half tile");
 
@@ -116,10 +123,22 @@ __device__ __forceinline__ void mbar_wait_backoff(uint64_t *bar, uint32_t parity
 
 // the same for a whole converged warp (the vote keeps the code after it warp-uniform); sixteen warps polling
 // without a pause took a third of the SM's issue slots
+__device__ __forceinline__ bool mbar_try_wait_hint(uint64_t *bar, uint32_t parity, uint32_t ns)
+{
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity), "r"(ns)
+        : "memory");
+    return ok != 0;
+}
 __device__ __forceinline__ void mbar_wait_warp_backoff(uint64_t *bar, uint32_t parity)
 {
-    for (uint32_t spins = 0; !__all_sync(0xffffffffu, mbar_try_wait(bar, parity)); ++spins) {
-        __nanosleep(MPB_TC_SLEEP_EPI);
+    // the try_wait itself suspends the thread (up to the hinted time) and is woken by the phase change
+    for (uint32_t spins = 0; !__all_sync(0xffffffffu, mbar_try_wait_hint(bar, parity, MPB_TC_WAIT_HINT)); ++spins) {
         if (spins > (1u << 26)) __trap();
     }
 }
@@ -138,6 +157,73 @@ __device__ __forceinline__ void tmem_ld32(uint32_t (&v)[32], uint32_t taddr)
         : "r"(taddr));
 }
 
+
+
+// ---- sorting networks over a thread's registers (every index is a compile-time constant after unrolling) ------
+// compare-exchange on keys alone
+#define TC_CE(x, y)                     \
+    {                                   \
+        const float lo_ = fminf(x, y);  \
+        const float hi_ = fmaxf(x, y);  \
+        x = lo_;                        \
+        y = hi_;                        \
+    }
+// ascending bitonic sort of a[OFF .. OFF + N)
+template <int OFF, int N, int LEN>
+__device__ __forceinline__ void tc_sort_asc(float (&a)[LEN])
+{
+#pragma unroll
+    for (int k = 2; k <= N; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+#pragma unroll
+            for (int i = 0; i < N; ++i) {
+                const int l = i ^ j;
+                if (l > i) {
+                    if ((i & k) == 0) {
+                        TC_CE(a[OFF + i], a[OFF + l]);
+                    } else {
+                        TC_CE(a[OFF + l], a[OFF + i]);
+                    }
+                }
+            }
+        }
+    }
+}
+// a[0 .. N) is bitonic: make it ascending (keys alone)
+template <int N, int LEN>
+__device__ __forceinline__ void tc_merge_asc(float (&a)[LEN])
+{
+#pragma unroll
+    for (int j = N >> 1; j > 0; j >>= 1) {
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+            const int l = i ^ j;
+            if (l > i) TC_CE(a[i], a[l]);
+        }
+    }
+}
+// the same with a payload riding along (equal keys keep their order of arrival: the lower position wins)
+template <int N>
+__device__ __forceinline__ void tc_merge_asc_kv(float (&a)[N], int (&b)[N])
+{
+#pragma unroll
+    for (int j = N >> 1; j > 0; j >>= 1) {
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+            const int l = i ^ j;
+            if (l > i) {
+                const bool sw = a[l] < a[i];
+                const float ka = sw ? a[l] : a[i], kb = sw ? a[i] : a[l];
+                const int va = sw ? b[l] : b[i], vb = sw ? b[i] : b[l];
+                a[i] = ka;
+                a[l] = kb;
+                b[i] = va;
+                b[l] = vb;
+            }
+        }
+    }
+}
 
 // ---- candidate tiles in the operand image ------------------------------------------------------------
 // One block per tile.  Tile t holds k-d leaves 2t and 2t+1 of the sample order (at most 128 points each, slot
@@ -160,7 +246,10 @@ __global__ void __launch_bounds__(kTcTile)
     if (leaf < leaves) {
         const int64_t start = kd_leaf_start(leaf, N, leaves);
         const int64_t cnt = kd_leaf_start(leaf + 1, N, leaves) - start;
-        if (i < cnt) j = (int64_t)perm[start + i];
+        // slot i of the half holds leaf position 37 i mod 128: the 32-column chunks an epilogue warp reads are
+        // then fair samples of the leaf instead of slices of its (sorted) last coordinate
+        const int src = (i * 37) & (kTcHalf - 1);
+        if (src < cnt) j = (int64_t)perm[start + src];
     }
     float row[kTcK], f[D];
 #pragma unroll
@@ -239,19 +328,18 @@ struct TcCtl {                 // per-CTA control block in shared memory
     int cursor;                // tiles below this index were all visited (rounds before any threshold existed)
     int has_lo;
     int final_round;           // the planned round covers everything that is left
+    int round_over;            // the epilogue has reached the end of the round (tells the threshold merger to stop)
     float rmax2;
 };
 
 struct TcSmem {
     static constexpr int A_OFF = 0;
     static constexpr int B_OFF = A_OFF + kTcQueryBytes;
-    static constexpr int LK_OFF = B_OFF + kTcStages * kTcTileBytes;
-    static constexpr int LI_OFF = LK_OFF + kTcBuf * kTcQueries * 4;
-    static constexpr int SCR_OFF = LI_OFF + kTcBuf * kTcQueries * 4;         // [epilogue warp][32 lanes][33]
-    static constexpr int THR_OFF = SCR_OFF + kTcEpiWarps * 32 * 33 * 4;        // [part][128] published thresholds
-    static constexpr int LOCK_OFF = THR_OFF + kTcLists * kTcQueries * 4;       // [128] list locks (shared-list build)
-    static constexpr int CNT_OFF = LOCK_OFF + kTcQueries * 4;                  // [128] entries in each query's buffer
-    static constexpr int NQ_OFF = CNT_OFF + kTcQueries * 4;                    // [128] |q^|^2, rounded up
+    static constexpr int PK_OFF = B_OFF + kTcStages * kTcTileBytes;            // [epilogue warp][32 lanes][kTcKeep + 1] keys
+    static constexpr int PI_OFF = PK_OFF + (kTcKeep + 1) * kTcEpiWarps * 32 * 4;   // the same shape: their candidate slots
+    static constexpr int SCR_OFF = PI_OFF + (kTcKeep + 1) * kTcEpiWarps * 32 * 4;  // [epilogue warp][32 lanes][33]
+    static constexpr int THR_OFF = SCR_OFF + kTcEpiWarps * 32 * 33 * 4;        // [128] the queries' published thresholds
+    static constexpr int NQ_OFF = THR_OFF + kTcQueries * 4;                    // [128] |q^|^2, rounded up
     static constexpr int LIST_OFF = NQ_OFF + kTcQueries * 4;                   // [kTcListCap] (lower bound, tile) keys
     static constexpr int CTL_OFF = LIST_OFF + kTcListCap * 8;
     static constexpr int BAR_OFF = CTL_OFF + 640;
@@ -260,7 +348,7 @@ struct TcSmem {
 static_assert(sizeof(TcCtl) <= 640, "control block overflows its slot");
 static_assert(TcSmem::LIST_OFF % 8 == 0 && TcSmem::CTL_OFF % 8 == 0 && TcSmem::BAR_OFF % 8 == 0, "alignment");
 static_assert(TcSmem::BYTES <= 227 * 1024, "shared memory per CTA");
-static_assert(MPB_TC_SHARED_LIST == 1, "the pruned scan reads the block's thresholds from the shared lists");
+static_assert(kTcParts == 4 && kTcEpiWarps == 16, "four epilogue warps per TMEM lane quarter");
 
 // squared k-th distance implied by a list threshold (a key is d^2 - |q^|^2), rounded up; +inf stays +inf
 __device__ __forceinline__ float tc_r2_of(float thr, float nq2_up)
@@ -299,12 +387,10 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     extern __shared__ __align__(1024) unsigned char smem[];
     unsigned char *sA = smem + TcSmem::A_OFF;
     unsigned char *sB = smem + TcSmem::B_OFF;
-    float *lk = reinterpret_cast<float *>(smem + TcSmem::LK_OFF);      // [128][kTcBuf] keys kept per query
-    int *li = reinterpret_cast<int *>(smem + TcSmem::LI_OFF);          // [128][kTcBuf] their candidate slots
-    int *cnts = reinterpret_cast<int *>(smem + TcSmem::CNT_OFF);
+    float *pk = reinterpret_cast<float *>(smem + TcSmem::PK_OFF);      // private sorted lists: keys
+    int *pi = reinterpret_cast<int *>(smem + TcSmem::PI_OFF);          // ... candidate slots
     float *scr = reinterpret_cast<float *>(smem + TcSmem::SCR_OFF);
     float *sthr = reinterpret_cast<float *>(smem + TcSmem::THR_OFF);
-    int *locks = reinterpret_cast<int *>(smem + TcSmem::LOCK_OFF);
     float *nq2s = reinterpret_cast<float *>(smem + TcSmem::NQ_OFF);
     unsigned long long *list = reinterpret_cast<unsigned long long *>(smem + TcSmem::LIST_OFF);
     TcCtl *ctl = reinterpret_cast<TcCtl *>(smem + TcSmem::CTL_OFF);
@@ -354,15 +440,9 @@ __global__ void __launch_bounds__(kTcThreads, 1)
             }
         }
     }
-    for (int i = tid; i < kTcBuf * kTcQueries; i += kTcThreads) {
-        lk[i] = INFINITY;
-        li[i] = -1;
-    }
-    for (int i = tid; i < kTcQueries; i += kTcThreads) {
-        sthr[i] = INFINITY;
-        locks[i] = 0;
-        cnts[i] = 0;
-    }
+    for (int i = tid; i < (kTcKeep + 1) * kTcEpiWarps * 32; i += kTcThreads) pk[i] = INFINITY;
+    for (int i = tid; i < (kTcKeep + 1) * kTcEpiWarps * 32; i += kTcThreads) pi[i] = -1;
+    for (int i = tid; i < kTcQueries; i += kTcThreads) sthr[i] = INFINITY;
     if (tid == 0) {
         for (int s = 0; s < kTcStages; ++s) {
             mbar_init(&full[s], 1);
@@ -377,6 +457,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         ctl->has_lo = 0;
         ctl->lo_key = 0ull;
         ctl->final_round = 0;
+        ctl->round_over = 0;
     }
     if (warp == kTcEpiWarps) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
@@ -535,6 +616,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
             }
         }
         if (tid == 0) {
+            ctl->round_over = 0;
             ctl->list_n = n;
             if (n > 0 && rmax2 < 3.0e38f && ctl->red_f[4] == 0.f) {     // a round ordered by distance, not by index
                 ctl->lo_key = list[n - 1];
@@ -548,32 +630,101 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     const int quarter = warp & 3, part = warp >> 2;
     const int q = quarter * 32 + lane;             // this thread's query (epilogue warps only)
     float thr = INFINITY;
+#ifdef MPB_TC_STATS
+    unsigned n_ev = 0, n_tk = 0, n_bulk = 0;
+#endif
     const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
     float *rows = scr + (warp < kTcEpiWarps ? warp : 0) * 32 * 33;
-    // The 32 keys a lane just received are examined with one min-tree.  When some lane's minimum beats its
-    // threshold, the flagged lanes park their keys in the warp's scratch rows, and each flagged lane is then
-    // served by the WHOLE warp: lane j reads key j of that row, one ballot finds the takers, and all takers are
-    // APPENDED side by side to the query's 32-entry buffer.  Only when the buffer is full is it sorted (a bitonic
-    // network over the 32 lanes) and cut back to its 16 smallest entries, whose largest becomes the query's new
-    // threshold.  A threshold is therefore up to 16 appends stale, which lets a few more keys in, but an append
-    // costs one store where a sorted insert cost a hundred instructions -- and with the nearest tiles first
-    // every query takes about 200 keys (measured), most of them from the first few tiles.
-    auto sort32 = [&](float &e, int &ei) {
+    // ---- what a query keeps.  Every epilogue thread (part p of query q) owns a PRIVATE sorted list of the 16
+    // smallest keys seen in its part's columns; the warp that owns it is the only writer, so inserting needs no
+    // lock and no fence.  The query's threshold is the 16th smallest key of the union of its four lists.  Lists only
+    // ever decrease, entry by entry, so that value may be computed from plain racy reads at any time -- whatever a
+    // reader sees is at least as large as the truth, i.e. a valid, slightly stale threshold: one warp of each lane
+    // quarter (taking turns) merges the four sorted lists of its 32 queries every fourth tile and publishes the
+    // result.  Candidates are dealt to the four parts like cards (the pack kernel strides the slots), so each part
+    // sees a fair quarter of every tile.
+    constexpr int KS = kTcKeep + 1;                // key lists are padded: lane-strided reads stay conflict-free
+    auto kbase = [&](int w, int l) -> float * { return pk + (w * 32 + l) * KS; };
+    auto ibase = [&](int w, int l) -> int * { return pi + (w * 32 + l) * KS; };
+    // 16th smallest key of the union of this lane's query's four sorted lists (inf while fewer than 16 keys)
+    auto union16 = [&](int quarter) -> float {
+        int hd[kTcParts];
+        float a[kTcParts];
 #pragma unroll
-        for (int k2 = 2; k2 <= 32; k2 <<= 1) {
-#pragma unroll
-            for (int j = k2 >> 1; j > 0; j >>= 1) {
-                const float ok = __shfl_xor_sync(FULL_MASK, e, j);
-                const int oi = __shfl_xor_sync(FULL_MASK, ei, j);
-                const bool other_less = (ok < e) || (ok == e && oi < ei);
-                const bool keep_min = ((lane & j) == 0) == ((lane & k2) == 0);
-                if (other_less == keep_min) {
-                    e = ok;
-                    ei = oi;
-                }
-            }
+        for (int p = 0; p < kTcParts; ++p) {
+            hd[p] = 0;
+            a[p] = *(volatile float *)(kbase(p * 4 + quarter, lane));
         }
+        // The largest of 16 values taken from 16 distinct list positions.  At rest that is the union's 16th
+        // smallest key.  While other warps insert, a position may be read before or after a shift (so the same key
+        // can turn up twice, or the pops may not come in order), but whatever is read from a position is at least
+        // that position's final value, and the largest of any 16 positions' final values is at least the union's
+        // 16th smallest: the result is a valid threshold in every interleaving.
+        float top = -INFINITY;
+#pragma unroll 1
+        for (int s = 0; s < kTcKeep; ++s) {
+            int best = 0;
+            float bv = a[0];
+#pragma unroll
+            for (int p = 1; p < kTcParts; ++p)
+                if (a[p] < bv) {
+                    bv = a[p];
+                    best = p;
+                }
+            top = fmaxf(top, bv);
+#pragma unroll
+            for (int p = 0; p < kTcParts; ++p)
+                if (p == best) {
+                    ++hd[p];
+                    a[p] = hd[p] < kTcKeep ? *(volatile float *)(kbase(p * 4 + quarter, lane) + hd[p]) : INFINITY;
+                }
+        }
+        return top;
     };
+
+    // Many lanes of a chunk flagged (the first tiles a block reads): instead of serving them one by one, every lane
+    // takes the 16 smallest of its 32 keys through a sorting network over its own registers and merges them with
+    // its list, all 32 lanes side by side -- about 700 instructions for the warp whatever the number of takers,
+    // where one sorted insert costs a hundred.  The column of a key rides through the network in its five lowest
+    // mantissa bits (a perturbation of at most 31 ulp, which the certificate's eta covers).
+    auto bulk = [&](const uint32_t (&v)[32], int cbase) {
+        float a[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+            a[j] = __uint_as_float(v[j]) < thr ? __uint_as_float((v[j] & 0xffffffe0u) | (uint32_t)j) : INFINITY;
+        tc_sort_asc<0, 16, 32>(a);
+        tc_sort_asc<16, 16, 32>(a);
+        float c[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) c[i] = fminf(a[i], a[31 - i]);      // the 16 smallest, as a bitonic sequence
+        tc_merge_asc<16, 16>(c);
+        float *kb = kbase(warp, lane);
+        int *ib = ibase(warp, lane);
+        float d[16];
+        int di[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const float mine = kb[i], cand = c[15 - i];
+            const bool take = cand < mine;                                // the incumbent wins a tie
+            d[i] = take ? cand : mine;
+            di[i] = take ? cbase + (int)(__float_as_uint(cand) & 31u) : ib[i];
+        }
+        tc_merge_asc_kv<16>(d, di);
+        // every position only ever gets a smaller key (the new list is the 16 smallest of old list + chunk), which
+        // is what the unsynchronised readers of union16 rely on
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            kb[i] = d[i];
+            ib[i] = di[i];
+        }
+        thr = fminf(thr, d[15]);
+        TC_CNT(n_bulk);
+    };
+
+    // The 32 keys a lane just received are examined with one min-tree.  When some lane's minimum beats its
+    // threshold, the flagged lanes park the groups of eight that hold such a key in the warp's scratch rows, and
+    // each flagged lane is then served by the WHOLE warp: lane j reads key j of that row, one ballot finds the
+    // takers, and each taker is inserted into the lane's private list by lanes 0..15 side by side.
     auto examine = [&](const uint32_t (&v)[32], int cbase) {
         float g[4];        // minima of the four groups of eight keys
 #pragma unroll
@@ -585,12 +736,14 @@ __global__ void __launch_bounds__(kTcThreads, 1)
         const float m = fminf(fminf(g[0], g[1]), fminf(g[2], g[3]));
         unsigned flagged = __ballot_sync(FULL_MASK, m < thr);
         if (flagged == 0) return;
-        // the threshold published for the query by whichever warp cut its buffer last (read without
-        // synchronisation: a stale value is only a larger one); then the chunk is tested again
+        // the union threshold published last for the query; then the chunk is tested again
         thr = fminf(thr, *(volatile float *)&sthr[q]);
         flagged = __ballot_sync(FULL_MASK, m < thr);
         if (flagged == 0) return;
-        // only the groups of eight that hold a key below the threshold are parked
+        if (__popc(flagged) >= MPB_TC_BULK_MIN) {
+            bulk(v, cbase);
+            return;
+        }
         unsigned gm = 0;
 #pragma unroll
         for (int gi = 0; gi < 4; ++gi) {
@@ -601,58 +754,42 @@ __global__ void __launch_bounds__(kTcThreads, 1)
             }
         }
         __syncwarp();
-        const unsigned lt = (1u << lane) - 1u;
         while (flagged) {
             const int L = __ffs(flagged) - 1;
             flagged &= flagged - 1;
-            const int qL = quarter * 32 + L;
-            if (lane == 0) TC_STAT(1, 1);
-            // the four warps of this lane quarter append to the same buffer: one warp at a time per query
-            if (lane == 0) {
-                for (uint32_t spins = 0; atomicCAS(&locks[qL], 0, 1) != 0; ++spins)
-                    if (spins > (1u << 24)) __trap();
-            }
-            __syncwarp();
-            __threadfence_block();
-            float thrL = *(volatile float *)&sthr[qL];
-            int c = *(volatile int *)&cnts[qL];
+            TC_CNT(n_ev);
+            float thrL = __shfl_sync(FULL_MASK, thr, L);
             const unsigned gmL = __shfl_sync(FULL_MASK, gm, L);
             const float mine = rows[L * 33 + lane];      // stale where the group was not parked: masked out
-            bool taker = ((gmL >> (lane >> 3)) & 1u) && mine < thrL;
-            float *bk = lk + qL * kTcBuf;
-            int *bi = li + qL * kTcBuf;
-            for (;;) {
-                const unsigned tk = __ballot_sync(FULL_MASK, taker);
-                if (tk == 0) break;
-                const int nt = __popc(tk), room = kTcBuf - c, rank = __popc(tk & lt);
-                if (lane == 0) TC_STAT(2, nt < room ? nt : room);
-                if (taker && rank < room) {
-                    bk[c + rank] = mine;
-                    bi[c + rank] = cbase + lane;
-                    taker = false;
+            unsigned takers = __ballot_sync(FULL_MASK, ((gmL >> (lane >> 3)) & 1u) && mine < thrL);
+            float *kb = kbase(warp, L);
+            int *ib = ibase(warp, L);
+            while (takers) {
+                const int j = __ffs(takers) - 1;
+                takers &= takers - 1;
+                const float key = __shfl_sync(FULL_MASK, mine, j);
+                if (key < thrL) {
+                    TC_CNT(n_tk);
+                    const bool in_list = lane < kTcKeep;
+                    const float e = in_list ? kb[lane] : INFINITY;
+                    const int ei = in_list ? ib[lane] : -1;
+                    // equal keys: the newcomer goes after the incumbents
+                    const int pos = __popc(__ballot_sync(FULL_MASK, in_list && e <= key));
+                    if (lane >= pos && lane < kTcKeep - 1) {
+                        kb[lane + 1] = e;
+                        ib[lane + 1] = ei;
+                    }
+                    if (lane == pos) {
+                        kb[pos] = key;
+                        ib[pos] = cbase + j;
+                    }
+                    // the list's new 16th: what was its 15th, or the key itself
+                    const float e14 = __shfl_sync(FULL_MASK, e, kTcKeep - 2);
+                    thrL = fminf(thrL, pos == kTcKeep - 1 ? key : e14);
+                    __syncwarp();
                 }
-                c += nt < room ? nt : room;
-                if (nt < room) break;
-                // full: keep the 16 smallest (sorted), the 16th is the new threshold
-                __syncwarp();
-                float e = bk[lane];
-                int ei = bi[lane];
-                sort32(e, ei);
-                thrL = __shfl_sync(FULL_MASK, e, kTcKeep - 1);
-                bk[lane] = lane < kTcKeep ? e : INFINITY;
-                bi[lane] = lane < kTcKeep ? ei : -1;
-                c = kTcKeep;
-                taker = taker && mine < thrL;
-                __syncwarp();
             }
             if (lane == L) thr = thrL;
-            if (lane == 0) {
-                *(volatile int *)&cnts[qL] = c;
-                *(volatile float *)&sthr[qL] = thrL;
-            }
-            __syncwarp();
-            __threadfence_block();
-            if (lane == 0) atomicExch(&locks[qL], 0);
         }
         __syncwarp();
     };
@@ -697,7 +834,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     uint32_t visited = 0;
 #ifdef MPB_TC_STATS
     long long c_start = clock64(), c_plan = 0, c_r0 = 0;
-    long long w_a = 0, w_b = 0, w_c = 0;
+    long long w_a = 0, w_b = 0;
     int round_no = 0;
 #endif
     for (;;) {
@@ -740,6 +877,16 @@ __global__ void __launch_bounds__(kTcThreads, 1)
                 }
                 ++it;
                 __syncwarp();
+            }
+        } else if (warp == kTcEpiWarps + 2) {
+            // ---- threshold merger: keeps publishing the union threshold of every query (one lane quarter per
+            // trip) from plain reads of the private lists, until the epilogue has seen the end of the round
+            if constexpr (!DIAG) {
+                for (int qt = 0; *(volatile int *)&ctl->round_over == 0; qt = (qt + 1) & 3) {
+                    const float u = union16(qt);
+                    float *dst = &sthr[qt * 32 + lane];
+                    if (u < *(volatile float *)dst) *(volatile float *)dst = u;
+                }
             }
         } else if (warp == kTcEpiWarps) {
             // ---- MMA issue: three k-steps per tile into accumulator it & 1
@@ -800,6 +947,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
                 if (t < 0) {
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&tempty[b]);
+                    if (tid == 0) *(volatile int *)&ctl->round_over = 1;
                     break;
                 }
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -838,20 +986,8 @@ __global__ void __launch_bounds__(kTcThreads, 1)
 #ifdef MPB_TC_STATS
         const long long c_p0 = clock64();
 #endif
-        // fresh thresholds for the planning: every buffer that took keys since its last cut is cut now
-        if (!DIAG && warp < kTcEpiWarps) {
-            for (int qq = warp; qq < kTcQueries; qq += kTcEpiWarps) {
-                if (cnts[qq] > kTcKeep) {
-                    float e = lk[qq * kTcBuf + lane];
-                    int ei = li[qq * kTcBuf + lane];
-                    sort32(e, ei);
-                    lk[qq * kTcBuf + lane] = lane < kTcKeep ? e : INFINITY;
-                    li[qq * kTcBuf + lane] = lane < kTcKeep ? ei : -1;
-                    if (lane == kTcKeep - 1) sthr[qq] = e;
-                    if (lane == 0) cnts[qq] = kTcKeep;
-                }
-            }
-        }
+        // exact thresholds for the planning (every list is at rest here)
+        if (!DIAG && warp < kTcParts) sthr[q] = union16(quarter);
         __syncthreads();
         plan_round();
 #ifdef MPB_TC_STATS
@@ -870,19 +1006,42 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     if (lane == 0) {
         if (warp == kTcEpiWarps + 1) TC_STAT(8, w_a);
         else if (warp == kTcEpiWarps) { TC_STAT(9, w_a); TC_STAT(10, w_b); }
-        else { TC_STAT(11, w_a); TC_STAT(12, w_b); }
+        else { TC_STAT(11, w_a); TC_STAT(12, w_b); TC_STAT(1, n_ev); TC_STAT(2, n_tk); TC_STAT(13, n_bulk); }
     }
 #endif
 
-    // the 16 survivors of every query (ascending fp32 key) and its final threshold
-    if (!DIAG && warp < kTcEpiWarps) {
-        for (int qq = warp; qq < kTcQueries; qq += kTcEpiWarps) {
-            float e = lk[qq * kTcBuf + lane];
-            int ei = li[qq * kTcBuf + lane];
-            sort32(e, ei);
-            if (lane < kTcKeep) surv_idx[(slot0 + qq) * kTcKeep + lane] = ei;
-            if (lane == kTcKeep - 1) surv_thr[slot0 + qq] = e;
+    // the 16 survivors of every query (ascending fp32 key: the 4-way merge of its lists) and its final threshold
+    if (!DIAG && warp < kTcParts) {
+        int hd[kTcParts];
+        float a[kTcParts];
+#pragma unroll
+        for (int p = 0; p < kTcParts; ++p) {
+            hd[p] = 0;
+            a[p] = kbase(p * 4 + quarter, lane)[0];
         }
+        float last = INFINITY;
+#pragma unroll 1
+        for (int s = 0; s < kTcKeep; ++s) {
+            int best = 0;
+            float bv = a[0];
+#pragma unroll
+            for (int p = 1; p < kTcParts; ++p)
+                if (a[p] < bv) {
+                    bv = a[p];
+                    best = p;
+                }
+            last = bv;
+            int slot = -1;
+#pragma unroll
+            for (int p = 0; p < kTcParts; ++p)
+                if (p == best) {
+                    slot = ibase(p * 4 + quarter, lane)[hd[p]];
+                    ++hd[p];
+                    a[p] = hd[p] < kTcKeep ? kbase(p * 4 + quarter, lane)[hd[p]] : INFINITY;
+                }
+            surv_idx[(slot0 + q) * kTcKeep + s] = (bv < INFINITY) ? slot : -1;
+        }
+        surv_thr[slot0 + q] = last;
     }
     if constexpr (DIAG) {
         if (warp < kTcEpiWarps && d_pairs > 0) {
@@ -978,7 +1137,9 @@ __global__ void __launch_bounds__(256)
         constexpr double U22 = 2.384185791015625e-07;    // 2^-22: TF32 split and accumulation budget per term
         const double nq = sqrt(nq2);
         const double delta = U24 * (R + nq) * 1.0001 + 1e-30;
-        const double eta = (double)(kTcK + 8) * U22 * 1.01 * (R * R + 2.0 * nq * R) + 1e-37;
+        // 2^-22 per operand column and accumulation step (measured: under 2 x 2^-22 in all, mpb_knn_tc_key_error), plus
+        // 16 x 2^-22 = 2^-18 for the column bits the sorting-network path writes into a key
+        const double eta = (double)(kTcK + 8 + 16) * U22 * 1.01 * (R * R + 2.0 * nq * R) + 1e-37;
         double slow = T - eta + nq2;
         slow -= 1e-12 * (fabs(T) + eta + nq2);
         double bound = 0.;

@@ -38,6 +38,6 @@ if __name__ == "__main__":
     u = raw[off:off + 136].view(np.uint64)
     ctas = max(1, int(u[1]))
     print("search ms %.3f  fallbacks %d  tiles/CTA %.1f" % (e0.elapsed_time(e1), int(stats[0]), int(u[0]) / ctas))
-    names = ["ctas", "flagged-lane events", "takers inserted", "rounds", "cycles total", "cycles plan", "cycles round0", "tiles listed", "producer wait empty", "mma wait full", "mma wait tempty", "epi wait tfull (16 warps)", "epi examine (16 warps)", "-", "-", "-"]
+    names = ["ctas", "flagged-lane events", "takers inserted", "rounds", "cycles total", "cycles plan", "cycles round0", "tiles listed", "producer wait empty", "mma wait full", "mma wait tempty", "epi wait tfull (16 warps)", "epi examine (16 warps)", "bulk chunks (thread count)", "-", "-"]
     for n, v in zip(names, u[1:]):
         print("  %-22s %14d   per CTA %10.1f" % (n, int(v), int(v) / ctas))
