@@ -645,6 +645,11 @@ bool use_tc(int64_t N, int D)
     return N >= kTcAutoMin[D];
 }
 
+// k-d partitions of the tensor-core scan: samples in leaves of at most 128 (two per candidate tile), a foreign query
+// set in leaves of at most 128 (one per query block)
+inline KdPlan tc_sample_plan(int64_t N, int D) { return kd_plan(N, 2 * ((N + kTcTile - 1) / kTcTile), D, true); }
+inline KdPlan tc_query_plan(int64_t M, int D) { return kd_plan(M, (M + kTcQueries - 1) / kTcQueries, D, false); }
+
 struct WsLayout {
     size_t packed_off, packed_bytes, tc_off, tc_bytes, slot_off, slot_bytes, box_off, box_bytes, fb_off, fb_bytes, surv_off,
         surv_bytes, thr_off, thr_bytes, qord_off, qord_bytes, sort_off, sort_bytes, total;
@@ -666,7 +671,7 @@ WsLayout ws_layout(int64_t N, int64_t M, int D, bool allow_tc = true)
     L.n_pad = L.n_tiles * TILE;
     L.packed_off = kHeaderBytes;
     L.packed_bytes = (size_t)L.n_pad * P * 16;
-    L.tc_tiles = tc ? (N + kTcTile - 1) / kTcTile : 0;
+    L.tc_tiles = tc ? tc_sample_plan(N, D).leaves / 2 : 0;
     L.tc_off = (L.packed_off + L.packed_bytes + 1023) & ~(size_t)1023;
     L.tc_bytes = (size_t)L.tc_tiles * kTcTileBytes;
     L.slot_off = up(L.tc_off + L.tc_bytes);
@@ -678,7 +683,7 @@ WsLayout ws_layout(int64_t N, int64_t M, int D, bool allow_tc = true)
     L.fb_bytes = up(m * sizeof(int));
     // query slots: blocks of 128; the sample set as its own query set uses the tiles' own slots
     const int64_t own = (M == N) ? L.tc_tiles * kTcTile : 0;
-    const int64_t other = ((M + kTcQueries - 1) / kTcQueries) * kTcQueries;
+    const int64_t other = tc ? tc_query_plan(M > 0 ? M : 1, D).leaves * kTcQueries : 0;
     L.tc_slots = tc ? (own > other ? own : other) : 0;
     L.surv_off = L.fb_off + L.fb_bytes;
     L.surv_bytes = tc ? up((size_t)L.tc_slots * kTcSurvivors * sizeof(int)) : 0;
@@ -757,8 +762,8 @@ int launch_prepare(const double *x, int64_t N, const Weights &wt, void *ws, bool
             float *boxes = reinterpret_cast<float *>(base + L.box_off);
             kd_dim_order_kernel<<<1, 32, 0, st>>>(h, D);
             MPB_LAUNCH_CHECK();
-            const int64_t leaves = 2 * L.tc_tiles;
-            const KdPlan plan = kd_plan(N, leaves, D);
+            const KdPlan plan = tc_sample_plan(N, D);
+            const int64_t leaves = plan.leaves;
             const KdScratch scratch = kd_scratch_at(base + L.sort_off, N);
             const uint32_t *perm = nullptr;
             int rc = kd_order<D>(x, N, wt, h, plan, scratch, &perm, st, &g_last_launches);
@@ -841,8 +846,8 @@ int launch_search(const double *x, int64_t N, const double *qs, int64_t M, const
             const bool own = (qs == x && M == N);
             if (!own) {
                 // any other query set gets its own k-d order, one leaf of at most 128 queries per block
-                blocks = (M + kTcQueries - 1) / kTcQueries;
-                const KdPlan plan = kd_plan(M, blocks, D);
+                const KdPlan plan = tc_query_plan(M, D);
+                blocks = plan.leaves;
                 const KdScratch scratch = kd_scratch_at(base + L.sort_off, N > M ? N : M);
                 const uint32_t *perm = nullptr;
                 int rc = kd_order<D>(qs, M, wt, h, plan, scratch, &perm, st, &g_last_launches);
@@ -888,8 +893,8 @@ int launch_tc_diag(const double *x, int64_t N, const double *qs, int64_t M, cons
         if (L.tc_tiles == 0) return MPB_EINVAL;
         KnnHeader *h = reinterpret_cast<KnnHeader *>(ws);
         char *base = reinterpret_cast<char *>(ws);
-        const int64_t blocks = (M + kTcQueries - 1) / kTcQueries;
-        const KdPlan plan = kd_plan(M, blocks, D);
+        const KdPlan plan = tc_query_plan(M, D);
+        const int64_t blocks = plan.leaves;
         const KdScratch scratch = kd_scratch_at(base + L.sort_off, N > M ? N : M);
         const uint32_t *perm = nullptr;
         int rc = kd_order<D>(qs, M, wt, h, plan, scratch, &perm, st, &g_last_launches);

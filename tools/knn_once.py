@@ -14,4 +14,4 @@ for _ in range(reps):
     e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True); e2 = torch.cuda.Event(enable_timing=True)
     index._prepared = False
     e0.record(); index.prepare(N); e1.record(); index.search(x, 11, stats=stats); e2.record(); torch.cuda.synchronize()
-    print("prepare %.3f ms  search %.3f ms  fallbacks %d  tiles/block %.1f" % (e0.elapsed_time(e1), e1.elapsed_time(e2), int(stats[0]), int(stats[1]) / max(1, 2 * ((N + 255) // 256))))
+    print("prepare %.3f ms  search %.3f ms  fallbacks %d  tiles per 128 queries %.1f" % (e0.elapsed_time(e1), e1.elapsed_time(e2), int(stats[0]), int(stats[1]) * 128.0 / N))
