@@ -63,6 +63,42 @@ int mpb_world_destroy(mpb_world *world);
  * q: dev [n, dim] f64; out: dev [n] u8. */
 int mpb_points_check(const mpb_world *world, const double *q, int64_t n, uint8_t *out, void *stream);
 
+/* ---- a serial arm approximated by spheres, among boxes in the 3-D workspace ----------------
+ * BASELINE.json configs[3]'s collision model.  The reference has no robot model -- its collision_fn is a
+ * callable the caller supplies (README.md:52-59) -- so this entry point has no counterpart there; it builds a
+ * collision_fn in the reference's terms: closed bounds on the configuration (tkinter/samplers.py:92) and, for
+ * every sphere k and box b, ||clamp(c_k, lo_b, hi_b) - c_k|| <= r_k + buffer (tkinter/viewer.py:80-82: norm =
+ * sqrt of a sequentially fused dot).  The model -- chain, spheres and the fixed-polynomial sincos of the forward
+ * kinematics -- is stated in oracle/arm_oracle.c, which the kernels follow operation for operation.
+ * Configuration q in R^n_joints; angle_i = fl(fl(q_i * theta_span[i]) + theta_lo[i]); frame i = frame i-1 turned
+ * about its local axis[i] (1 = y, 2 = z); link i = a[i] along the turned x + d[i] along the turned z; sphere j
+ * sits on frame sph_link[j] at sph_u[j] along x and sph_w[j] along z from the frame's origin.
+ * The returned handle is an mpb_world: mpb_points_check, mpb_edges_check, mpb_edges_check_pairs and
+ * mpb_edges_check_knn take it (configurations have n_joints coordinates); the entry points that are stated for
+ * configuration-space obstacles only (circular joints, the resident-tree planners) refuse it.
+ * box_lo/box_hi: HOST [n_box, 3] raw bounds; env_lo/env_hi: HOST [n_joints]. */
+#define MPB_ARM_MAX_JOINTS 8
+#define MPB_ARM_MAX_SPHERES 32
+typedef struct mpb_arm_model {
+    int n_joints;
+    int axis[MPB_ARM_MAX_JOINTS];
+    double theta_lo[MPB_ARM_MAX_JOINTS];
+    double theta_span[MPB_ARM_MAX_JOINTS];
+    double a[MPB_ARM_MAX_JOINTS];
+    double d[MPB_ARM_MAX_JOINTS];
+    double base[3];
+    int n_sph;
+    int sph_link[MPB_ARM_MAX_SPHERES];
+    double sph_u[MPB_ARM_MAX_SPHERES];
+    double sph_w[MPB_ARM_MAX_SPHERES];
+    double sph_r[MPB_ARM_MAX_SPHERES];
+} mpb_arm_model;
+int mpb_arm_world_create(const mpb_arm_model *model, const double *box_lo, const double *box_hi, int n_box,
+                         const double *env_lo, const double *env_hi, double buffer, mpb_world **out);
+/* Forward kinematics alone: out_centres dev [n, n_sph, 3] f64 = the sphere centres of q dev [n, n_joints]
+ * (what the collision test of an arm world compares with the boxes; for tests and visualisation). */
+int mpb_arm_fk(const mpb_world *world, const double *q, int64_t n, double *out_centres, void *stream);
+
 /* ---- extend_fn + collision_fn fused over a batch of directed edges ----------------------
  * For each edge q1 -> q2: discretise with tkinter/samplers.py:113-127 get_extend_fn
  * (circular = {}, norm = inf): n = int(max_d |(q2-q1)/step|) + 1 waypoints from the serial

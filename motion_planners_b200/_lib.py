@@ -28,6 +28,9 @@ SIGNATURES = {
     "mpb_world_create": (c_int, [c_hostf64, c_hostf64, c_int, c_hostf64, c_hostf64, c_int, c_int, c_hostf64,
                                  c_hostf64, c_dbl, ctypes.POINTER(c_vp)]),
     "mpb_world_destroy": (c_int, [c_vp]),
+    "mpb_arm_world_create": (c_int, [c_vp, c_hostf64, c_hostf64, c_int, c_hostf64, c_hostf64, c_dbl,
+                                     ctypes.POINTER(c_vp)]),
+    "mpb_arm_fk": (c_int, [c_vp, c_vp, c_i64, c_vp, c_vp]),
     "mpb_points_check": (c_int, [c_vp, c_vp, c_i64, c_vp, c_vp]),
     "mpb_edges_check": (c_int, [c_vp, c_vp, c_i64, c_vp, c_vp, c_i64, c_dbl, c_int, c_int, c_vp, c_vp, c_vp]),
     "mpb_edges_check_knn": (c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, c_int, c_i64, c_dbl, c_int, c_int, c_vp, c_vp,

@@ -1,0 +1,346 @@
+// collision_fn and fused extend_fn + collision_fn for a sphere-approximated serial arm among workspace boxes
+// (BASELINE.json configs[3]).
+//
+// The reference has no robot model; its collision_fn is a caller-supplied callable (README.md:52-59).  What is
+// reproduced from it: the closed environment test on the configuration (tkinter/samplers.py:92), the obstacle
+// test `norm(...) <= radius + buffer` (tkinter/viewer.py:80-82, norm = sqrt of a sequentially fused dot) and the
+// waypoint recurrence of tkinter/samplers.py:113-127 in joint space.  The model itself (chain, spheres, the
+// fixed-polynomial sincos) is defined in oracle/arm_oracle.c, which this file follows operation for operation.
+//
+// One thread per directed edge (persistent grid); the workspace boxes, and a 16^3 grid that lists for every cell
+// the boxes a sphere centred there could touch, are staged in shared memory once per block.  The chain is walked
+// joint by joint and the spheres of a joint are tested as soon as its frame is known, so a colliding waypoint
+// usually costs a fraction of the forward kinematics.
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "arm.cuh"
+
+struct mpb_arm_host {
+    ArmDev dev;
+    void *blob;
+};
+
+namespace {
+
+template <int NJ>
+__global__ void __launch_bounds__(256) arm_points_kernel(ArmDev A, const double *__restrict__ q, int64_t n,
+                                                         uint8_t *__restrict__ out)
+{
+    extern __shared__ __align__(16) unsigned char sm[];
+    const ArmSmem S = arm_stage(A, sm);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        double p[NJ];
+#pragma unroll
+        for (int d = 0; d < NJ; ++d) p[d] = q[i * NJ + d];
+        out[i] = arm_collides<NJ>(A, S, p, nullptr) ? 1 : 0;
+    }
+}
+
+template <int NJ>
+__global__ void __launch_bounds__(256) arm_fk_kernel(ArmDev A, const double *__restrict__ q, int64_t n,
+                                                     double *__restrict__ out)
+{
+    const ArmSmem S = {nullptr, nullptr, nullptr};
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        double p[NJ];
+#pragma unroll
+        for (int d = 0; d < NJ; ++d) p[d] = q[i * NJ + d];
+        arm_collides<NJ>(A, S, p, out + i * 3 * A.n_sph);
+    }
+}
+
+// Edges: explicit endpoints (Bp != NULL), index pairs (src/dst), or the rows of a neighbour matrix (kk > 0: edge e
+// runs from sample row_offset + e / kk to sample dst[e]).  Modes and skip_last as mpb_edges_check.
+template <int NJ>
+__global__ void __launch_bounds__(256)
+    arm_edges_kernel(ArmDev A, const double *__restrict__ Ap, const double *__restrict__ Bp,
+                     const int64_t *__restrict__ src, const int64_t *__restrict__ dst, int kk, int64_t row_offset,
+                     int64_t E, double step, int mode, int skip_last, int32_t *__restrict__ out_hit,
+                     int32_t *__restrict__ out_n)
+{
+    extern __shared__ __align__(16) unsigned char sm[];
+    const ArmSmem S = arm_stage(A, sm);
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < E; e += (int64_t)gridDim.x * blockDim.x) {
+        int64_t ia = e, ib = e;
+        const double *pb = Bp;
+        if (!Bp) {
+            ia = kk > 0 ? row_offset + e / kk : src[e];
+            ib = dst[e];
+            pb = Ap;
+            if (ia < 0 || ib < 0) {
+                out_hit[e] = -1;
+                if (out_n) out_n[e] = 0;
+                continue;
+            }
+        }
+        double a[NJ], b[NJ];
+#pragma unroll
+        for (int d = 0; d < NJ; ++d) {
+            a[d] = Ap[ia * NJ + d];
+            b[d] = pb[ib * NJ + d];
+        }
+        const int n = waypoint_count<NJ>(a, b, step);
+        const int lim = n - (skip_last ? 1 : 0);
+        int best = -1;
+        for (int i = 0; i < lim; ++i) {
+            waypoint_step<NJ>(a, b, n, i);          // a is the running waypoint
+            if (arm_collides<NJ>(A, S, a, nullptr)) {
+                best = i;
+                if (mode != MPB_EDGE_LAST) break;
+            }
+        }
+        out_hit[e] = best;
+        if (out_n) out_n[e] = n;
+    }
+}
+
+int sm_count_arm()
+{
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    return sms;
+}
+
+#define ARM_DISPATCH(nj, CALL)   \
+    switch (nj) {                \
+        case 1: return CALL(1);  \
+        case 2: return CALL(2);  \
+        case 3: return CALL(3);  \
+        case 4: return CALL(4);  \
+        case 5: return CALL(5);  \
+        case 6: return CALL(6);  \
+        case 7: return CALL(7);  \
+        case 8: return CALL(8);  \
+        default: break;          \
+    }
+
+template <int NJ>
+int launch_arm_points(const ArmDev &A, const double *q, int64_t n, uint8_t *out, cudaStream_t st)
+{
+    const size_t smem = arm_smem_bytes(A);
+    MPB_CUDA_CHECK(cudaFuncSetAttribute(arm_points_kernel<NJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int64_t blocks = (n + 255) / 256;
+    const int64_t cap = (int64_t)sm_count_arm() * 8;
+    if (blocks > cap) blocks = cap;
+    arm_points_kernel<NJ><<<(unsigned)blocks, 256, smem, st>>>(A, q, n, out);
+    MPB_LAUNCH_CHECK();
+    return MPB_OK;
+}
+
+template <int NJ>
+int launch_arm_fk(const ArmDev &A, const double *q, int64_t n, double *out, cudaStream_t st)
+{
+    int64_t blocks = (n + 255) / 256;
+    const int64_t cap = (int64_t)sm_count_arm() * 8;
+    if (blocks > cap) blocks = cap;
+    arm_fk_kernel<NJ><<<(unsigned)blocks, 256, 0, st>>>(A, q, n, out);
+    MPB_LAUNCH_CHECK();
+    return MPB_OK;
+}
+
+template <int NJ>
+int launch_arm_edges(const ArmDev &A, const double *Ap, const double *Bp, const int64_t *src, const int64_t *dst, int kk,
+                     int64_t row_offset, int64_t E, double step, int mode, int skip_last, int32_t *out_hit,
+                     int32_t *out_n, cudaStream_t st)
+{
+    const size_t smem = arm_smem_bytes(A);
+    MPB_CUDA_CHECK(cudaFuncSetAttribute(arm_edges_kernel<NJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 1;
+    MPB_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, arm_edges_kernel<NJ>, 256, smem));
+    if (per_sm < 1) per_sm = 1;
+    int64_t blocks = (E + 255) / 256;
+    const int64_t cap = (int64_t)sm_count_arm() * per_sm;
+    if (blocks > cap) blocks = cap;
+    arm_edges_kernel<NJ><<<(unsigned)blocks, 256, smem, st>>>(A, Ap, Bp, src, dst, kk, row_offset, E, step, mode,
+                                                             skip_last, out_hit, out_n);
+    MPB_LAUNCH_CHECK();
+    return MPB_OK;
+}
+
+}   // namespace
+
+// ---- entry points used by world.cu's dispatch -------------------------------------------------------------
+int mpb_arm_points_check_impl(const mpb_arm_host *arm, const double *q, int64_t n, uint8_t *out, cudaStream_t st)
+{
+#define CALL(NJ) launch_arm_points<NJ>(arm->dev, q, n, out, st)
+    ARM_DISPATCH(arm->dev.n_joints, CALL)
+#undef CALL
+    return MPB_EINVAL;
+}
+
+int mpb_arm_edges_check_impl(const mpb_arm_host *arm, const double *Ap, const double *Bp, const int64_t *src,
+                             const int64_t *dst, int kk, int64_t row_offset, int64_t E, double step, int mode,
+                             int skip_last, int32_t *out_hit, int32_t *out_n, cudaStream_t st)
+{
+#define CALL(NJ) \
+    launch_arm_edges<NJ>(arm->dev, Ap, Bp, src, dst, kk, row_offset, E, step, mode, skip_last, out_hit, out_n, st)
+    ARM_DISPATCH(arm->dev.n_joints, CALL)
+#undef CALL
+    return MPB_EINVAL;
+}
+
+void mpb_arm_destroy_impl(mpb_arm_host *arm)
+{
+    if (!arm) return;
+    cudaFree(arm->blob);
+    delete arm;
+}
+
+MPB_API int mpb_arm_fk(const mpb_world *world, const double *q, int64_t n, double *out_centres, void *stream)
+{
+    MPB_REQUIRE(world && world->arm, "mpb_arm_fk: not an arm world");
+    MPB_REQUIRE(n >= 0, "mpb_arm_fk: negative count");
+    if (n == 0) return MPB_OK;
+    MPB_REQUIRE(q && out_centres, "mpb_arm_fk: NULL buffer");
+    const mpb_arm_host *arm = world->arm;
+#define CALL(NJ) launch_arm_fk<NJ>(arm->dev, q, n, out_centres, (cudaStream_t)stream)
+    ARM_DISPATCH(arm->dev.n_joints, CALL)
+#undef CALL
+    return MPB_EINVAL;
+}
+
+MPB_API int mpb_arm_world_create(const mpb_arm_model *m, const double *box_lo, const double *box_hi, int n_box,
+                                 const double *env_lo, const double *env_hi, double buffer, mpb_world **out)
+{
+    MPB_REQUIRE(out != nullptr, "mpb_arm_world_create: out is NULL");
+    *out = nullptr;
+    MPB_REQUIRE(m != nullptr && env_lo && env_hi, "mpb_arm_world_create: NULL model or bounds");
+    MPB_REQUIRE(m->n_joints >= 1 && m->n_joints <= kArmMaxJoints, "mpb_arm_world_create: %d joints outside [1, %d]",
+                m->n_joints, kArmMaxJoints);
+    MPB_REQUIRE(m->n_sph >= 1 && m->n_sph <= kArmMaxSpheres, "mpb_arm_world_create: %d spheres outside [1, %d]",
+                m->n_sph, kArmMaxSpheres);
+    MPB_REQUIRE(n_box >= 0 && n_box <= 65535, "mpb_arm_world_create: box count outside [0, 65535]");
+    MPB_REQUIRE(n_box == 0 || (box_lo && box_hi), "mpb_arm_world_create: box arrays are NULL");
+    for (int i = 0; i < m->n_joints; ++i)
+        MPB_REQUIRE(m->axis[i] == 1 || m->axis[i] == 2, "mpb_arm_world_create: joint %d: axis must be 1 (y) or 2 (z)", i);
+    for (int j = 0; j < m->n_sph; ++j)
+        MPB_REQUIRE(m->sph_link[j] >= 0 && m->sph_link[j] < m->n_joints && m->sph_r[j] >= 0.,
+                    "mpb_arm_world_create: sphere %d: bad joint or radius", j);
+
+    mpb_arm_host *arm = new mpb_arm_host();
+    ArmDev &A = arm->dev;
+    memset(&A, 0, sizeof(A));
+    A.n_joints = m->n_joints;
+    A.n_sph = m->n_sph;
+    A.n_box = n_box;
+    for (int i = 0; i < m->n_joints; ++i) {
+        A.axis[i] = m->axis[i];
+        A.theta_lo[i] = m->theta_lo[i];
+        A.theta_span[i] = m->theta_span[i];
+        A.a[i] = m->a[i];
+        A.d[i] = m->d[i];
+        A.env_lo[i] = env_lo[i];
+        A.env_hi[i] = env_hi[i];
+    }
+    for (int k = 0; k < 3; ++k) A.base[k] = m->base[k];
+    // spheres grouped by the joint that carries them (the verdict is an `any`, so the order is free)
+    int pos = 0;
+    double rmax = 0.;
+    for (int i = 0; i < m->n_joints; ++i) {
+        A.sph_first[i] = pos;
+        for (int j = 0; j < m->n_sph; ++j) {
+            if (m->sph_link[j] != i) continue;
+            A.sph_orig[pos] = j;
+            A.sph_u[pos] = m->sph_u[j];
+            A.sph_w[pos] = m->sph_w[j];
+            const double rb = m->sph_r[j] + buffer;          // viewer.py:82 radius + buffer
+            A.sph_rb[pos] = rb;
+            A.sph_lo2[pos] = rb * rb * (1.0 - 1e-12);
+            A.sph_hi2[pos] = rb * rb * (1.0 + 1e-12);
+            rmax = std::max(rmax, rb);
+            ++pos;
+        }
+    }
+    for (int i = m->n_joints; i <= kArmMaxJoints; ++i) A.sph_first[i] = pos;
+
+    // the grid: it spans every box inflated by the largest radius; cell lists hold every box whose inflated
+    // bounds (plus a margin far above any rounding of the cell index) overlap the cell
+    const int G = kArmGrid;
+    double glo[3] = {0., 0., 0.}, ghi[3] = {1., 1., 1.};
+    const double infl = rmax * (1.0 + 1e-6) + 1e-9;
+    for (int k = 0; k < 3; ++k) {
+        double lo = INFINITY, hi = -INFINITY;
+        for (int b = 0; b < n_box; ++b) {
+            lo = std::min(lo, box_lo[3 * b + k] - infl);
+            hi = std::max(hi, box_hi[3 * b + k] + infl);
+        }
+        if (!(lo < hi)) {
+            lo = 0.;
+            hi = 1.;
+        }
+        const double pad = 1e-6 * (hi - lo) + 1e-9;
+        glo[k] = lo - pad;
+        ghi[k] = hi + pad;
+        A.grid_lo[k] = glo[k];
+        A.grid_inv[k] = (double)G / (ghi[k] - glo[k]);
+    }
+    std::vector<std::vector<unsigned short>> cells((size_t)G * G * G);
+    for (int b = 0; b < n_box; ++b) {
+        int c0[3], c1[3];
+        for (int k = 0; k < 3; ++k) {
+            const double h = (ghi[k] - glo[k]) / G;
+            const double margin = infl + 1e-6 * h;
+            c0[k] = std::max(0, std::min(G - 1, (int)floor((box_lo[3 * b + k] - margin - glo[k]) / h)));
+            c1[k] = std::max(0, std::min(G - 1, (int)floor((box_hi[3 * b + k] + margin - glo[k]) / h)));
+        }
+        for (int x = c0[0]; x <= c1[0]; ++x)
+            for (int y = c0[1]; y <= c1[1]; ++y)
+                for (int z = c0[2]; z <= c1[2]; ++z) cells[((size_t)x * G + y) * G + z].push_back((unsigned short)b);
+    }
+    std::vector<int> cell_start((size_t)G * G * G + 1);
+    std::vector<unsigned short> items;
+    for (size_t c = 0; c < cells.size(); ++c) {
+        cell_start[c] = (int)items.size();
+        items.insert(items.end(), cells[c].begin(), cells[c].end());
+    }
+    cell_start[cells.size()] = (int)items.size();
+    A.n_items = (int)items.size();
+    if (arm_smem_bytes(A) > 200 * 1024) {
+        delete arm;
+        mpb_set_error("mpb_arm_world_create: %d boxes with %d grid entries exceed the shared-memory budget", n_box,
+                      A.n_items);
+        return MPB_EINVAL;
+    }
+    std::vector<double> boxes((size_t)n_box * 6);
+    for (int b = 0; b < n_box; ++b)
+        for (int k = 0; k < 3; ++k) {
+            boxes[(size_t)b * 6 + 2 * k] = box_lo[3 * b + k];
+            boxes[(size_t)b * 6 + 2 * k + 1] = box_hi[3 * b + k];
+        }
+    const size_t box_bytes = (boxes.size() * sizeof(double) + 255) & ~(size_t)255;
+    const size_t cs_bytes = (cell_start.size() * sizeof(int) + 255) & ~(size_t)255;
+    const size_t it_bytes = (items.size() * sizeof(unsigned short) + 255) & ~(size_t)255;
+    cudaError_t e = cudaMalloc(&arm->blob, box_bytes + cs_bytes + it_bytes + 256);
+    if (e != cudaSuccess) {
+        delete arm;
+        mpb_set_error("mpb_arm_world_create: cudaMalloc failed: %s", cudaGetErrorString(e));
+        return MPB_ENOMEM;
+    }
+    char *base = reinterpret_cast<char *>(arm->blob);
+    e = cudaMemcpy(base, boxes.data(), boxes.size() * sizeof(double), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(base + box_bytes, cell_start.data(), cell_start.size() * sizeof(int), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && !items.empty())
+        e = cudaMemcpy(base + box_bytes + cs_bytes, items.data(), items.size() * sizeof(unsigned short), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        cudaFree(arm->blob);
+        delete arm;
+        mpb_set_error("mpb_arm_world_create: cudaMemcpy failed: %s", cudaGetErrorString(e));
+        return MPB_ECUDA;
+    }
+    A.boxes = reinterpret_cast<const double *>(base);
+    A.cell_start = reinterpret_cast<const int *>(base + box_bytes);
+    A.cell_items = reinterpret_cast<const unsigned short *>(base + box_bytes + cs_bytes);
+
+    mpb_world *w = new mpb_world();
+    memset(&w->dev, 0, sizeof(w->dev));
+    w->dev.dim = m->n_joints;
+    w->blob = nullptr;
+    w->arm = arm;
+    cudaGetDevice(&w->device);
+    *out = w;
+    return MPB_OK;
+}

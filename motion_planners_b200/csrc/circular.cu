@@ -334,6 +334,7 @@ MPB_API int mpb_edges_check_circular(const mpb_world *world, const double *a, co
 {
     const char *who = "mpb_edges_check_circular";
     MPB_REQUIRE(world != nullptr, "%s: world is NULL", who);
+    MPB_REQUIRE_CSPACE(world, who);
     MPB_REQUIRE(n_edges >= 0, "%s: negative edge count", who);
     MPB_REQUIRE(mode == MPB_EDGE_ANY || mode == MPB_EDGE_FIRST || mode == MPB_EDGE_LAST, "%s: bad mode %d", who, mode);
     MPB_REQUIRE(step > 0., "%s: step must be positive", who);

@@ -51,11 +51,25 @@ struct WorldDev {
     const double *env_hi;   // [dim]
 };
 
+struct mpb_arm_host;   // arm.cu: a serial arm approximated by spheres among workspace boxes
+
 struct mpb_world {
     WorldDev dev;
     void *blob;    // single device allocation backing every array above
     int device;
+    mpb_arm_host *arm;   // non-NULL: the collision model is the arm's (dev then only carries dim = joints)
 };
+
+// arm.cu
+int mpb_arm_points_check_impl(const mpb_arm_host *arm, const double *q, int64_t n, uint8_t *out, cudaStream_t st);
+int mpb_arm_edges_check_impl(const mpb_arm_host *arm, const double *Ap, const double *Bp, const int64_t *src,
+                             const int64_t *dst, int kk, int64_t row_offset, int64_t E, double step, int mode,
+                             int skip_last, int32_t *out_hit, int32_t *out_n, cudaStream_t st);
+void mpb_arm_destroy_impl(mpb_arm_host *arm);
+
+// entry points that only know configuration-space boxes and spheres
+#define MPB_REQUIRE_CSPACE(world, who) \
+    MPB_REQUIRE((world) == nullptr || (world)->arm == nullptr, "%s: not available for an arm world", who)
 
 // ---- exactly rounded fp64 steps (never contracted into FMA) -------------------------------
 __device__ __forceinline__ double d_sub(double a, double b) { return __dsub_rn(a, b); }

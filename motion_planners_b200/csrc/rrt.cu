@@ -322,6 +322,7 @@ MPB_API int mpb_rrt_connect_batch(const mpb_world *world, const double *starts, 
                                   int32_t *out_overflow, void *stream)
 {
     MPB_REQUIRE(world != nullptr, "mpb_rrt_connect_batch: world is NULL");
+    MPB_REQUIRE_CSPACE(world, "mpb_rrt_connect_batch");
     MPB_REQUIRE(metric >= 0 && metric <= 2, "mpb_rrt_connect_batch: bad metric %d", metric);
     MPB_REQUIRE(n_queries >= 0 && n_queries < 2147483647LL, "mpb_rrt_connect_batch: bad query count");
     MPB_REQUIRE(iters >= 0 && cap >= 1, "mpb_rrt_connect_batch: bad iteration count or capacity");

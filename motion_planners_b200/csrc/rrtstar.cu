@@ -304,6 +304,7 @@ MPB_API int mpb_rrt_star_step(const mpb_world *world, double *table, int64_t n_n
 {
     const char *who = "mpb_rrt_star_step";
     MPB_REQUIRE(world != nullptr, "%s: world is NULL", who);
+    MPB_REQUIRE_CSPACE(world, who);
     MPB_REQUIRE(table && sample && workspace && out_record, "%s: NULL buffer", who);
     MPB_REQUIRE(n_nodes >= 1 && n_nodes < capacity && capacity < 2147483647LL,
                 "%s: need 1 <= n_nodes < capacity (the new node takes slot n_nodes)", who);

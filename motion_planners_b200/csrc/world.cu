@@ -88,6 +88,7 @@ MPB_API int mpb_world_create(const double *box_lo, const double *box_hi, int n_b
 MPB_API int mpb_world_destroy(mpb_world *w)
 {
     if (!w) return MPB_OK;
+    mpb_arm_destroy_impl(w->arm);
     cudaFree(w->blob);
     delete w;
     return MPB_OK;
@@ -135,6 +136,7 @@ MPB_API int mpb_points_check(const mpb_world *world, const double *q, int64_t n,
     MPB_REQUIRE(n >= 0, "mpb_points_check: negative count");
     if (n == 0) return MPB_OK;
     MPB_REQUIRE(q && out, "mpb_points_check: NULL buffer");
+    if (world->arm) return mpb_arm_points_check_impl(world->arm, q, n, out, (cudaStream_t)stream);
     MPB_REQUIRE(world_smem_bytes(world->dev) + 16 <= kMaxWorldSmem,
                 "mpb_points_check: obstacle set (%zu bytes) exceeds the %zu-byte shared-memory budget",
                 world_smem_bytes(world->dev), kMaxWorldSmem);
@@ -318,6 +320,9 @@ static int edges_common(const char *who, const mpb_world *world, const double *A
     if (E == 0) return MPB_OK;
     MPB_REQUIRE(A && out_hit, "%s: NULL buffer", who);
     MPB_REQUIRE((E + 127) / 128 <= 0x7fffffffLL, "%s: too many edges", who);
+    if (world->arm)
+        return mpb_arm_edges_check_impl(world->arm, A, B, src, dst, 0, 0, E, step, mode, skip_last, out_hit, out_n,
+                                        (cudaStream_t)stream);
     MPB_REQUIRE(world_smem_bytes(world->dev) + 16 <= kMaxWorldSmem,
                 "%s: obstacle set (%zu bytes) exceeds the %zu-byte shared-memory budget", who,
                 world_smem_bytes(world->dev), kMaxWorldSmem);
@@ -501,6 +506,10 @@ MPB_API int mpb_edges_check_knn(const mpb_world *world, const double *samples, i
     MPB_REQUIRE(step > 0., "mpb_edges_check_knn: step must be positive");
     if (n_rows == 0) return MPB_OK;
     MPB_REQUIRE(samples && nbr && out_hit, "mpb_edges_check_knn: NULL buffer");
+    if (world->arm)
+        return mpb_arm_edges_check_impl(world->arm, samples, nullptr, nullptr, nbr, row_len, row_offset,
+                                        n_rows * (int64_t)row_len, step, mode, skip_last, out_hit, out_n,
+                                        (cudaStream_t)stream);
     MPB_REQUIRE(world_smem_bytes(world->dev) + 16 <= kMaxWorldSmem,
                 "mpb_edges_check_knn: obstacle set (%zu bytes) exceeds the %zu-byte shared-memory budget",
                 world_smem_bytes(world->dev), kMaxWorldSmem);

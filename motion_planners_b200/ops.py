@@ -12,6 +12,7 @@ import numpy as np
 import torch
 
 from . import _lib
+from .arm import ArmWorld
 from .geometry import STEP_SIZE, World
 
 EDGE_ANY, EDGE_FIRST, EDGE_LAST = 0, 1, 2
@@ -69,12 +70,36 @@ def _host_circular(circular, dim):
     return (lo, hi), hp(lo), hp(hi)
 
 
+class _ArmModelC(ctypes.Structure):
+    """mpb_arm_model of include/mpb200.h"""
+    _fields_ = [("n_joints", ctypes.c_int), ("axis", ctypes.c_int * 8), ("theta_lo", ctypes.c_double * 8),
+                ("theta_span", ctypes.c_double * 8), ("a", ctypes.c_double * 8), ("d", ctypes.c_double * 8),
+                ("base", ctypes.c_double * 3), ("n_sph", ctypes.c_int), ("sph_link", ctypes.c_int * 32),
+                ("sph_u", ctypes.c_double * 32), ("sph_w", ctypes.c_double * 32), ("sph_r", ctypes.c_double * 32)]
+
+
+def _arm_model_struct(model):
+    m = _ArmModelC()
+    m.n_joints = model.n_joints
+    for i in range(model.n_joints):
+        m.axis[i] = model.axis[i]
+        m.theta_lo[i], m.theta_span[i] = float(model.theta_lo[i]), float(model.theta_span[i])
+        m.a[i], m.d[i] = float(model.a[i]), float(model.d[i])
+    for k in range(3):
+        m.base[k] = float(model.base[k])
+    m.n_sph = model.n_sph
+    for j in range(model.n_sph):
+        m.sph_link[j] = model.sph_link[j]
+        m.sph_u[j], m.sph_w[j], m.sph_r[j] = float(model.sph_u[j]), float(model.sph_w[j]), float(model.sph_r[j])
+    return m
+
+
 class ObstacleSet(object):
     """Device-resident obstacle set (mpb_world) for one World on the current CUDA device."""
 
     def __init__(self, world):
-        if not isinstance(world, World):
-            raise TypeError("world must be a geometry.World")
+        if not isinstance(world, (World, ArmWorld)):
+            raise TypeError("world must be a geometry.World or an arm.ArmWorld")
         if not torch.cuda.is_available():
             raise _lib.MpbError("no CUDA device: the collision kernels have no CPU fallback")
         self.world = world
@@ -82,6 +107,14 @@ class ObstacleSet(object):
         self.device = torch.cuda.current_device()
         hp = lambda a: a.ctypes.data_as(ctypes.POINTER(ctypes.c_double))
         handle = ctypes.c_void_p()
+        if isinstance(world, ArmWorld):
+            # the sphere-approximated arm among workspace boxes (mpb_arm_world_create)
+            model = _arm_model_struct(world.model)
+            rc = _lib.lib().mpb_arm_world_create(ctypes.byref(model), hp(world.box_lo), hp(world.box_hi), world.n_box,
+                                                 hp(world.env_lo), hp(world.env_hi), world.buffer, ctypes.byref(handle))
+            _lib.check(rc, "mpb_arm_world_create")
+            self._h = handle
+            return
         rc = _lib.lib().mpb_world_create(hp(world.box_lo), hp(world.box_hi), world.n_box, hp(world.sph_c),
                                          hp(world.sph_r), world.n_sph, world.dim, hp(world.env_lo),
                                          hp(world.env_hi), world.buffer, ctypes.byref(handle))
@@ -96,6 +129,16 @@ class ObstacleSet(object):
             except Exception:
                 pass
             self._h = None
+
+    # -- sphere centres of an arm world's configurations: [n, n_sph, 3]
+    def arm_centres(self, q):
+        if not isinstance(self.world, ArmWorld):
+            raise TypeError("not an arm world")
+        q = _f64(q, "q", self.dim)
+        out = torch.empty((q.shape[0], self.world.n_sph, 3), dtype=torch.float64, device=q.device)
+        rc = _lib.lib().mpb_arm_fk(self._h, _ptr(q), q.shape[0], _ptr(out), _stream())
+        _lib.check(rc, "mpb_arm_fk")
+        return out
 
     # -- collision_fn over a batch (tkinter/samplers.py:88-98)
     def points_check(self, q):

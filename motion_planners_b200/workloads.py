@@ -7,6 +7,7 @@ stream the reference's `sample_fn` consumes for a unit-box environment
 """
 import numpy as np
 
+from .arm import ArmWorld, seven_dof_arm
 from .geometry import World, create_box, create_cylinder
 
 
@@ -68,6 +69,24 @@ def c4lite_world(seed=0):
     extents U(0.1, 0.5).  (The sphere-approximated arm of config 4 has no counterpart in
     the reference; see DESIGN.md.)"""
     return boxes_world(7, 256, 0.1, 0.5, seed)
+
+
+def c4_world(seed=0, n_box=256, n_sph=16):
+    """Config 4 as written: a 7-DoF arm approximated by 16 spheres among 256 boxes in the 3-D workspace.
+    Boxes: centre ~ U([-0.9, 0.9]^2 x [-0.1, 1.1]), per-axis extent ~ U(0.03, 0.12), drawn box by box from
+    RandomState(seed); a box is redrawn while it stands in the column around the arm's fixed first links (every
+    configuration would collide with it).  About half of the uniform configurations are collision-free."""
+    rs = np.random.RandomState(seed)
+    lo, hi = [], []
+    while len(lo) < n_box:
+        c = rs.uniform([-0.9, -0.9, -0.1], [0.9, 0.9, 1.1])
+        e = rs.uniform(0.03, 0.12, size=3)
+        if np.hypot(c[0], c[1]) < 0.25 + e[:2].max() / 2 and c[2] - e[2] / 2 < 0.45:
+            continue
+        box = create_box(c, e)
+        lo.append(box.lower)
+        hi.append(box.upper)
+    return ArmWorld(seven_dof_arm(n_sph), np.array(lo), np.array(hi))
 
 
 def c5_world(seed=0):

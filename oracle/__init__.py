@@ -28,7 +28,7 @@ def lib():
     global _lib
     if _lib is None:
         path = _build.OUT
-        if not os.path.exists(path) or os.path.getmtime(path) < os.path.getmtime(_build.SRC):
+        if not os.path.exists(path) or any(os.path.getmtime(path) < os.path.getmtime(f) for f in _build.SRCS):
             path = _build.build()
         _lib = ctypes.CDLL(path)
         _lib.orc_sqdist_scipy.restype = ctypes.c_double
@@ -271,3 +271,78 @@ def use_all_cores():
     OMP_NUM_THREADS=1 for their workers)."""
     lib().orc_set_threads(int(os.cpu_count() or 1))
     return num_threads()
+
+
+# ------------------------------------------------------------------ configs[3]: the sphere-approximated arm
+class _ArmModelC(ctypes.Structure):
+    _fields_ = [("n_joints", ctypes.c_int), ("axis", ctypes.c_int * 8), ("theta_lo", ctypes.c_double * 8),
+                ("theta_span", ctypes.c_double * 8), ("a", ctypes.c_double * 8), ("d", ctypes.c_double * 8),
+                ("base", ctypes.c_double * 3), ("n_sph", ctypes.c_int), ("sph_link", ctypes.c_int * 32),
+                ("sph_u", ctypes.c_double * 32), ("sph_w", ctypes.c_double * 32), ("sph_r", ctypes.c_double * 32)]
+
+
+def _arm_model_c(model):
+    """model: any object with the fields of motion_planners_b200.arm.ArmModel (plain data)."""
+    m = _ArmModelC()
+    m.n_joints = int(model.n_joints)
+    for i in range(m.n_joints):
+        m.axis[i] = int(model.axis[i])
+        m.theta_lo[i] = float(model.theta_lo[i])
+        m.theta_span[i] = float(model.theta_span[i])
+        m.a[i] = float(model.a[i])
+        m.d[i] = float(model.d[i])
+    for k in range(3):
+        m.base[k] = float(model.base[k])
+    m.n_sph = int(model.n_sph)
+    for j in range(m.n_sph):
+        m.sph_link[j] = int(model.sph_link[j])
+        m.sph_u[j] = float(model.sph_u[j])
+        m.sph_w[j] = float(model.sph_w[j])
+        m.sph_r[j] = float(model.sph_r[j])
+    return m
+
+
+class ArmWorld:
+    """The collision model of configs[3] as oracle/arm_oracle.c defines it: a serial arm approximated by
+    spheres against workspace boxes.  `world`: anything with .model, .box_lo/.box_hi [n_box, 3], .env_lo/.env_hi
+    [n_joints], .buffer (e.g. motion_planners_b200.arm.ArmWorld; only its plain data is read)."""
+
+    def __init__(self, world):
+        self.m = _arm_model_c(world.model)
+        self.dim = int(world.model.n_joints)
+        self.n_sph = int(world.model.n_sph)
+        self.box_lo = _c(world.box_lo).reshape(-1, 3)
+        self.box_hi = _c(world.box_hi).reshape(-1, 3)
+        self.env_lo = _c(world.env_lo).reshape(self.dim)
+        self.env_hi = _c(world.env_hi).reshape(self.dim)
+        self.buffer = float(world.buffer)
+
+    def _args(self):
+        return (ctypes.byref(self.m), ctypes.c_int(self.box_lo.shape[0]), _p(self.box_lo, _f64p), _p(self.box_hi, _f64p),
+                _p(self.env_lo, _f64p), _p(self.env_hi, _f64p), ctypes.c_double(self.buffer))
+
+    def centres(self, q):
+        q = _c(q).reshape(-1, self.dim)
+        out = np.empty((q.shape[0], self.n_sph, 3))
+        lib().orc_arm_centres(ctypes.byref(self.m), _p(q, _f64p), ctypes.c_int64(q.shape[0]), _p(out, _f64p))
+        return out
+
+    def points_check(self, q):
+        q = _c(q).reshape(-1, self.dim)
+        out = np.empty(q.shape[0], dtype=np.uint8)
+        lib().orc_arm_points_check(*self._args(), _p(q, _f64p), ctypes.c_int64(q.shape[0]), _p(out, _u8p))
+        return out.astype(bool)
+
+    def edges_check_indexed(self, samples, src, dst, step=1e-2, skip_last=False):
+        samples = _c(samples).reshape(-1, self.dim)
+        src = _c(src, np.int64)
+        dst = _c(dst, np.int64)
+        E = src.shape[0]
+        n = np.empty(E, np.int32)
+        first = np.empty(E, np.int32)
+        last = np.empty(E, np.int32)
+        rc = lib().orc_arm_edges_check(*self._args(), _p(samples, _f64p), _p(src, _i64p), _p(dst, _i64p),
+                                       ctypes.c_int64(E), ctypes.c_double(step), ctypes.c_int(int(skip_last)),
+                                       _p(n, _i32p), _p(first, _i32p), _p(last, _i32p))
+        assert rc == 0
+        return n, first, last

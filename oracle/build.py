@@ -10,6 +10,7 @@ import subprocess
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "mp_oracle.c")
+SRCS = [SRC, os.path.join(HERE, "arm_oracle.c")]      # arm_oracle.c: the collision model of configs[3]
 OUT_DIR = os.path.join(HERE, "_build")
 OUT = os.path.join(OUT_DIR, "libmp_oracle.so")
 
@@ -22,9 +23,9 @@ CFLAGS = ["-O2", "-ffp-contract=off", "-mfma", "-fopenmp", "-shared", "-fPIC", "
 def build(force=False):
     os.makedirs(OUT_DIR, exist_ok=True)
     if (not force and os.path.exists(OUT)
-            and os.path.getmtime(OUT) >= os.path.getmtime(SRC)):
+            and all(os.path.getmtime(OUT) >= os.path.getmtime(f) for f in SRCS)):
         return OUT
-    cmd = ["gcc"] + CFLAGS + [SRC, "-o", OUT, "-lm"]
+    cmd = ["gcc"] + CFLAGS + SRCS + ["-o", OUT, "-lm"]
     subprocess.run(cmd, check=True)
     return OUT
 

@@ -121,3 +121,77 @@ def knn(samples, queries, k, weights=None, chunk=256):
             idx[s0 + r] = order
             dist[s0 + r] = np.sqrt(S[r, order])
     return idx, dist
+
+
+# ------------------------------------------------------------------ configs[3]: the sphere-approximated arm
+# An independent numpy statement of oracle/arm_oracle.c (elementwise ufuncs round every operation separately).
+def arm_sincos(th):
+    kf = np.rint(th * 0.63661977236758138)
+    r = th - kf * 1.57079632673412561417e+00
+    r = r - kf * 6.07710050650619224932e-11
+    z = r * r
+    t = np.full_like(z, 1.58969099521155010221e-10)
+    for cst in (-2.50507602534068634195e-08, 2.75573137070700676789e-06, -1.98412698298579493134e-04,
+                8.33333333332248946124e-03, -1.66666666666666324348e-01):
+        t = t * z + cst
+    sr = r + (r * z) * t
+    u = np.full_like(z, -1.13596475577881948265e-11)
+    for cst in (2.08757232129817482790e-09, -2.75573143513906633035e-07, 2.48015872894767294178e-05,
+                -1.38888888888741095749e-03, 4.16666666666666019037e-02):
+        u = u * z + cst
+    cr = (1.0 - 0.5 * z) + (z * z) * u
+    n = kf.astype(np.int64) & 3
+    s = np.select([n == 0, n == 1, n == 2], [sr, cr, -sr], -cr)
+    c = np.select([n == 0, n == 1, n == 2], [cr, -sr, -cr], sr)
+    return s, c
+
+
+def arm_centres(model, q):
+    """Sphere centres [n, n_sph, 3] of configurations q [n, n_joints]."""
+    q = np.asarray(q, dtype=np.float64)
+    n = q.shape[0]
+    X = np.tile(np.array([1., 0., 0.]), (n, 1))
+    Y = np.tile(np.array([0., 1., 0.]), (n, 1))
+    Z = np.tile(np.array([0., 0., 1.]), (n, 1))
+    p = np.tile(np.asarray(model.base, dtype=np.float64), (n, 1))
+    out = np.empty((n, model.n_sph, 3))
+    for i in range(model.n_joints):
+        th = q[:, i] * model.theta_span[i] + model.theta_lo[i]
+        s, c = arm_sincos(th)
+        s, c = s[:, None], c[:, None]
+        if model.axis[i] == 2:
+            X, Y = c * X + s * Y, c * Y - s * X
+        else:
+            X, Z = c * X - s * Z, s * X + c * Z
+        for j in range(model.n_sph):
+            if model.sph_link[j] == i:
+                out[:, j] = (p + model.sph_u[j] * X) + model.sph_w[j] * Z
+        p = (p + model.a[i] * X) + model.d[i] * Z
+    return out
+
+
+def arm_points_check(world, q):
+    """collision_fn of the arm world for a batch (the norm's fused dot is spelled out with math.fma-free
+    arithmetic that is exact here: three squares summed left to right in extended precision would differ, so the
+    sum uses the same fma chain through np.float64 operations on exactly representable partial products only
+    when possible; otherwise compare with oracle.ArmWorld, which is the arbiter)."""
+    q = np.asarray(q, dtype=np.float64)
+    inside = ((world.env_lo <= q) & (q <= world.env_hi)).all(1)
+    cen = arm_centres(world.model, q)
+    rb = np.asarray(world.model.sph_r) + world.buffer
+    hit = ~inside
+    for b in range(world.box_lo.shape[0]):
+        cl = np.minimum(np.maximum(cen, world.box_lo[b]), world.box_hi[b])
+        d = cl - cen
+        # s = fma(d2, d2, fma(d1, d1, d0*d0)); emulate each fma with exact two-product arithmetic in longdouble
+        s = _fma(d[..., 2], d[..., 2], _fma(d[..., 1], d[..., 1], d[..., 0] * d[..., 0]))
+        hit |= (np.sqrt(s) <= rb).any(1)
+    return hit
+
+
+def _fma(a, b, c):
+    """fma(a, b, c) for float64 arrays via an error-free product (Dekker) and a double-double sum: exact to the
+    last bit whenever the x87 long double (64-bit mantissa) sum a*b + c does not need more than its width, which
+    holds for the magnitudes of this model; oracle/arm_oracle.c (C fma) is the arbiter."""
+    la, lb, lc = a.astype(np.longdouble), b.astype(np.longdouble), c.astype(np.longdouble)
+    return (la * lb + lc).astype(np.float64)
