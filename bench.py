@@ -5,10 +5,11 @@
     python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N --steps K --warmup W
     python bench.py --impl reference ...                                (CPU arm: the oracle port)
 
-Default workload: `c4lite` = configs[3], the samples-sharded + all-gathered PRM that BASELINE.json's
-"at 1/2/4/8 B200" metric and its target (1M samples, 7-DoF, k=10) are quoted on, with the reference's own
-box primitives (the sphere-approximated arm has no counterpart in the reference); it fits one GPU.
-`extra_c2` in the same line is configs[1] (100k x 6-DoF, 64 boxes).
+Default workload: `c4` = configs[3] as written, the samples-sharded + all-gathered PRM that BASELINE.json's
+"at 1/2/4/8 B200" metric and its target are quoted on: 1M samples, 7-DoF, k=10, a sphere-approximated arm
+(16 spheres) among 256 workspace boxes (the collision model is defined in oracle/arm_oracle.c: the reference has
+none); it fits one GPU.  `extra_c4lite` is the same roadmap with the reference's own primitives (256 boxes in
+configuration space), `extra_c2` is configs[1] (100k x 6-DoF, 64 boxes).
 
 A step = one pass of the hot path over one synthetic roadmap: [all-gather of the sample shards when
 N > 1] -> kNN (k+1 = 11) of every sample of this rank's shard against the global set -> collision_fn
@@ -31,8 +32,13 @@ if ROOT not in sys.path:
 
 import numpy as np  # noqa: E402
 
-NCU_DRAM_BYTES_PER_LAUNCH = {"c4lite": 978.515968e6 + 182.364672e6}          # knn_filter_kernel (FFMA2 scan)
-NCU_DRAM_BYTES_PER_LAUNCH_TC = {"c4lite": 5.530121e9 + 75.893248e6}        # knn_tc_kernel (tensor-core scan)
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the kernel, from the committed `ncu --set full`
+# captures under profiles/ (1 GPU, the workload's full size); None = not captured
+NCU = {
+    "knn_tc_kernel": {"traffic": None, "tensor_pipe_active_pct": None, "source": None},
+    "arm_edges_kernel": {"traffic": None, "fp64_pipe_active_pct": None, "source": None},
+    "edges_check_rows_kernel": {"traffic": None, "fp64_pipe_active_pct": None, "source": None},
+}
 
 METRIC = "PRM edges collision-checked/sec (kNN k=10 + vertex + edge checks per roadmap build step)"
 UNIT = "edges/s"
@@ -40,10 +46,18 @@ UNIT = "edges/s"
 WORKLOADS = {
     # name -> (world factory name, dim, n_samples, k, description)
     "c2": ("c2_world", 6, 100000, 10, "configs[1]: lazy-PRM roadmap, 100k samples, 6-DoF unit cube, 64 random boxes, k=10"),
-    "c4lite": ("c4lite_world", 7, 1000000, 10, "configs[3] (the sharded, all-gathered PRM the 1/2/4/8-GPU metric and the "
-               "north-star target are quoted on) with reference primitives: 1M samples, 7-DoF, 256 C-space boxes, k=10"),
+    "c4": ("c4_world", 7, 1000000, 10, "configs[3]: the sharded, all-gathered PRM the 1/2/4/8-GPU metric and the north-star "
+           "target are quoted on: 1M samples, 7-DoF arm approximated by 16 spheres, 256 workspace boxes, k=10"),
+    "c4lite": ("c4lite_world", 7, 1000000, 10, "configs[3]'s roadmap with the reference's own primitives: 1M samples, 7-DoF, "
+               "256 boxes in configuration space, k=10"),
     "c1": ("c1", 2, 2000, 10, "configs[0]: 2-D demo fixture, 2k samples, k=10"),
 }
+
+
+def collision_model(world):
+    if hasattr(world, "model"):
+        return "%d-joint arm, %d spheres vs %d workspace boxes" % (world.model.n_joints, world.n_sph, world.n_box)
+    return "configuration-space obstacles: %d boxes, %d spheres" % (world.n_box, world.n_sph)
 
 
 def make_workload(name):
@@ -118,7 +132,7 @@ def cpu_sample_rate(world, X, k, budget_s=12.0, first=8000):
     t0 = time.perf_counter()
     tree = KDTree(X)
     build_s = time.perf_counter() - t0
-    hi = min(first, n)
+    hi = min(first if not hasattr(world, "model") else first // 4, n)
     r = cpu_baseline.native_port_step(world, X, 0, hi, k, tree=tree)
     while r["seconds"] < budget_s / 4 and hi < n:
         hi = min(n, hi * 4)
@@ -139,7 +153,8 @@ def run_reference_arm(args, rank):
     world, X, k, desc = make_workload(args.workload)
     n = X.shape[0]
     tree = KDTree(X)
-    sample = min(n, args.ref_sample)
+    # the arm's collision_fn costs the CPU ~40x more per waypoint than a box test: fewer queries per step
+    sample = min(n, args.ref_sample or (10000 if hasattr(world, "model") else 100000))
     for _ in range(args.warmup):
         cpu_baseline.native_port_step(world, X, 0, min(sample, 2000), k, tree=tree)
     secs, edges, queries = 0.0, 0, 0
@@ -156,7 +171,7 @@ def run_reference_arm(args, rank):
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "knn_queries_per_s": queries / secs,
         "config": {"workload": args.workload, "description": desc, "n_samples": n, "dim": X.shape[1], "k": k,
-                   "n_box": world.n_box, "n_sph": world.n_sph},
+                   "n_box": world.n_box, "n_sph": world.n_sph, "collision_model": collision_model(world)},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cpu_baseline.cores(), "kind": "port",
                          "sample": "%d of %d queries and their %d directed edges per step; kd-tree built once, "
                                    "untimed" % (sample, n, sample * k)},
@@ -279,8 +294,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default=os.environ.get("MPB_BENCH_WORKLOAD", "c4lite"), choices=sorted(WORKLOADS))
-    ap.add_argument("--ref-sample", type=int, default=100000)
+    ap.add_argument("--workload", default=os.environ.get("MPB_BENCH_WORKLOAD", "c4"), choices=sorted(WORKLOADS))
+    ap.add_argument("--ref-sample", type=int, default=0, help="queries per step of the CPU arm (0: per workload)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra", action="store_true", help="skip the extra 1M-sample measurement")
     args = ap.parse_args()
@@ -357,15 +372,29 @@ def main():
         total_ms = float(t.item())
         edges_local = torch.tensor([rm.n_edges_checked()], device="cuda", dtype=torch.int64)
         fb = rm.stats[:1].clone()
+        tiles_visited = rm.stats[1:2].clone()
         if world_size > 1:
             dist.all_reduce(edges_local)
             dist.all_reduce(fb)
+            dist.all_reduce(tiles_visited)
         edges_total = int(edges_local.item())
+        # waypoints per directed edge (samplers.py:119-120), measured on the first rows of this rank (untimed)
+        rows = min(hi - lo, 50000)
+        own = torch.arange(rows, device="cuda") + rm.offset
+        nb = rm.nbr_idx[:rows]
+        real = (nb >= 0) & (nb != own.unsqueeze(1))
+        q1 = rm.samples[own].unsqueeze(1).expand(-1, nb.shape[1], -1)[real]
+        q2 = rm.samples[nb.clamp(min=0)][real]
+        wp = ops.edges_count(q1.contiguous(), q2.contiguous(), step=rm.step).double()
+        hit_frac = float((rm.edge_hit[:rows][real] >= 0).double().mean().item())
+        free_vertices = 1.0 - float(rm.vertex_hit.double().mean().item())
         ms_step = total_ms / steps
         out = {"world": world, "X": X, "k": k, "desc": desc, "n": n, "D": D, "ms_step": ms_step,
                "edges": edges_total, "value": edges_total / (ms_step * 1e-3), "qps": n / (ms_step * 1e-3),
                "phase_ms": {a: b / steps for a, b in phase.items()}, "clocks": clocks, "launches": rm.launches,
-               "fallback_queries": int(fb.item()), "n_local": hi - lo, "wall_s": wall_s}
+               "fallback_queries": int(fb.item()), "n_local": hi - lo, "wall_s": wall_s,
+               "tiles_visited": int(tiles_visited.item()), "mean_waypoints": float(wp.mean().item()),
+               "edge_hit_frac": hit_frac, "free_vertex_frac": free_vertices}
 
         if with_e2e:
             pinned = torch.from_numpy(np.ascontiguousarray(X[lo:hi])).pin_memory()
@@ -383,7 +412,7 @@ def main():
                 def e2e_step():
                     dev = pinned.cuda(non_blocking=True)
                     rm2.build(dev, gathered=rm2.gather_samples_equal(dev, gathered_buf) if equal else None)
-                    outs = (rm2.nbr_idx, rm2.vertex_hit, rm2.edge_hit)
+                    outs = (rm2.nbr_idx.to(torch.int32), rm2.vertex_hit, rm2.edge_hit)
                     if not hasattr(rm2, "_host_out"):
                         rm2._host_out = tuple(torch.empty(o.shape, dtype=o.dtype).pin_memory() for o in outs)
                     for hbuf, o in zip(rm2._host_out, outs):
@@ -410,72 +439,110 @@ def main():
 
     m = measure(args.workload, args.steps, args.warmup, with_e2e=True)
 
-    # ---- roofline of the dominant kernel (the fp32 filter pass of the kNN)
+    # ---- rooflines (every number below can be recomputed from the keys beside it)
     peaks_file = {}
     try:
         peaks_file = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except Exception:
         pass
-    fp32_scalar = ops.peak_fma(torch.float32)
-    fp32_packed = ops.peak_fma(torch.float32, packed=True)
-    fp32_peak = max(fp32_scalar, fp32_packed)            # the higher of the FFMA and FFMA2 issue peaks
-    fp64_peak = ops.peak_fma(torch.float64)
+    fp32_peak = max(ops.peak_fma(torch.float32), ops.peak_fma(torch.float32, packed=True))
+    fp64_peak = ops.peak_fma(torch.float64)              # FLOP/s, FMA = 2
+    hbm_peak = peaks_file.get("hbm_gbs")
+    bf16_peak = peaks_file.get("bf16_tflops_sustained") or peaks_file.get("bf16_tflops")
+    tf32_peak = (bf16_peak / 2.0) if bf16_peak else 1130.0
+    from motion_planners_b200 import _lib as _mplib
+
+    def knn_roofline(r):
+        """kNN scan.  SURVEY 8d: algorithmic work = 3*D flop per (query, sample) pair, all pairs."""
+        n, D, k, n_local = r["n"], r["D"], r["k"], r["n_local"]
+        ms = r["phase_ms"].get("knn", float("nan"))
+        pairs = float(n_local) * world_size * n
+        alg = 3.0 * D * pairs
+        kind = _mplib.lib().mpb_knn_filter_kind(int(n), int(D), int(k) + 1)
+        out = {"kernel": {0: "knn_filter_kernel", 1: "knn_tc_kernel", 2: "knn_exact_kernel"}[kind],
+               "kernel_ms": ms, "pairs": pairs, "algorithmic_flops_per_pair": 3 * D,
+               "algorithmic_tflops": alg / (ms * 1e-3) / 1e12}
+        if kind == 1:
+            # tensor-core scan: TF32 pipe.  Executed work = tiles read x (128 queries x 256 candidates) x 2 x 24
+            # (every fp32 value enters as two TF32 parts: 24 operand columns).  The scan skips the tiles whose
+            # bounding box is provably too far from a query block, so executed << algorithmic and
+            # frac (algorithmic / peak) can exceed 1; frac_executed is what the tensor pipe actually did.
+            executed = float(r["tiles_visited"]) * 128 * 256 * 48
+            out.update({
+                "bound": "tensor", "achieved": alg / (ms * 1e-3) / 1e12, "peak": tf32_peak, "unit": "TFLOP/s",
+                "frac": alg / (ms * 1e-3) / 1e12 / tf32_peak,
+                "peak_source": ("MEASURED_PEAKS.json bf16_tflops_sustained / 2 (TF32 runs at half the bf16 rate); that figure "
+                                "was measured at a %s MHz median SM clock under power capping, this kernel runs at the clock in "
+                                "`clocks`" % peaks_file.get("clocks_under_load", {}).get("sm_mhz_median", "?")) if bf16_peak
+                else "fallback: nominal dense TF32, 1130 TFLOP/s",
+                "executed_flops_per_pair_visited": 48, "tiles_read": r["tiles_visited"],
+                "tiles_read_per_query_block": r["tiles_visited"] / max(1.0, n_local * world_size / 128.0),
+                "tiles_total": (n + 255) // 256, "pairs_visited_frac": executed / 48.0 / pairs,
+                "executed_tflops": executed / (ms * 1e-3) / 1e12,
+                "frac_executed": executed / (ms * 1e-3) / 1e12 / tf32_peak,
+                "ncu_tensor_pipe_active_pct": NCU["knn_tc_kernel"]["tensor_pipe_active_pct"],
+                "traffic": NCU["knn_tc_kernel"]["traffic"] if (world_size == 1 and r is m) else None,
+                "ncu_source": NCU["knn_tc_kernel"]["source"],
+            })
+        else:
+            out.update({"bound": "fp32", "achieved": alg / (ms * 1e-3) / 1e12, "peak": fp32_peak / 1e12, "unit": "TFLOP/s",
+                        "frac": alg / (ms * 1e-3) / fp32_peak, "executed_flops_per_pair": 2 * D,
+                        "frac_executed": 2.0 * D * pairs / (ms * 1e-3) / fp32_peak,
+                        "peak_source": "measured live: max of the FFMA and FFMA2 micro-benchmarks (mpb_peak_fma_f32*)",
+                        "traffic": None})
+        return out
+
+    def edges_roofline(r):
+        """extend_fn + collision_fn over the directed edges.  SURVEY 8d: per waypoint 3*D flop for the recurrence
+        plus the collision test; per edge 16 B of indices + 2*D*8 B of gathered end points + 4 B of verdict."""
+        n, D, k = r["n"], r["D"], r["k"]
+        world = r["world"]
+        ms = r["phase_ms"].get("edges", float("nan"))
+        rows_edges = float(r["n_local"]) * world_size * (k + 1)       # edges the kernel walks (self-edges included)
+        wp = r["mean_waypoints"]
+        arm = hasattr(world, "model")
+        if arm:
+            S, B, J = world.n_sph, world.n_box, world.model.n_joints
+            fk = 68 * J + 12 * S                                      # chain (sincos, frame turn, link) + sphere centres
+            test_all = 17 * S * B                                     # clamp / subtract / fused square-add per axis + compare
+            kernel = "arm_edges_kernel"
+            model = ("per waypoint: %d (recurrence) + %d (forward kinematics of %d joints, %d sphere centres) + %d "
+                     "(%d spheres x %d boxes x 17, un-culled; the kernel tests only the boxes listed for the sphere's grid "
+                     "cell and stops at the first hit)" % (3 * D, fk, J, S, test_all, S, B))
+        else:
+            fk = 0
+            test_all = 2 * D * world.n_box + (2 * D + 2) * world.n_sph
+            kernel = "edges_check_rows_kernel" if r["n_local"] >= 300000 else "edges_check_kernel"
+            model = ("per waypoint: %d (recurrence) + %d (%d boxes x 2*D compares + %d spheres, un-culled; the kernel culls "
+                     "obstacles against the row's bounding box first)" % (3 * D, test_all, world.n_box, world.n_sph))
+        flop_wp = 3 * D + fk + test_all
+        alg = rows_edges * wp * flop_wp
+        bytes_edge = 16 + 2 * D * 8 + 4
+        gbs = rows_edges * bytes_edge / (ms * 1e-3) / 1e9
+        tfl = alg / (ms * 1e-3) / 1e12
+        f64 = fp64_peak / 1e12
+        frac_f64 = tfl / f64
+        frac_hbm = (gbs / hbm_peak) if hbm_peak else None
+        ncu = NCU.get(kernel, {})
+        return {"kernel": kernel, "kernel_ms": ms, "edges_walked": rows_edges, "mean_waypoints_per_edge": wp,
+                "colliding_edge_frac": r["edge_hit_frac"], "free_vertex_frac": r["free_vertex_frac"],
+                "algorithmic_flops_per_waypoint": flop_wp, "flop_model": model,
+                "bound": "fp64", "achieved": tfl, "peak": f64, "unit": "TFLOP/s", "frac": frac_f64,
+                "peak_source": "measured live: DFMA micro-benchmark (mpb_peak_fma_f64), FMA = 2 flop",
+                "note": "algorithmic (un-culled, no early exit) flop over time: above 1 means the culling and the early "
+                        "exit skipped that much work, not that the pipe ran faster than its peak",
+                "bytes_per_edge": bytes_edge, "hbm": {"achieved_gbs": gbs, "peak_gbs": hbm_peak, "frac": frac_hbm},
+                "binding": "fp64 pipe / latency (hbm fraction %.4f)" % (frac_hbm or 0.0),
+                "ncu_fp64_pipe_active_pct": ncu.get("fp64_pipe_active_pct"), "traffic": ncu.get("traffic") if world_size == 1 else None,
+                "ncu_source": ncu.get("source")}
+
+    roofline_knn = knn_roofline(m)
+    roofline_edges = edges_roofline(m)
     n, D, k = m["n"], m["D"], m["k"]
     knn_ms = m["phase_ms"].get("knn", float("nan"))
-    fma_flops = 2.0 * D * float(m["n_local"]) * n            # one FFMA per dimension per (query, sample) pair
-    achieved = fma_flops / (knn_ms * 1e-3)
-    hbm_peak = peaks_file.get("hbm_gbs")
-    # algorithmic HBM bytes of the step: samples in (fp64), packed tiles out+in once, neighbour matrix
-    # (idx + dist) out and idx back in for the edge pass, flags out
-    step_bytes = m["n_local"] * (D * 8 + (k + 1) * (8 + 8 + 8 + 4) + 1) + n * (D * 8 + 2 * 32)
-    roofline = {
-        "kernel": "knn_filter_kernel", "bound": "fp32", "achieved": achieved / 1e12, "peak": fp32_peak / 1e12,
-        "unit": "TFLOP/s", "frac": achieved / fp32_peak,
-        "peak_source": "measured live on this GPU: max of the FFMA and FFMA2 micro-benchmarks (mpb_peak_fma_f32 / "
-                       "mpb_peak_fma_f32x2); MEASURED_PEAKS.json carries only HBM and bf16 tensor peaks; nominal "
-                       "fp32 = 148 SM x 128 lanes x 2 x 1.965 GHz = 74.4",
-        "peak_ffma_tflops": fp32_scalar / 1e12, "peak_ffma2_tflops": fp32_packed / 1e12,
-        "flops_per_pair": 2 * D, "survey_flops_per_pair": 3 * D,
-        "frac_on_survey_count": (3.0 * D * m["n_local"] * n / (knn_ms * 1e-3)) / fp32_peak,
-        # dram__bytes_read.sum + dram__bytes_write.sum of one launch, from the committed ncu --set full capture
-        # (profiles/r1_ncu_full_knn_filter_edges_check_raw.csv); measured for the default workload only
-        "traffic": NCU_DRAM_BYTES_PER_LAUNCH.get(args.workload) if world_size == 1 else None,
-        "kernel_ms": knn_ms,
-        "hbm": {"achieved_gbs": step_bytes / (m["ms_step"] * 1e-3) / 1e9, "peak_gbs": hbm_peak,
-                "frac": (step_bytes / (m["ms_step"] * 1e-3) / 1e9 / hbm_peak) if hbm_peak else None,
-                "note": "whole step, algorithmic bytes; the path is FMA-pipe bound, not HBM bound"},
-        "fp64_fma_peak_tflops": fp64_peak / 1e12,
-    }
-
-    from motion_planners_b200 import _lib as _mplib
-    if _mplib.lib().mpb_knn_filter_kind(int(n), int(D), int(k) + 1) == 1:
-        # The kNN ran on the tensor-core scan: three tcgen05.mma kind::tf32 k-steps (K = 24 operand columns: every
-        # fp32 value enters as two TF32 parts) per 128-query x 256-candidate tile.  Executed tensor flops per
-        # (query, sample) pair = 2 * 24.  Peak: MEASURED_PEAKS.json has the dense bf16 rate (sustained figure: the
-        # kernel is timed inside a long step); TF32 runs at half of it.
-        tc_flops = 2.0 * 24 * float(m["n_local"]) * n
-        bf16_peak = peaks_file.get("bf16_tflops_sustained") or peaks_file.get("bf16_tflops")
-        tf32_peak = (bf16_peak / 2.0) if bf16_peak else 1130.0
-        tc_achieved = tc_flops / (knn_ms * 1e-3) / 1e12
-        fp32_view = dict(roofline)
-        for key in ("kernel", "bound", "traffic", "hbm", "kernel_ms"):
-            fp32_view.pop(key, None)
-        roofline = {
-            "kernel": "knn_tc_kernel", "bound": "tensor", "achieved": tc_achieved, "peak": tf32_peak,
-            "unit": "TFLOP/s", "frac": tc_achieved / tf32_peak,
-            "peak_source": ("MEASURED_PEAKS.json bf16_tflops_sustained / 2 (TF32 is half the bf16 rate)" if bf16_peak
-                            else "fallback: nominal dense TF32, 1130 TFLOP/s"),
-            "flops_per_pair": 48, "survey_flops_per_pair": 3 * D,
-            "note": "the MMAs occupy about a quarter of the kernel; what bounds it is the CUDA-core epilogue that "
-                    "reads every key out of tensor memory (tcgen05.ld), takes a min-tree per 32 keys and inserts the "
-                    "takers (profiles/r1_summary.md, r1h)",
-            # dram__bytes_read.sum + dram__bytes_write.sum of one launch (profiles/r1j_ncu_full_knn_tc_raw.csv)
-            "traffic": NCU_DRAM_BYTES_PER_LAUNCH_TC.get(args.workload) if world_size == 1 else None,
-            "kernel_ms": knn_ms, "hbm": roofline["hbm"],
-            # the same time expressed on the fp32 formulation's count (2*D flop per pair) against the FFMA2 peak:
-            # above 1 means faster than a perfect FFMA2 kernel could be
-            "as_fp32_filter": fp32_view,
-        }
+    dominant = roofline_knn if knn_ms >= m["phase_ms"].get("edges", 0.0) else roofline_edges
+    roofline = dict(dominant)
+    roofline["dominant_of"] = {p_: v for p_, v in m["phase_ms"].items()}
 
     line = {
         "metric": METRIC, "value": m["value"], "unit": UNIT, "n_gpus": world_size, "steps": args.steps,
@@ -484,14 +551,16 @@ def main():
         "dtype": "f64 (fp32 / split-TF32 filter pass inside the kNN, results bit-exact to the fp64 reference)",
         "data": "synthetic", "knn_queries_per_s": m["qps"],
         "config": {"workload": args.workload, "description": m["desc"], "n_samples": n, "dim": D, "k": k,
-                   "n_box": m["world"].n_box, "n_sph": m["world"].n_sph, "edges_per_step": m["edges"],
+                   "n_box": m["world"].n_box, "n_sph": m["world"].n_sph, "collision_model": collision_model(m["world"]),
+                   "edges_per_step": m["edges"],
                    "sharding": "samples sharded over ranks, one NCCL all-gather per step, edges stay sharded",
                    "l2": "flushed between timed steps (256 MiB write, untimed); inputs are smaller than L2"},
         "phases_ms": m["phase_ms"],
         "kernel_rates": {"knn_queries_per_s": m["n_local"] * world_size / (knn_ms * 1e-3),
                          "edges_per_s": m["edges"] / (m["phase_ms"].get("edges", float("nan")) * 1e-3)},
         "fallback_queries": m["fallback_queries"],
-        "roofline": roofline, "clocks": m["clocks"], "e2e": m["e2e"], "gpu_launches": m["launches"] * args.steps,
+        "roofline": roofline, "roofline_knn": roofline_knn, "roofline_edges": roofline_edges,
+        "clocks": m["clocks"], "e2e": m["e2e"], "gpu_launches": m["launches"] * args.steps,
         "wall_s_timed_region": m["wall_s"],
     }
 
@@ -511,14 +580,13 @@ def main():
             "sample": "first 40 queries, %d edges, per-call Python structure of the reference" % p["n_edges"]}
 
     if not args.no_extra:
-        other = "c2" if args.workload != "c2" else "c4lite"
-        x = measure(other, max(2, min(args.steps, 10 if other == "c2" else 3)), 3, with_e2e=False)
-        x_knn = x["phase_ms"].get("knn", float("nan"))
-        line["extra_" + other] = {
-            "description": x["desc"], "ms_per_step": x["ms_step"], "edges_per_s": x["value"],
-            "knn_queries_per_s": x["qps"], "edges_per_step": x["edges"], "phases_ms": x["phase_ms"],
-            "knn_fp32_frac": (2.0 * x["D"] * x["n_local"] * x["n"] / (x_knn * 1e-3)) / fp32_peak,
-            "fallback_queries": x["fallback_queries"], "clocks": x["clocks"]}
+        for other in [w_ for w_ in ("c4lite", "c2") if w_ != args.workload]:
+            x = measure(other, max(2, min(args.steps, 10 if other == "c2" else 5)), 3, with_e2e=False)
+            line["extra_" + other] = {
+                "description": x["desc"], "ms_per_step": x["ms_step"], "edges_per_s": x["value"],
+                "knn_queries_per_s": x["qps"], "edges_per_step": x["edges"], "phases_ms": x["phase_ms"],
+                "roofline_knn": knn_roofline(x), "roofline_edges": edges_roofline(x),
+                "fallback_queries": x["fallback_queries"], "clocks": x["clocks"]}
 
     if not args.no_extra:
         line["extra_c3_rrt_connect_batch"] = measure_rrt_batch(world_size, rank, dist if world_size > 1 else None)

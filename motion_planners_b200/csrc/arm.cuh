@@ -174,3 +174,117 @@ __device__ __forceinline__ bool arm_collides(const ArmDev &A, const ArmSmem &S, 
     }
     return hit;
 }
+
+
+// ---- the model's per-joint and per-sphere numbers in shared memory (lanes of a warp sit at different joints) ----
+struct ArmTables {
+    double theta_lo[kArmMaxJoints], theta_span[kArmMaxJoints], a[kArmMaxJoints], d[kArmMaxJoints];
+    double sgn[kArmMaxJoints];                     // +1: joint turns about z (mixes x, y), -1: about y (mixes x, z)
+    double sph_u[kArmMaxSpheres], sph_w[kArmMaxSpheres], sph_rb[kArmMaxSpheres], sph_lo2[kArmMaxSpheres],
+        sph_hi2[kArmMaxSpheres];
+    int sph_first[kArmMaxJoints + 1];
+};
+
+__device__ __forceinline__ void arm_fill_tables(const ArmDev &A, ArmTables *T)
+{
+    for (int i = threadIdx.x; i < kArmMaxJoints; i += blockDim.x) {
+        T->theta_lo[i] = A.theta_lo[i];
+        T->theta_span[i] = A.theta_span[i];
+        T->a[i] = A.a[i];
+        T->d[i] = A.d[i];
+        T->sgn[i] = A.axis[i] == 2 ? 1.0 : -1.0;
+    }
+    for (int i = threadIdx.x; i <= kArmMaxJoints; i += blockDim.x) T->sph_first[i] = A.sph_first[i];
+    for (int j = threadIdx.x; j < kArmMaxSpheres; j += blockDim.x) {
+        T->sph_u[j] = A.sph_u[j];
+        T->sph_w[j] = A.sph_w[j];
+        T->sph_rb[j] = A.sph_rb[j];
+        T->sph_lo2[j] = A.sph_lo2[j];
+        T->sph_hi2[j] = A.sph_hi2[j];
+    }
+}
+
+// the sphere test of arm_sphere_hits with the sphere's numbers from the shared tables
+__device__ __forceinline__ bool arm_sphere_hits_t(const ArmDev &A, const ArmTables &T, const ArmSmem &S, int j, double cx,
+                                                  double cy, double cz)
+{
+    const int ix = (int)floor((cx - A.grid_lo[0]) * A.grid_inv[0]);
+    const int iy = (int)floor((cy - A.grid_lo[1]) * A.grid_inv[1]);
+    const int iz = (int)floor((cz - A.grid_lo[2]) * A.grid_inv[2]);
+    if (ix < 0 || iy < 0 || iz < 0 || ix >= kArmGrid || iy >= kArmGrid || iz >= kArmGrid) return false;
+    const int cell = (ix * kArmGrid + iy) * kArmGrid + iz;
+    const int e = S.cell_start[cell + 1];
+    const double lo2 = T.sph_lo2[j], hi2 = T.sph_hi2[j];
+    for (int it = S.cell_start[cell]; it < e; ++it) {
+        const double2 *bb = S.boxes + 3 * (int)S.cell_items[it];
+        double2 b = bb[0];
+        double cl = cx < b.x ? b.x : cx;
+        cl = cl > b.y ? b.y : cl;
+        double dk = d_sub(cl, cx);
+        double s = __fma_rn(dk, dk, 0.);
+        b = bb[1];
+        cl = cy < b.x ? b.x : cy;
+        cl = cl > b.y ? b.y : cl;
+        dk = d_sub(cl, cy);
+        s = __fma_rn(dk, dk, s);
+        b = bb[2];
+        cl = cz < b.x ? b.x : cz;
+        cl = cl > b.y ? b.y : cl;
+        dk = d_sub(cl, cz);
+        s = __fma_rn(dk, dk, s);
+        if (s < lo2) return true;
+        if (s <= hi2 && __dsqrt_rn(s) <= T.sph_rb[j]) return true;
+    }
+    return false;
+}
+
+// One joint of the chain for a lane whose frame is (X, P = Y or Z by the joint's axis, p): the turn.  Written once
+// for both axes: with s' = +s (about z) or -s (about y),
+//   x' = fl(c x) + fl(s' p),  p' = fl(c p) - fl(s' x)
+// are bit for bit the oracle's c x + s y, c y - s x (about z) and c x - s z, s x + c z (about y): negation is exact
+// and addition commutes.
+struct ArmFrame {
+    double X0, X1, X2, Y0, Y1, Y2, Z0, Z1, Z2, p0, p1, p2;
+};
+
+__device__ __forceinline__ void arm_turn(const ArmTables &T, int ji, double qi, ArmFrame &F)
+{
+    const double th = d_add(d_mul(qi, T.theta_span[ji]), T.theta_lo[ji]);
+    double s, c;
+    arm_sincos(th, s, c);
+    const bool about_z = T.sgn[ji] > 0.;
+    const double sp = about_z ? s : -s;
+    const double P0 = about_z ? F.Y0 : F.Z0, P1 = about_z ? F.Y1 : F.Z1, P2 = about_z ? F.Y2 : F.Z2;
+    const double x0 = F.X0, x1 = F.X1, x2 = F.X2;
+    F.X0 = d_add(d_mul(c, x0), d_mul(sp, P0));
+    F.X1 = d_add(d_mul(c, x1), d_mul(sp, P1));
+    F.X2 = d_add(d_mul(c, x2), d_mul(sp, P2));
+    const double n0 = d_sub(d_mul(c, P0), d_mul(sp, x0));
+    const double n1 = d_sub(d_mul(c, P1), d_mul(sp, x1));
+    const double n2 = d_sub(d_mul(c, P2), d_mul(sp, x2));
+    F.Y0 = about_z ? n0 : F.Y0;
+    F.Y1 = about_z ? n1 : F.Y1;
+    F.Y2 = about_z ? n2 : F.Y2;
+    F.Z0 = about_z ? F.Z0 : n0;
+    F.Z1 = about_z ? F.Z1 : n1;
+    F.Z2 = about_z ? F.Z2 : n2;
+}
+
+// to the end of link ji
+__device__ __forceinline__ void arm_link(const ArmTables &T, int ji, ArmFrame &F)
+{
+    const double al = T.a[ji], dl = T.d[ji];
+    F.p0 = d_add(d_add(F.p0, d_mul(al, F.X0)), d_mul(dl, F.Z0));
+    F.p1 = d_add(d_add(F.p1, d_mul(al, F.X1)), d_mul(dl, F.Z1));
+    F.p2 = d_add(d_add(F.p2, d_mul(al, F.X2)), d_mul(dl, F.Z2));
+}
+
+// sphere j of the current frame against the boxes of its grid cell
+__device__ __forceinline__ bool arm_sphere(const ArmDev &A, const ArmTables &T, const ArmSmem &S, int j, const ArmFrame &F)
+{
+    const double u = T.sph_u[j], w = T.sph_w[j];
+    const double cx = d_add(d_add(F.p0, d_mul(u, F.X0)), d_mul(w, F.Z0));
+    const double cy = d_add(d_add(F.p1, d_mul(u, F.X1)), d_mul(w, F.Z1));
+    const double cz = d_add(d_add(F.p2, d_mul(u, F.X2)), d_mul(w, F.Z2));
+    return arm_sphere_hits_t(A, T, S, j, cx, cy, cz);
+}

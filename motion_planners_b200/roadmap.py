@@ -173,12 +173,13 @@ class DeviceRoadmap(object):
         return {b: self.events[a].elapsed_time(self.events[b]) for a, b in zip(have[:-1], have[1:])}
 
     def build_from_host(self, pinned_samples):
-        """End-to-end call with HOST buffers: a pinned float64 [N, D] CPU tensor in; neighbour matrix,
+        """End-to-end call with HOST buffers: a pinned float64 [N, D] CPU tensor in; neighbour matrix (int32),
         vertex flags and edge flags back on the host.  Host->device and device->host copies are part of
         the call; this is what bench.py times as `e2e`."""
         dev = pinned_samples.cuda(non_blocking=True)
         self.build(dev)
-        outs = (self.nbr_idx, self.vertex_hit, self.edge_hit)
+        # sample indices are below 2^31 (the C ABI refuses larger sets): the neighbour matrix crosses PCIe as int32
+        outs = (self.nbr_idx.to(torch.int32), self.vertex_hit, self.edge_hit)
         host = getattr(self, "_host_out", None)
         if host is None or any(h.shape != o.shape for h, o in zip(host, outs)):
             host = self._host_out = tuple(torch.empty(o.shape, dtype=o.dtype).pin_memory() for o in outs)

@@ -20,6 +20,8 @@ import oracle
 
 
 def _oracle_world(world):
+    if hasattr(world, "model"):                      # configs[3]: the sphere-approximated arm (oracle/arm_oracle.c)
+        return oracle.ArmWorld(world)
     return oracle.World(world.dim, world.env_lo, world.env_hi, world.box_lo, world.box_hi, world.sph_c,
                         world.sph_r, world.buffer)
 
@@ -48,7 +50,24 @@ def _py_contains_box(point, lower, upper, buffer):
     return np.less_equal(lo, point).all() and np.less_equal(point, hi).all()
 
 
+def _py_collision_arm(world, q):
+    """The arm's collision_fn written the way a user of the reference would: numpy per call, one forward
+    kinematics and a Python loop over the boxes per configuration."""
+    from oracle import np_oracle
+    if not _py_contains_box(q, world.env_lo, world.env_hi, 0.):
+        return True
+    cen = np_oracle.arm_centres(world.model, np.asarray(q, dtype=np.float64).reshape(1, -1))[0]
+    rb = np.asarray(world.model.sph_r) + world.buffer
+    for lo, hi in zip(world.box_lo, world.box_hi):
+        d = np.minimum(np.maximum(cen, lo), hi) - cen
+        if (np.sqrt((d * d).sum(1)) <= rb).any():
+            return True
+    return False
+
+
 def _py_collision(world, q):
+    if hasattr(world, "model"):
+        return _py_collision_arm(world, q)
     if not _py_contains_box(q, world.env_lo, world.env_hi, 0.):
         return True
     for lo, hi in zip(world.box_lo, world.box_hi):
