@@ -380,7 +380,7 @@ def main():
         edges_total = int(edges_local.item())
         # waypoints per directed edge (samplers.py:119-120), measured on the first rows of this rank (untimed)
         rows = min(hi - lo, 50000)
-        own = torch.arange(rows, device="cuda") + rm.offset
+        own = rm.row_ids[:rows]
         nb = rm.nbr_idx[:rows]
         real = (nb >= 0) & (nb != own.unsqueeze(1))
         q1 = rm.samples[own].unsqueeze(1).expand(-1, nb.shape[1], -1)[real]

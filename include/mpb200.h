@@ -359,6 +359,15 @@ int mpb_knn_tc_key_error(const double *samples, int64_t n_samples, const double 
                          int dim, const double *weights, void *workspace, size_t workspace_bytes,
                          unsigned long long *out, void *stream);
 
+/* The spatial order of a prepared sample set: out_order dev [n_samples] i32 = the sample indices in the leaf order
+ * of the balanced k-d partition mpb_knn_prepare built for the tensor-core scan (consecutive entries are close in
+ * space).  A multi-GPU caller gives every rank a contiguous slice of this order as its queries, so that each
+ * rank's query blocks are as compact as a single GPU's (roadmap.py).  MPB_EINVAL when the set is not served by
+ * the tensor-core scan (mpb_knn_filter_kind), which builds no order.  No counterpart in the reference (scipy's
+ * cKDTree keeps its tree to itself, nearest.py:59-61). */
+int mpb_knn_sample_order(const void *workspace, size_t workspace_bytes, int64_t n_samples, int dim,
+                         int32_t *out_order, void *stream);
+
 /* Kernels launched so far by the mpb_knn_* entry points on the calling host thread (a monotone counter;
  * callers report differences).  No counterpart in the reference. */
 int mpb_knn_launch_count(void);

@@ -52,6 +52,7 @@ SIGNATURES = {
     "mpb_knn_filter_kind": (c_int, [c_i64, c_int, c_int]),
     "mpb_knn_tc_key_error": (c_int, [c_vp, c_i64, c_vp, c_i64, c_int, c_hostf64, c_vp, c_sz, c_vp, c_vp]),
     "mpb_knn_launch_count": (c_int, []),
+    "mpb_knn_sample_order": (c_int, [c_vp, c_sz, c_i64, c_int, c_vp, c_vp]),
     "mpb_knn_f64": (c_int, [c_vp, c_i64, c_vp, c_i64, c_int, c_hostf64, c_int, c_dbl, c_vp, c_vp, c_vp]),
     "mpb_knn_f64_metric": (c_int, [c_vp, c_i64, c_vp, c_i64, c_int, c_hostf64, c_int, c_int, c_dbl, c_vp, c_vp, c_vp]),
     "mpb_knn_workspace_bytes": (c_sz, [c_i64, c_i64, c_int]),

@@ -651,7 +651,8 @@ inline KdPlan tc_sample_plan(int64_t N, int D) { return kd_plan(N, 2 * ((N + kTc
 inline KdPlan tc_query_plan(int64_t M, int D) { return kd_plan(M, (M + kTcQueries - 1) / kTcQueries, D, false); }
 
 struct WsLayout {
-    size_t packed_off, packed_bytes, tc_off, tc_bytes, slot_off, slot_bytes, box_off, box_bytes, fb_off, fb_bytes, surv_off,
+    size_t packed_off, packed_bytes, tc_off, tc_bytes, slot_off, slot_bytes, box_off, box_bytes, perm_off, perm_bytes, fb_off,
+        fb_bytes, surv_off,
         surv_bytes, thr_off, thr_bytes, qord_off, qord_bytes, sort_off, sort_bytes, total;
     int64_t n_tiles, n_pad, tc_tiles, tc_slots;
     int box_stride;
@@ -679,7 +680,9 @@ WsLayout ws_layout(int64_t N, int64_t M, int D, bool allow_tc = true)
     L.box_stride = (int)((L.tc_tiles + 31) & ~(int64_t)31);
     L.box_off = L.slot_off + L.slot_bytes;
     L.box_bytes = up((size_t)16 * L.box_stride * sizeof(float));
-    L.fb_off = L.box_off + L.box_bytes;
+    L.perm_off = L.box_off + L.box_bytes;
+    L.perm_bytes = tc ? up((size_t)(N > 0 ? N : 1) * sizeof(uint32_t)) : 0;     // the samples' k-d leaf order, kept
+    L.fb_off = L.perm_off + L.perm_bytes;
     L.fb_bytes = up(m * sizeof(int));
     // query slots: blocks of 128; the sample set as its own query set uses the tiles' own slots
     const int64_t own = (M == N) ? L.tc_tiles * kTcTile : 0;
@@ -771,6 +774,8 @@ int launch_prepare(const double *x, int64_t N, const Weights &wt, void *ws, bool
             knn_tc_pack_kernel<D><<<(unsigned)L.tc_tiles, kTcTile, 0, st>>>(x, N, leaves, perm, wt, h, tiles, slot_idx,
                                                                          boxes, L.box_stride);
             MPB_LAUNCH_CHECK();
+            // the order outlives the sort scratch (mpb_knn_sample_order hands it to callers that shard by it)
+            MPB_CUDA_CHECK(cudaMemcpyAsync(base + L.perm_off, perm, (size_t)N * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
             g_last_launches += 2;
         }
     }
@@ -1037,6 +1042,22 @@ MPB_API int mpb_knn_tc_key_error(const double *samples, int64_t n_samples, const
     MPB_DISPATCH_DIM(dim, CALL)
 #undef CALL
     return MPB_EINVAL;
+}
+
+MPB_API int mpb_knn_sample_order(const void *workspace, size_t workspace_bytes, int64_t n_samples, int dim,
+                                 int32_t *out_order, void *stream)
+{
+    MPB_REQUIRE(dim >= 1 && dim <= MPB_MAX_DIM && n_samples > 0 && workspace && out_order, "mpb_knn_sample_order: bad argument");
+    const WsLayout L = ws_layout(n_samples, 0, dim, true);
+    if (L.tc_tiles == 0) {
+        mpb_set_error("mpb_knn_sample_order: a set of %lld samples at dim %d is not spatially ordered (the tensor-core "
+                      "scan does not serve it)", (long long)n_samples, dim);
+        return MPB_EINVAL;
+    }
+    MPB_REQUIRE(workspace_bytes >= L.total, "mpb_knn_sample_order: workspace too small");
+    MPB_CUDA_CHECK(cudaMemcpyAsync(out_order, reinterpret_cast<const char *>(workspace) + L.perm_off,
+                                   (size_t)n_samples * sizeof(int32_t), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    return MPB_OK;
 }
 
 MPB_API int mpb_knn_launch_count(void) { return g_last_launches; }

@@ -282,6 +282,17 @@ class KnnIndex(object):
             self._prepared = True
         return ws, nbytes
 
+    def spatial_order(self):
+        """Sample indices in the k-d leaf order of the prepared set (int64 [N], neighbours in the list are
+        neighbours in space), or None when the set is too small for the scan that builds it."""
+        if _lib.lib().mpb_knn_filter_kind(self.n, self.dim, 11) != 1:
+            return None
+        ws, nbytes = self.prepare(self._ws_queries if self._ws_queries > 0 else 0)
+        out = torch.empty(self.n, dtype=torch.int32, device=self.samples.device)
+        rc = _lib.lib().mpb_knn_sample_order(ws, nbytes, self.n, self.dim, _ptr(out), _stream())
+        _lib.check(rc, "mpb_knn_sample_order")
+        return out.long()
+
     def search(self, queries, k, max_dist=math.inf, want_dist=True, stats=None, out_idx=None, out_dist=None):
         queries = _f64(queries, "queries", self.dim)
         M = queries.shape[0]

@@ -12,8 +12,12 @@ passes over tensors that stay in HBM:
                                     -1: free (or no edge: self / missing neighbour)
 
 Samples are sharded across ranks; one all-gather (NCCL over NVLink) builds the global sample
-set, every rank answers the queries of its own shard against it and checks the directed
-edges that leave its shard.  Results are identical for every world size.
+set, every rank answers its share of the queries against it and checks the directed edges that
+leave those samples.  Which rows a rank owns (`row_ids`): its own index shard for small sets;
+for sets the tensor-core scan serves, a contiguous slice of the set's spatial (k-d leaf) order,
+so that the 128-query blocks of every rank are as compact in space as a single GPU's and the
+scan prunes as well at 8 GPUs as at 1.  The union of the ranks' rows is identical for every
+world size (`gather_global` assembles it in sample order).
 """
 import math
 
@@ -85,6 +89,7 @@ class DeviceRoadmap(object):
         self.step = float(step)
         self.group = group
         self.obstacles = ops.ObstacleSet(world)
+        self.sharding = "auto"                     # "index": every rank keeps the rows of its own sample shard
         self.launches = 0                          # kernels of this library launched by the last build()
         self.profile = False                       # record CUDA events around each phase of build()
         self.events = {}
@@ -115,7 +120,6 @@ class DeviceRoadmap(object):
             samples, offset = gathered
         n_local = local_samples.shape[0]
         self.samples, self.offset, self.n_local = samples, offset, n_local
-        queries = samples[offset:offset + n_local]
         launches = 0
         mark = self._mark
         mark("start")
@@ -125,7 +129,21 @@ class DeviceRoadmap(object):
             self._index = ops.KnnIndex(samples, self.weights)
         count0 = _lib.lib().mpb_knn_launch_count()  # the library counts the kernels its kNN entry points launch
         self._index._prepared = False
-        self._index.prepare(n_local)
+        _, ws_size, rank = self._dist()
+        N = samples.shape[0]
+        spatial = ws_size > 1 and n_local < N and self.sharding != "index"
+        self._index.prepare(max(n_local, -(-N // ws_size)))
+        order = self._index.spatial_order() if spatial else None
+        if order is not None:
+            # this rank's rows: a contiguous slice of the spatial order (every rank computes the same order)
+            a, b = shard_bounds(N, ws_size, rank)
+            self.row_ids = order[a:b].contiguous()
+            n_local = self.n_local = b - a
+            queries = samples.index_select(0, self.row_ids)
+            self.offset = None
+        else:
+            self.row_ids = torch.arange(offset, offset + n_local, device=samples.device, dtype=torch.int64)
+            queries = samples[offset:offset + n_local]
         mark("packed")
         if getattr(self, "nbr_idx", None) is None or self.nbr_idx.shape != (n_local, self.kk):
             self.nbr_idx = torch.empty((n_local, self.kk), dtype=torch.int64, device=samples.device)
@@ -142,7 +160,13 @@ class DeviceRoadmap(object):
             mark("vertices")
             # self-edges (one waypoint) and missing neighbours (-1, skipped) ride along, so the neighbour
             # matrix is consumed in place with no compaction pass
-            if n_local >= self.ROWS_KERNEL_MIN:
+            if self.offset is None:
+                # rows in spatial order: explicit source indices
+                src = self.row_ids.unsqueeze(1).expand(-1, self.kk).reshape(-1)
+                hit, _ = self.obstacles.edges_check(samples, src, self.nbr_idx.view(-1), mode=ops.EDGE_ANY,
+                                                    step=self.step, want_counts=False)
+                self.edge_hit = hit.view(n_local, self.kk)
+            elif n_local >= self.ROWS_KERNEL_MIN:
                 # one thread per row: obstacles culled once per sample (1.7x faster at 1M rows, measured)
                 self.edge_hit, _ = self.obstacles.edges_check_knn(samples, self.nbr_idx, row_offset=offset,
                                                                   mode=ops.EDGE_ANY, step=self.step)
@@ -307,14 +331,26 @@ class DeviceRoadmap(object):
     # -- counts for the metric
     def n_edges_checked(self):
         """Directed sample->neighbour edges checked (self and missing slots excluded)."""
-        own = torch.arange(self.n_local, device=self.nbr_idx.device).unsqueeze(1) + self.offset
+        own = self.row_ids.unsqueeze(1)
         return int(((self.nbr_idx >= 0) & (self.nbr_idx != own)).sum().item())
+
+    def gather_global(self):
+        """Every rank's rows assembled in sample order on every rank:
+        -> (nbr_idx [N, k+1], nbr_dist, vertex_hit [N] bool, edge_hit [N, k+1])."""
+        ids = gather_rows(self.row_ids.unsqueeze(1))[:, 0]
+        out = []
+        for t in (self.nbr_idx, self.nbr_dist, self.vertex_hit.to(torch.uint8).unsqueeze(1), self.edge_hit):
+            rows = gather_rows(t)
+            full = torch.empty_like(rows)
+            full[ids] = rows
+            out.append(full)
+        return out[0], out[1], out[2][:, 0].bool(), out[3]
 
     # -- host views
     def undirected_edges(self):
         """Sorted unique (v1 < v2) pairs of this rank's directed edges, as a numpy int64 [E, 2]."""
         idx = self.nbr_idx.cpu().numpy()
-        own = np.arange(self.n_local)[:, None] + self.offset
+        own = self.row_ids.cpu().numpy()[:, None]
         mask = (idx >= 0) & (idx != own)
         a = np.broadcast_to(own, idx.shape)[mask]
         b = idx[mask]

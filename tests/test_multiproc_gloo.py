@@ -76,3 +76,22 @@ def test_shard_bounds_cover_everything():
             assert all(a[1] == b[0] for a, b in zip(spans[:-1], spans[1:]))
             sizes = [b - a for a, b in spans]
             assert max(sizes) - min(sizes) <= 1
+
+
+def test_spatial_slices_partition_the_samples():
+    """Rows owned by slices of a spatial order (any permutation of the samples) cover every sample exactly once for
+    every world size, and scattering per-rank rows back by their ids rebuilds the global table: the host logic of
+    DeviceRoadmap's spatial sharding and gather_global."""
+    from motion_planners_b200.roadmap import shard_bounds
+    rs = np.random.RandomState(0)
+    for n in (1, 5, 1000, 4097):
+        order = torch.from_numpy(rs.permutation(n))
+        table = torch.from_numpy(rs.uniform(size=(n, 3)))
+        for ws in (1, 2, 3, 8):
+            ids = [order[slice(*shard_bounds(n, ws, r))] for r in range(ws)]
+            allids = torch.cat(ids)
+            assert sorted(allids.tolist()) == list(range(n))
+            rows = torch.cat([table[i] for i in ids])          # what each rank computes, concatenated in rank order
+            full = torch.empty_like(rows)
+            full[allids] = rows
+            assert torch.equal(full, table)
