@@ -128,6 +128,11 @@ int mpb_edges_check(const mpb_world *world, const double *samples, int64_t n_sam
 int mpb_edges_check_knn(const mpb_world *world, const double *samples, int64_t n_samples,
                         const int64_t *nbr, int64_t n_rows, int row_len, int64_t row_offset, double step,
                         int mode, int skip_last, int32_t *out_hit, int32_t *out_n, void *stream);
+/* mpb_edges_check_knn for rows that are not a contiguous range of samples: row r leaves sample row_ids[r]
+ * (dev [n_rows] i64) -- the rows of one rank of a roadmap sharded by spatial order (mpb_knn_search_part). */
+int mpb_edges_check_knn_rows(const mpb_world *world, const double *samples, int64_t n_samples,
+                             const int64_t *row_ids, const int64_t *nbr, int64_t n_rows, int row_len, double step,
+                             int mode, int skip_last, int32_t *out_hit, int32_t *out_n, void *stream);
 /* edges as explicit endpoint arrays: q1, q2 dev [E, dim] f64 */
 int mpb_edges_check_pairs(const mpb_world *world, const double *q1, const double *q2,
                           int64_t n_edges, double step, int mode, int skip_last, int32_t *out_hit,
@@ -367,6 +372,21 @@ int mpb_knn_tc_key_error(const double *samples, int64_t n_samples, const double 
  * cKDTree keeps its tree to itself, nearest.py:59-61). */
 int mpb_knn_sample_order(const void *workspace, size_t workspace_bytes, int64_t n_samples, int dim,
                          int32_t *out_order, void *stream);
+
+/* mpb_knn_search for one share of the sample set queried against itself -- the multi-GPU form of
+ * lazy_prm.py:148-160 add_samples (every sample asks for its neighbours among all samples): after the all-gather
+ * every rank holds all samples, prepares the same workspace, and answers part `part` of `parts` of the queries.
+ * The parts are contiguous slices of the set's spatial order (whole k-d leaves), so every rank's 128-query blocks
+ * are exactly the blocks a single-GPU search forms, a share of them, and prune as well.
+ * out_rows dev [rows] i64 (may be NULL): the sample index of every row; out_idx dev [rows, k], out_dist dev
+ * [rows, k] (may be NULL); rows = mpb_knn_part_rows(n_samples, dim, part, parts) (host arithmetic; -1 when the
+ * tensor-core scan does not serve the set: use mpb_knn_search on an index shard then).  The union of all parts'
+ * rows is the result of mpb_knn_search(samples, samples), bit for bit.  k <= 12.  Workspace as for
+ * mpb_knn_workspace_bytes(n_samples, n_samples, dim), prepared by mpb_knn_prepare. */
+int64_t mpb_knn_part_rows(int64_t n_samples, int dim, int part, int parts);
+int mpb_knn_search_part(const double *samples, int64_t n_samples, int dim, const double *weights, int k,
+                        double max_dist, void *workspace, size_t workspace_bytes, int part, int parts,
+                        int64_t *out_rows, int64_t *out_idx, double *out_dist, int64_t *stats, void *stream);
 
 /* Kernels launched so far by the mpb_knn_* entry points on the calling host thread (a monotone counter;
  * callers report differences).  No counterpart in the reference. */

@@ -35,6 +35,8 @@ SIGNATURES = {
     "mpb_edges_check": (c_int, [c_vp, c_vp, c_i64, c_vp, c_vp, c_i64, c_dbl, c_int, c_int, c_vp, c_vp, c_vp]),
     "mpb_edges_check_knn": (c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, c_int, c_i64, c_dbl, c_int, c_int, c_vp, c_vp,
                                     c_vp]),
+    "mpb_edges_check_knn_rows": (c_int, [c_vp, c_vp, c_i64, c_vp, c_vp, c_i64, c_int, c_dbl, c_int, c_int, c_vp, c_vp,
+                                         c_vp]),
     "mpb_edges_check_pairs": (c_int, [c_vp, c_vp, c_vp, c_i64, c_dbl, c_int, c_int, c_vp, c_vp, c_vp]),
     "mpb_edges_count": (c_int, [c_vp, c_vp, c_i64, c_int, c_dbl, c_vp, c_vp]),
     "mpb_edges_waypoints": (c_int, [c_vp, c_vp, c_i64, c_int, c_dbl, c_vp, c_vp, c_vp]),
@@ -52,6 +54,9 @@ SIGNATURES = {
     "mpb_knn_filter_kind": (c_int, [c_i64, c_int, c_int]),
     "mpb_knn_tc_key_error": (c_int, [c_vp, c_i64, c_vp, c_i64, c_int, c_hostf64, c_vp, c_sz, c_vp, c_vp]),
     "mpb_knn_launch_count": (c_int, []),
+    "mpb_knn_part_rows": (c_i64, [c_i64, c_int, c_int, c_int]),
+    "mpb_knn_search_part": (c_int, [c_vp, c_i64, c_int, c_hostf64, c_int, c_dbl, c_vp, c_sz, c_int, c_int, c_vp, c_vp,
+                                    c_vp, c_vp, c_vp]),
     "mpb_knn_sample_order": (c_int, [c_vp, c_sz, c_i64, c_int, c_vp, c_vp]),
     "mpb_knn_f64": (c_int, [c_vp, c_i64, c_vp, c_i64, c_int, c_hostf64, c_int, c_dbl, c_vp, c_vp, c_vp]),
     "mpb_knn_f64_metric": (c_int, [c_vp, c_i64, c_vp, c_i64, c_int, c_hostf64, c_int, c_int, c_dbl, c_vp, c_vp, c_vp]),

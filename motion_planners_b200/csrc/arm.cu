@@ -76,12 +76,13 @@ __global__ void __launch_bounds__(256)
     const ArmSmem S = arm_stage(A, sm);                 // ends with __syncthreads()
     const int lane = threadIdx.x & 31;
     const unsigned lt = (1u << lane) - 1u;
-    // this warp's contiguous share of the edges
+    // this warp's share of the edges: every `warps`-th chunk of kChunk consecutive edges.  (Contiguous shares were
+    // badly balanced when the rows come in spatial order: whole regions collide, whole regions are free.)
+    constexpr int64_t kChunk = 64;
     const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     const int64_t wid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int64_t per = (E + warps - 1) / warps;
-    int64_t cursor = wid * per;
-    const int64_t stop = cursor + per < E ? cursor + per : E;
+    int64_t chunk = wid;                                // this warp's current chunk
+    int64_t cursor = chunk * kChunk;                    // next edge of that chunk
 
     bool active = false;
     int64_t e = 0;
@@ -92,14 +93,20 @@ __global__ void __launch_bounds__(256)
         // ---- lanes without an edge take the next ones of the share
         const unsigned need = __ballot_sync(0xffffffffu, !active);
         if (need) {
+            int64_t stop = (chunk + 1) * kChunk < E ? (chunk + 1) * kChunk : E;
+            if (cursor >= stop && chunk * kChunk < E) {   // on to this warp's next chunk
+                chunk += warps;
+                cursor = chunk * kChunk;
+                stop = (chunk + 1) * kChunk < E ? (chunk + 1) * kChunk : E;
+            }
             const int64_t mine = cursor + __popc(need & lt);
-            cursor += __popc(need);
+            cursor = cursor + __popc(need) < stop ? cursor + __popc(need) : (cursor > stop ? cursor : stop);
             if (!active && mine < stop) {
                 e = mine;
                 int64_t ia = e, ib = e;
                 const double *pb = Bp;
                 if (!Bp) {
-                    ia = kk > 0 ? row_offset + e / kk : src[e];
+                    ia = kk > 0 ? (src ? src[e / kk] : row_offset + e / kk) : src[e];
                     ib = dst[e];
                     pb = Ap;
                 }
@@ -126,7 +133,7 @@ __global__ void __launch_bounds__(256)
                 }
             }
             if (__ballot_sync(0xffffffffu, active) == 0) {
-                if (cursor >= stop) break;
+                if (chunk * kChunk >= E) break;
                 continue;
             }
         }

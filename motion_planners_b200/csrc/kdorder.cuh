@@ -138,6 +138,18 @@ __global__ void kd_dim_order_kernel(KnnHeader *h, int D)
     }
 }
 
+__global__ void __launch_bounds__(256) kd_invert_kernel(const uint32_t *__restrict__ perm, int64_t n, int32_t *__restrict__ inv)
+{
+    const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < n) inv[perm[p]] = (int32_t)p;
+}
+
+__global__ void __launch_bounds__(256) kd_rows_kernel(const uint32_t *__restrict__ perm, int64_t pos0, int64_t rows, int64_t *__restrict__ out)
+{
+    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < rows) out[r] = (int64_t)perm[pos0 + r];
+}
+
 // keys of one level: (first leaf of the point's current cell) << 24 | leading bits of its centred coordinate
 template <int D>
 __global__ void __launch_bounds__(256)

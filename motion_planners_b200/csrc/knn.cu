@@ -138,6 +138,14 @@ __global__ void __launch_bounds__(256) knn_minmax_kernel(const double *__restric
 
 __global__ void knn_set_stat_kernel(int64_t *stats, int64_t v) { stats[0] = v; }
 
+// Where the answer of query q goes: row q, or -- when the queries are a slice of the samples' spatial order
+// (mpb_knn_search_part) -- the query's position in that order, counted from the slice's first position.
+struct RowMap {
+    const int32_t *inv;     // sample index -> position in the spatial order (NULL: row = q)
+    int64_t pos0;
+    __device__ __forceinline__ int64_t row(int64_t q) const { return inv ? (int64_t)inv[q] - pos0 : q; }
+};
+
 __global__ void knn_finalize_kernel(KnnHeader *h, int D)
 {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
@@ -202,7 +210,7 @@ template <int D>
 __global__ void __launch_bounds__(256)
     knn_exact_kernel(const double *__restrict__ x, int64_t N, const double *__restrict__ qs, int64_t M, Weights wt,
                      int metric, int k, double lim, const int *__restrict__ list, const int *__restrict__ list_count,
-                     const unsigned long long *__restrict__ visited, int64_t *__restrict__ out_idx, double *__restrict__ out_dist, int64_t *__restrict__ stats)
+                     const unsigned long long *__restrict__ visited, RowMap rows, int64_t *__restrict__ out_idx, double *__restrict__ out_dist, int64_t *__restrict__ stats)
 {
     const int lane = threadIdx.x & 31;
     const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -264,8 +272,9 @@ __global__ void __launch_bounds__(256)
         if (lane < k) {
             const bool kd = (metric == MPB_METRIC_KDTREE);
             const bool keep = (li >= 0) && (kd ? (lk < lim) : (lk <= lim));
-            out_idx[q * k + lane] = keep ? (int64_t)li : -1;
-            if (out_dist) out_dist[q * k + lane] = keep ? (kd ? __dsqrt_rn(lk) : lk) : INFINITY;
+            const int64_t r = rows.row(q);
+            out_idx[r * k + lane] = keep ? (int64_t)li : -1;
+            if (out_dist) out_dist[r * k + lane] = keep ? (kd ? __dsqrt_rn(lk) : lk) : INFINITY;
         }
     }
 }
@@ -651,7 +660,7 @@ inline KdPlan tc_sample_plan(int64_t N, int D) { return kd_plan(N, 2 * ((N + kTc
 inline KdPlan tc_query_plan(int64_t M, int D) { return kd_plan(M, (M + kTcQueries - 1) / kTcQueries, D, false); }
 
 struct WsLayout {
-    size_t packed_off, packed_bytes, tc_off, tc_bytes, slot_off, slot_bytes, box_off, box_bytes, perm_off, perm_bytes, fb_off,
+    size_t packed_off, packed_bytes, tc_off, tc_bytes, slot_off, slot_bytes, box_off, box_bytes, perm_off, perm_bytes, inv_off, inv_bytes, fb_off,
         fb_bytes, surv_off,
         surv_bytes, thr_off, thr_bytes, qord_off, qord_bytes, sort_off, sort_bytes, total;
     int64_t n_tiles, n_pad, tc_tiles, tc_slots;
@@ -682,7 +691,9 @@ WsLayout ws_layout(int64_t N, int64_t M, int D, bool allow_tc = true)
     L.box_bytes = up((size_t)16 * L.box_stride * sizeof(float));
     L.perm_off = L.box_off + L.box_bytes;
     L.perm_bytes = tc ? up((size_t)(N > 0 ? N : 1) * sizeof(uint32_t)) : 0;     // the samples' k-d leaf order, kept
-    L.fb_off = L.perm_off + L.perm_bytes;
+    L.inv_off = L.perm_off + L.perm_bytes;
+    L.inv_bytes = L.perm_bytes;                                                  // ... and its inverse
+    L.fb_off = L.inv_off + L.inv_bytes;
     L.fb_bytes = up(m * sizeof(int));
     // query slots: blocks of 128; the sample set as its own query set uses the tiles' own slots
     const int64_t own = (M == N) ? L.tc_tiles * kTcTile : 0;
@@ -722,14 +733,15 @@ int sm_count()
 template <int D>
 int launch_exact(const double *x, int64_t N, const double *qs, int64_t M, const Weights &wt, int metric, int k,
                  double lim, const int *list, const int *list_count, int64_t *out_idx, double *out_dist,
-                 int64_t *stats, cudaStream_t st, const unsigned long long *visited = nullptr)
+                 int64_t *stats, cudaStream_t st, const unsigned long long *visited = nullptr,
+                 RowMap rows = RowMap{nullptr, 0})
 {
     const int threads = 256;
     int64_t blocks = list ? (int64_t)sm_count() * 4 : (M * 32 + threads - 1) / threads;
     if (blocks > (int64_t)sm_count() * 32) blocks = (int64_t)sm_count() * 32;
     if (blocks < 1) blocks = 1;
     knn_exact_kernel<D><<<(unsigned)blocks, threads, 0, st>>>(x, N, qs, M, wt, metric, k, lim, list, list_count,
-                                                              visited, out_idx, out_dist, stats);
+                                                              visited, rows, out_idx, out_dist, stats);
     MPB_LAUNCH_CHECK();
     return MPB_OK;
 }
@@ -776,6 +788,9 @@ int launch_prepare(const double *x, int64_t N, const Weights &wt, void *ws, bool
             MPB_LAUNCH_CHECK();
             // the order outlives the sort scratch (mpb_knn_sample_order hands it to callers that shard by it)
             MPB_CUDA_CHECK(cudaMemcpyAsync(base + L.perm_off, perm, (size_t)N * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+            kd_invert_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(perm, N, reinterpret_cast<int32_t *>(base + L.inv_off));
+            MPB_LAUNCH_CHECK();
+            g_last_launches += 1;
             g_last_launches += 2;
         }
     }
@@ -811,7 +826,8 @@ int launch_filter(const double *x, int64_t N, const double *qs, int64_t M, const
 
 template <int D>
 int launch_search(const double *x, int64_t N, const double *qs, int64_t M, const Weights &wt, int k, double r2,
-                  void *ws, bool allow_tc, int64_t *out_idx, double *out_dist, int64_t *stats, cudaStream_t st)
+                  void *ws, bool allow_tc, int64_t *out_idx, double *out_dist, int64_t *stats, cudaStream_t st,
+                  int part = -1, int parts = 1, int64_t *out_rows = nullptr)
 {
 #ifndef MPB_KNN_Q
 #define MPB_KNN_Q 8
@@ -848,8 +864,29 @@ int launch_search(const double *x, int64_t N, const double *qs, int64_t M, const
             float *sthr = reinterpret_cast<float *>(base + L.thr_off);
             const int *qorder = slot_idx;                  // the sample set queried against itself: block = half tile
             int64_t blocks = 2 * L.tc_tiles;
+            int64_t own_block0 = 0;
+            RowMap rows = RowMap{nullptr, 0};
             const bool own = (qs == x && M == N);
-            if (!own) {
+            if (part >= 0) {
+                // the queries are the samples of leaves [leaf_begin, leaf_end) of the spatial order: the same blocks a
+                // whole-set search has, a share of them; answers go to rows counted from the slice's first position
+                const KdPlan plan = tc_sample_plan(N, D);
+                const int64_t leaf_begin = plan.leaves * part / parts, leaf_end = plan.leaves * (part + 1) / parts;
+                const int64_t pos0 = kd_leaf_start(leaf_begin, N, plan.leaves);
+                const int64_t n_rows = kd_leaf_start(leaf_end, N, plan.leaves) - pos0;
+                qorder = slot_idx + leaf_begin * kTcQueries;
+                blocks = leaf_end - leaf_begin;
+                own_block0 = leaf_begin;
+                rows = RowMap{reinterpret_cast<const int32_t *>(base + L.inv_off), pos0};
+                if (out_rows && n_rows > 0) {
+                    kd_rows_kernel<<<(unsigned)((n_rows + 255) / 256), 256, 0, st>>>(
+                        reinterpret_cast<const uint32_t *>(base + L.perm_off), pos0, n_rows, out_rows);
+                    MPB_LAUNCH_CHECK();
+                    g_last_launches += 1;
+                }
+                if (blocks == 0) return MPB_OK;
+            } else if (!own) {
+                own_block0 = -1;
                 // any other query set gets its own k-d order, one leaf of at most 128 queries per block
                 const KdPlan plan = tc_query_plan(M, D);
                 blocks = plan.leaves;
@@ -866,16 +903,16 @@ int launch_search(const double *x, int64_t N, const double *qs, int64_t M, const
             MPB_CUDA_CHECK(cudaFuncSetAttribute(knn_tc_kernel<D, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                 (int)TcSmem::BYTES));
             knn_tc_kernel<D, false><<<(unsigned)blocks, kTcThreads, TcSmem::BYTES, st>>>(
-                qs, qorder, wt, tiles, (int)L.tc_tiles, boxes, L.box_stride, h, surv, sthr, nullptr, nullptr, nullptr, own ? 1 : 0);
+                qs, qorder, wt, tiles, (int)L.tc_tiles, boxes, L.box_stride, h, surv, sthr, nullptr, nullptr, nullptr, own_block0);
             MPB_LAUNCH_CHECK();
             const int64_t n_slots = blocks * kTcQueries;
             const int64_t rthreads = n_slots * 32;
             knn_tc_rerank_kernel<D><<<(unsigned)((rthreads + 255) / 256), 256, 0, st>>>(
-                x, N, qs, M, wt, k, r2, h, qorder, n_slots, slot_idx, surv, sthr, fb, out_idx, out_dist);
+                x, N, qs, M, wt, k, r2, h, qorder, n_slots, slot_idx, surv, sthr, fb, rows, out_idx, out_dist);
             MPB_LAUNCH_CHECK();
             g_last_launches += 3;
             return launch_exact<D>(x, N, qs, M, wt, MPB_METRIC_KDTREE, k, r2, fb, &h->fb_count, out_idx, out_dist, stats,
-                                   st, &h->tiles_visited);
+                                   st, &h->tiles_visited, rows);
         }
     }
     // 16 survivors per query leave a comfortable certificate margin up to k = 12 (a PRM's k + 1 = 11) and
@@ -913,7 +950,7 @@ int launch_tc_diag(const double *x, int64_t N, const double *qs, int64_t M, cons
         knn_tc_kernel<D, true><<<(unsigned)blocks, kTcThreads, TcSmem::BYTES, st>>>(
             qs, qo, wt, reinterpret_cast<const unsigned char *>(base + L.tc_off), (int)L.tc_tiles,
             reinterpret_cast<const float *>(base + L.box_off), L.box_stride, h, nullptr, nullptr, x,
-            reinterpret_cast<const int *>(base + L.slot_off), out, 0);
+            reinterpret_cast<const int *>(base + L.slot_off), out, -1);
         MPB_LAUNCH_CHECK();
         return MPB_OK;
     } else {
@@ -937,9 +974,10 @@ int dispatch_prepare(int D, const double *x, int64_t N, const Weights &wt, void 
     return MPB_EINVAL;
 }
 int dispatch_search(int D, const double *x, int64_t N, const double *qs, int64_t M, const Weights &wt, int k, double r2,
-                    void *ws, bool allow_tc, int64_t *out_idx, double *out_dist, int64_t *stats, cudaStream_t st)
+                    void *ws, bool allow_tc, int64_t *out_idx, double *out_dist, int64_t *stats, cudaStream_t st,
+                    int part = -1, int parts = 1, int64_t *out_rows = nullptr)
 {
-#define CALL(DD) launch_search<DD>(x, N, qs, M, wt, k, r2, ws, allow_tc, out_idx, out_dist, stats, st)
+#define CALL(DD) launch_search<DD>(x, N, qs, M, wt, k, r2, ws, allow_tc, out_idx, out_dist, stats, st, part, parts, out_rows)
     MPB_DISPATCH_DIM(D, CALL)
 #undef CALL
     return MPB_EINVAL;
@@ -1042,6 +1080,33 @@ MPB_API int mpb_knn_tc_key_error(const double *samples, int64_t n_samples, const
     MPB_DISPATCH_DIM(dim, CALL)
 #undef CALL
     return MPB_EINVAL;
+}
+
+MPB_API int64_t mpb_knn_part_rows(int64_t n_samples, int dim, int part, int parts)
+{
+    if (dim < 1 || dim > kTcMaxDim || n_samples <= 0 || parts < 1 || part < 0 || part >= parts) return -1;
+    if (!use_tc(n_samples, dim)) return -1;
+    const KdPlan plan = tc_sample_plan(n_samples, dim);
+    const int64_t b = plan.leaves * part / parts, e = plan.leaves * (part + 1) / parts;
+    return kd_leaf_start(e, n_samples, plan.leaves) - kd_leaf_start(b, n_samples, plan.leaves);
+}
+
+MPB_API int mpb_knn_search_part(const double *samples, int64_t n_samples, int dim, const double *weights, int k,
+                                double max_dist, void *workspace, size_t workspace_bytes, int part, int parts,
+                                int64_t *out_rows, int64_t *out_idx, double *out_dist, int64_t *stats, void *stream)
+{
+    int rc = check_common("mpb_knn_search_part", samples, n_samples, samples, n_samples, dim, k, out_idx);
+    if (rc != MPB_OK) return rc;
+    MPB_REQUIRE(max_dist >= 0., "mpb_knn_search_part: max_dist must be >= 0");
+    MPB_REQUIRE(parts >= 1 && part >= 0 && part < parts, "mpb_knn_search_part: part %d of %d", part, parts);
+    MPB_REQUIRE(k <= kSmallListMaxK && mpb_knn_part_rows(n_samples, dim, part, parts) >= 0,
+                "mpb_knn_search_part: needs a set the tensor-core scan serves (mpb_knn_filter_kind) and k <= %d",
+                kSmallListMaxK);
+    rc = check_ws("mpb_knn_search_part", workspace, workspace_bytes, n_samples, n_samples, dim);
+    if (rc != MPB_OK) return rc;
+    return dispatch_search(dim, samples, n_samples, samples, n_samples, make_weights(weights, dim), k,
+                           max_dist * max_dist, workspace, true, out_idx, out_dist, stats, (cudaStream_t)stream, part,
+                           parts, out_rows);
 }
 
 MPB_API int mpb_knn_sample_order(const void *workspace, size_t workspace_bytes, int64_t n_samples, int dim,

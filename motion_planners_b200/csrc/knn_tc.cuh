@@ -382,7 +382,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
                   const unsigned char *__restrict__ tiles, int n_tiles, const float *__restrict__ tile_box,
                   int box_stride, const KnnHeader *__restrict__ h, int *__restrict__ surv_idx,
                   float *__restrict__ surv_thr, const double *__restrict__ x, const int *__restrict__ slot_idx,
-                  unsigned long long *__restrict__ diag, int own_blocks)
+                  unsigned long long *__restrict__ diag, int64_t own_block0)
 {
     extern __shared__ __align__(1024) unsigned char smem[];
     unsigned char *sA = smem + TcSmem::A_OFF;
@@ -494,11 +494,12 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     };
 
     // ---- round 0: the nearest tile alone (ties: lowest index); it gives every query of the block a first
-    // threshold.  own_blocks: the queries are the samples themselves, block b is one half of tile b / 2.
-    if (own_blocks) {
+    // threshold.  own_block0 >= 0: the queries are samples in their own leaf order, block b is leaf own_block0 + b,
+    // one half of tile (own_block0 + b) / 2.
+    if (own_block0 >= 0) {
         if (tid == 0) {
-            ctl->home = (int)(blockIdx.x >> 1);
-            list[0] = key_of(0.f, (int)(blockIdx.x >> 1));
+            ctl->home = (int)((own_block0 + blockIdx.x) >> 1);
+            list[0] = key_of(0.f, (int)((own_block0 + blockIdx.x) >> 1));
             ctl->list_n = 1;
         }
         __syncthreads();
@@ -1067,8 +1068,8 @@ __global__ void __launch_bounds__(256)
     knn_tc_rerank_kernel(const double *__restrict__ x, int64_t N, const double *__restrict__ qs, int64_t M, Weights wt,
                          int k, double r2, KnnHeader *__restrict__ h, const int *__restrict__ qorder, int64_t n_slots,
                          const int *__restrict__ slot_idx, const int *__restrict__ surv_idx,
-                         const float *__restrict__ surv_thr, int *__restrict__ fb_list, int64_t *__restrict__ out_idx,
-                         double *__restrict__ out_dist)
+                         const float *__restrict__ surv_thr, int *__restrict__ fb_list, RowMap rows,
+                         int64_t *__restrict__ out_idx, double *__restrict__ out_dist)
 {
     constexpr int NU = (kTcSurvivors + 31) / 32;   // survivors per lane
     const int lane = threadIdx.x & 31;
@@ -1150,17 +1151,18 @@ __global__ void __launch_bounds__(256)
         ok = (Sk < bound) || (r2 <= bound);
     }
     if (ok) {
+        const int64_t row = rows.row(q);
 #pragma unroll
         for (int u = 0; u < NU; ++u) {
             if (ci[u] >= 0 && rank[u] < k) {
                 const bool keep = S[u] < r2;
-                out_idx[q * k + rank[u]] = keep ? (int64_t)ci[u] : -1;
-                if (out_dist) out_dist[q * k + rank[u]] = keep ? __dsqrt_rn(S[u]) : INFINITY;
+                out_idx[row * k + rank[u]] = keep ? (int64_t)ci[u] : -1;
+                if (out_dist) out_dist[row * k + rank[u]] = keep ? __dsqrt_rn(S[u]) : INFINITY;
             }
         }
         if (lane < k && lane >= nvalid) {
-            out_idx[q * k + lane] = -1;
-            if (out_dist) out_dist[q * k + lane] = INFINITY;
+            out_idx[row * k + lane] = -1;
+            if (out_dist) out_dist[row * k + lane] = INFINITY;
         }
     } else if (lane == 0) {
         const int pos = atomicAdd(&h->fb_count, 1);

@@ -362,14 +362,15 @@ MPB_API int mpb_edges_check_pairs(const mpb_world *world, const double *q1, cons
 template <int D>
 __global__ void __launch_bounds__(128)
     edges_check_rows_kernel(WorldDev w, const double *__restrict__ X, const int64_t *__restrict__ nbr, int64_t M,
-                            int kk, int64_t row_offset, double step, int mode, int skip_last,
+                            int kk, int64_t row_offset, const int64_t *__restrict__ row_ids, double step, int mode,
+                            int skip_last,
                             int32_t *__restrict__ out_hit, int32_t *__restrict__ out_n)
 {
     extern __shared__ __align__(16) double sm[];
     const WorldSmem s = stage_world(w, sm);
     for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < M; r += (int64_t)gridDim.x * blockDim.x) {
         double a[D];
-        const double *pa = X + (row_offset + r) * D;
+        const double *pa = X + (row_ids ? row_ids[r] : row_offset + r) * D;
 #pragma unroll
         for (int d = 0; d < D; ++d) a[d] = pa[d];
         // bounding box of the row, inflated like the per-edge boxes of edges_check_kernel
@@ -472,7 +473,8 @@ __global__ void __launch_bounds__(128)
 
 template <int D>
 static int launch_edges_rows(const mpb_world *world, const double *X, const int64_t *nbr, int64_t M, int kk,
-                             int64_t row_offset, double step, int mode, int skip_last, int32_t *out_hit,
+                             int64_t row_offset, const int64_t *row_ids, double step, int mode, int skip_last,
+                             int32_t *out_hit,
                              int32_t *out_n, cudaStream_t st)
 {
     const size_t smem = world_smem_bytes(world->dev) + 16;
@@ -487,18 +489,18 @@ static int launch_edges_rows(const mpb_world *world, const double *X, const int6
     if (smem > 48 * 1024)
         MPB_CUDA_CHECK(cudaFuncSetAttribute(edges_check_rows_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                             (int)smem));
-    edges_check_rows_kernel<D><<<(unsigned)blocks, threads, smem, st>>>(world->dev, X, nbr, M, kk, row_offset, step,
+    edges_check_rows_kernel<D><<<(unsigned)blocks, threads, smem, st>>>(world->dev, X, nbr, M, kk, row_offset, row_ids, step,
                                                                         mode, skip_last, out_hit, out_n);
     MPB_LAUNCH_CHECK();
     return MPB_OK;
 }
 
-MPB_API int mpb_edges_check_knn(const mpb_world *world, const double *samples, int64_t n_samples, const int64_t *nbr,
-                                int64_t n_rows, int row_len, int64_t row_offset, double step, int mode, int skip_last,
-                                int32_t *out_hit, int32_t *out_n, void *stream)
+static int edges_knn_common(const mpb_world *world, const double *samples, int64_t n_samples, const int64_t *nbr,
+                            int64_t n_rows, int row_len, int64_t row_offset, const int64_t *row_ids, double step,
+                            int mode, int skip_last, int32_t *out_hit, int32_t *out_n, void *stream)
 {
     MPB_REQUIRE(world != nullptr, "mpb_edges_check_knn: world is NULL");
-    MPB_REQUIRE(n_rows >= 0 && row_len >= 1 && row_offset >= 0 && row_offset + n_rows <= n_samples,
+    MPB_REQUIRE(n_rows >= 0 && row_len >= 1 && row_offset >= 0 && (row_ids || row_offset + n_rows <= n_samples),
                 "mpb_edges_check_knn: rows [%lld, %lld) outside the %lld samples", (long long)row_offset,
                 (long long)(row_offset + n_rows), (long long)n_samples);
     MPB_REQUIRE(mode == MPB_EDGE_ANY || mode == MPB_EDGE_FIRST || mode == MPB_EDGE_LAST,
@@ -507,17 +509,34 @@ MPB_API int mpb_edges_check_knn(const mpb_world *world, const double *samples, i
     if (n_rows == 0) return MPB_OK;
     MPB_REQUIRE(samples && nbr && out_hit, "mpb_edges_check_knn: NULL buffer");
     if (world->arm)
-        return mpb_arm_edges_check_impl(world->arm, samples, nullptr, nullptr, nbr, row_len, row_offset,
+        return mpb_arm_edges_check_impl(world->arm, samples, nullptr, row_ids, nbr, row_len, row_offset,
                                         n_rows * (int64_t)row_len, step, mode, skip_last, out_hit, out_n,
                                         (cudaStream_t)stream);
     MPB_REQUIRE(world_smem_bytes(world->dev) + 16 <= kMaxWorldSmem,
                 "mpb_edges_check_knn: obstacle set (%zu bytes) exceeds the %zu-byte shared-memory budget",
                 world_smem_bytes(world->dev), kMaxWorldSmem);
     cudaStream_t st = (cudaStream_t)stream;
-#define CALL(DD) launch_edges_rows<DD>(world, samples, nbr, n_rows, row_len, row_offset, step, mode, skip_last, out_hit, out_n, st)
+#define CALL(DD) launch_edges_rows<DD>(world, samples, nbr, n_rows, row_len, row_offset, row_ids, step, mode, skip_last, out_hit, out_n, st)
     MPB_DISPATCH_DIM(world->dev.dim, CALL)
 #undef CALL
     return MPB_EINVAL;
+}
+
+MPB_API int mpb_edges_check_knn(const mpb_world *world, const double *samples, int64_t n_samples, const int64_t *nbr,
+                                int64_t n_rows, int row_len, int64_t row_offset, double step, int mode, int skip_last,
+                                int32_t *out_hit, int32_t *out_n, void *stream)
+{
+    return edges_knn_common(world, samples, n_samples, nbr, n_rows, row_len, row_offset, nullptr, step, mode, skip_last,
+                            out_hit, out_n, stream);
+}
+
+MPB_API int mpb_edges_check_knn_rows(const mpb_world *world, const double *samples, int64_t n_samples,
+                                     const int64_t *row_ids, const int64_t *nbr, int64_t n_rows, int row_len, double step,
+                                     int mode, int skip_last, int32_t *out_hit, int32_t *out_n, void *stream)
+{
+    MPB_REQUIRE(n_rows == 0 || row_ids, "mpb_edges_check_knn_rows: row_ids is NULL");
+    return edges_knn_common(world, samples, n_samples, nbr, n_rows, row_len, 0, row_ids, step, mode, skip_last, out_hit,
+                            out_n, stream);
 }
 
 // ------------------------------------------------------------------------------------------

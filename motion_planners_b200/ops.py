@@ -174,13 +174,23 @@ class ObstacleSet(object):
 
     # -- the same for the rows of a neighbour matrix (culling once per row)
     def edges_check_knn(self, samples, nbr, row_offset=0, mode=EDGE_ANY, skip_last=False, step=STEP_SIZE,
-                        want_counts=False):
+                        want_counts=False, row_ids=None):
         samples = _f64(samples, "samples", self.dim)
         if not (nbr.is_cuda and nbr.dtype == torch.int64 and nbr.dim() == 2 and nbr.is_contiguous()):
             raise TypeError("nbr must be a contiguous 2-D int64 CUDA tensor")
         M, kk = nbr.shape
         hit = torch.empty((M, kk), dtype=torch.int32, device=samples.device)
         cnt = torch.empty((M, kk), dtype=torch.int32, device=samples.device) if want_counts else None
+        if row_ids is not None:
+            # row r leaves sample row_ids[r] (rows of a spatially sharded roadmap)
+            row_ids = _i64(row_ids, "row_ids")
+            if row_ids.shape[0] != M:
+                raise ValueError("row_ids and nbr differ in length")
+            rc = _lib.lib().mpb_edges_check_knn_rows(self._h, _ptr(samples), samples.shape[0], _ptr(row_ids), _ptr(nbr), M,
+                                                     kk, float(step), int(mode), int(bool(skip_last)), _ptr(hit),
+                                                     _ptr(cnt), _stream())
+            _lib.check(rc, "mpb_edges_check_knn_rows")
+            return hit, cnt
         rc = _lib.lib().mpb_edges_check_knn(self._h, _ptr(samples), samples.shape[0], _ptr(nbr), M, kk,
                                             int(row_offset), float(step), int(mode), int(bool(skip_last)),
                                             _ptr(hit), _ptr(cnt), _stream())
@@ -292,6 +302,28 @@ class KnnIndex(object):
         rc = _lib.lib().mpb_knn_sample_order(ws, nbytes, self.n, self.dim, _ptr(out), _stream())
         _lib.check(rc, "mpb_knn_sample_order")
         return out.long()
+
+    def part_rows(self, part, parts):
+        """Rows of share `part` of `parts` of the set queried against itself (-1: the set has no spatial order)."""
+        return int(_lib.lib().mpb_knn_part_rows(self.n, self.dim, int(part), int(parts)))
+
+    def search_part(self, part, parts, k, max_dist=math.inf, stats=None):
+        """Share `part` of `parts` of the set's own kNN graph (mpb_knn_search_part): -> (row_ids [rows] int64 =
+        sample index per row, idx [rows, k], dist [rows, k]); the parts are slices of the spatial order."""
+        rows = self.part_rows(part, parts)
+        if rows < 0:
+            raise _lib.MpbError("this sample set has no spatial order (the tensor-core scan does not serve it)")
+        ws, nbytes = self.prepare(self.n)
+        dev = self.samples.device
+        row_ids = torch.empty(rows, dtype=torch.int64, device=dev)
+        idx = torch.empty((rows, k), dtype=torch.int64, device=dev)
+        dist = torch.empty((rows, k), dtype=torch.float64, device=dev)
+        _, wp = _host_weights(self.weights, self.dim)
+        rc = _lib.lib().mpb_knn_search_part(_ptr(self.samples), self.n, self.dim, wp, int(k), float(max_dist), ws, nbytes,
+                                            int(part), int(parts), _ptr(row_ids), _ptr(idx), _ptr(dist), _ptr(stats),
+                                            _stream())
+        _lib.check(rc, "mpb_knn_search_part")
+        return row_ids, idx, dist
 
     def search(self, queries, k, max_dist=math.inf, want_dist=True, stats=None, out_idx=None, out_dist=None):
         queries = _f64(queries, "queries", self.dim)

@@ -78,7 +78,7 @@ def gather_rows(local, group=None):
 
 
 class DeviceRoadmap(object):
-    ROWS_KERNEL_MIN = 300000     # rows from which the per-row edge kernel beats the per-edge one
+    ROWS_KERNEL_MIN = 50000      # rows from which the per-row edge kernel beats the per-edge one (measured: 0.47 vs 0.54 ms at 50k rows, 0.88 vs 1.26 at 125k, 5.5 vs 9.5 at 1M; tools/edges_ab.py)
 
     def __init__(self, world, k=10, weights=None, max_distance=math.inf, step=STEP_SIZE, group=None):
         self.world = world
@@ -131,26 +131,30 @@ class DeviceRoadmap(object):
         self._index._prepared = False
         _, ws_size, rank = self._dist()
         N = samples.shape[0]
-        spatial = ws_size > 1 and n_local < N and self.sharding != "index"
-        self._index.prepare(max(n_local, -(-N // ws_size)))
-        order = self._index.spatial_order() if spatial else None
-        if order is not None:
-            # this rank's rows: a contiguous slice of the spatial order (every rank computes the same order)
-            a, b = shard_bounds(N, ws_size, rank)
-            self.row_ids = order[a:b].contiguous()
-            n_local = self.n_local = b - a
+        spatial = ws_size > 1 and n_local < N and self.sharding != "index" and self.kk <= 12 \
+            and self._index.part_rows(rank, ws_size) >= 0
+        if getattr(self, "stats", None) is None:
+            self.stats = torch.zeros(2, dtype=torch.int64, device=samples.device)
+        if spatial:
+            # this rank's rows: a contiguous slice of the set's spatial order (every rank computes the same order), i.e.
+            # a share of the very query blocks a single-GPU build forms
+            self._index.prepare(N)
+            mark("packed")
+            self.row_ids, self.nbr_idx, self.nbr_dist = self._index.search_part(rank, ws_size, self.kk, self.max_distance,
+                                                                                stats=self.stats)
+            n_local = self.n_local = self.row_ids.shape[0]
             queries = samples.index_select(0, self.row_ids)
             self.offset = None
         else:
+            self._index.prepare(n_local)
+            mark("packed")
             self.row_ids = torch.arange(offset, offset + n_local, device=samples.device, dtype=torch.int64)
             queries = samples[offset:offset + n_local]
-        mark("packed")
-        if getattr(self, "nbr_idx", None) is None or self.nbr_idx.shape != (n_local, self.kk):
-            self.nbr_idx = torch.empty((n_local, self.kk), dtype=torch.int64, device=samples.device)
-            self.nbr_dist = torch.empty((n_local, self.kk), dtype=torch.float64, device=samples.device)
-            self.stats = torch.zeros(2, dtype=torch.int64, device=samples.device)
-        self._index.search(queries, self.kk, self.max_distance, stats=self.stats, out_idx=self.nbr_idx,
-                           out_dist=self.nbr_dist)
+            if getattr(self, "nbr_idx", None) is None or self.nbr_idx.shape != (n_local, self.kk):
+                self.nbr_idx = torch.empty((n_local, self.kk), dtype=torch.int64, device=samples.device)
+                self.nbr_dist = torch.empty((n_local, self.kk), dtype=torch.float64, device=samples.device)
+            self._index.search(queries, self.kk, self.max_distance, stats=self.stats, out_idx=self.nbr_idx,
+                               out_dist=self.nbr_dist)
         launches += _lib.lib().mpb_knn_launch_count() - count0
         mark("knn")
 
@@ -162,11 +166,9 @@ class DeviceRoadmap(object):
             # matrix is consumed in place with no compaction pass
             if self.offset is None:
                 # rows in spatial order: explicit source indices
-                src = self.row_ids.unsqueeze(1).expand(-1, self.kk).reshape(-1)
-                hit, _ = self.obstacles.edges_check(samples, src, self.nbr_idx.view(-1), mode=ops.EDGE_ANY,
-                                                    step=self.step, want_counts=False)
-                self.edge_hit = hit.view(n_local, self.kk)
-            elif n_local >= self.ROWS_KERNEL_MIN:
+                self.edge_hit, _ = self.obstacles.edges_check_knn(samples, self.nbr_idx, row_ids=self.row_ids,
+                                                                  mode=ops.EDGE_ANY, step=self.step)
+            elif n_local >= self.ROWS_KERNEL_MIN or hasattr(self.world, "model"):
                 # one thread per row: obstacles culled once per sample (1.7x faster at 1M rows, measured)
                 self.edge_hit, _ = self.obstacles.edges_check_knn(samples, self.nbr_idx, row_offset=offset,
                                                                   mode=ops.EDGE_ANY, step=self.step)
