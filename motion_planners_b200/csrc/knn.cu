@@ -569,7 +569,9 @@ __global__ void __launch_bounds__(kWarps * 32, kBlocksPerSM)
         const unsigned valid_all = __ballot_sync(FULL_MASK, ci >= 0);
         const int nvalid = __popc((valid_all >> ((SEG * seg) & 31)) & SEGMASK);
         const double T = (double)T32;
-        bool ok = isinf(T) && T > 0;   // list never filled: every sample is a survivor
+        // list never filled: every sample should be a survivor; fewer means a key was not comparable (overflow,
+        // NaN) and the query goes to the exact kernel
+        bool ok = isinf(T) && T > 0 && (int64_t)nvalid >= N;
         if (!ok) {
             // every sample outside the list has computed key >= T, hence exact squared
             // distance >= (sqrt(T - eta + |q|^2) - delta)^2  ("kNN certificate")

@@ -8,6 +8,8 @@ distance_fn and uses the exact kernel when that function is one of the accelerat
 The stored configurations stay Python objects in `.data` (lazy_prm looks start/goal up by identity).
 """
 import numpy as np
+
+from . import utils
 import torch
 
 from . import ops
@@ -132,6 +134,8 @@ class BruteForceNeighbors(NearestNeighbors):
             idx, dist = self.query_batch([x], k)
             return [(dist[0, j], int(idx[0, j]), self.data[int(idx[0, j])]) for j in range(idx.shape[1])
                     if idx[0, j] >= 0]
-        # arbitrary user metric: nothing to accelerate, scan it the way the reference does (nearest.py:102-109)
+        # arbitrary user metric: nothing to accelerate; only on request is it scanned on the host the way the
+        # reference does (nearest.py:102-109)
+        utils.require_device_primitives('BruteForceNeighbors.query_neighbors', getattr(self, 'allow_host', False))
         scored = [(self.distance_fn(x, x2), i, x2) for i, x2 in enumerate(self.data)]
         return sorted(scored, key=lambda t: t[0])[:k]

@@ -80,6 +80,41 @@ def require_plain_extend(extend_fn, who):
         raise NotImplementedError('%s: circular joints are supported by lazy_prm and the primitives only' % who)
 
 
+_HOST_DOT_CHECKED = False
+
+
+def check_host_rounding():
+    """The scalar distance_fn below evaluates the reference's own numpy expressions on the host, while the ranking
+    kernels restate them operation by operation: numpy's `dot` / `linalg.norm` go through BLAS, and on the host
+    the fixtures were made on that is a sequential chain of fused multiply-adds, s = fma(a_k, b_k, s).  That is a
+    property of the host's BLAS build.  Here it is checked once, exactly, on a fixed vector set, so that a host
+    whose `dot` rounds differently is reported instead of silently making the scalar and the batched form of the
+    same distance_fn disagree in the last bit.  Raises RuntimeError."""
+    global _HOST_DOT_CHECKED
+    if _HOST_DOT_CHECKED:
+        return
+    from fractions import Fraction
+    rs = np.random.RandomState(20261107)
+    for D in (2, 3, 7, 14):
+        for _ in range(8):
+            a = rs.uniform(0.5, 2.0, size=D)
+            b = rs.uniform(-1.0, 1.0, size=D)
+            sq = b * b
+            s = 0.0
+            for k in range(D):                                   # exactly rounded fused multiply-add chain
+                s = float(Fraction(a[k]) * Fraction(sq[k]) + Fraction(s))
+            t = 0.0
+            for k in range(D):
+                t = float(Fraction(b[k]) * Fraction(b[k]) + Fraction(t))
+            if float(np.dot(a, sq)) != s or float(np.linalg.norm(b, ord=2)) != float(np.sqrt(t)):
+                raise RuntimeError(
+                    "this host's numpy dot / linalg.norm do not round like a sequential fused multiply-add chain "
+                    "(BLAS build differs from the one the reference fixtures were generated with): the scalar "
+                    "distance_fn would disagree with the batched kernels in the last bit.  Use the batched forms "
+                    "(distance_fn.nearest, ops.knn) or rebuild the fixtures with oracle/make_golden.py on this host.")
+    _HOST_DOT_CHECKED = True
+
+
 class GpuDistanceFn(object):
     """distance_fn(q1, q2) -> float for the weighted Euclidean family, tagged with the reference
     rounding procedure it follows (`metric`) so that batched ranking kernels reproduce its values bit
@@ -91,6 +126,8 @@ class GpuDistanceFn(object):
         self.metric = int(metric)
 
     def __call__(self, q1, q2):
+        if self.metric != ops.METRIC_KDTREE:
+            check_host_rounding()                                   # once per process
         if self.metric == ops.METRIC_SAMPLERS:                      # samplers.py:13-15
             diff = np.array(q2) - np.array(q1)
             return np.sqrt(np.dot(self.weights, diff * diff))

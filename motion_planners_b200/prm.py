@@ -18,6 +18,8 @@ one distance scan (mpb_scan_nearest_radius) and its remaining candidates checked
 from heapq import heappop, heappush
 
 import numpy as np
+
+from . import utils
 import torch
 
 from . import ops
@@ -121,6 +123,7 @@ class DegreePRM(object):
         if self.target_degree == 0 or not new:
             return new
         if not self._accelerated():
+            utils.require_device_primitives('prm', getattr(self, 'allow_host', False))
             return self._grow_reference_order(new)
         fn = self.distance_fn
         table = as_config_array([v.q for v in self.order])

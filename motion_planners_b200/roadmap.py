@@ -241,6 +241,8 @@ class DeviceRoadmap(object):
             rounds += 8
             if int(changed.item()) == 0:
                 break
+        else:
+            raise RuntimeError('shortest_path: distances still changing after %d sweeps (max_rounds)' % max_rounds)
         self.sssp_sweeps = rounds
         if target is None or not bool(torch.isfinite(dist[int(target)]).item()):
             return dist, None

@@ -11,6 +11,8 @@ import random
 import time
 
 import numpy as np
+
+from . import utils
 import torch
 
 from . import ops
@@ -118,7 +120,7 @@ class _DeviceTree(object):
 
 
 def rrt(start, goal_sample, distance_fn, sample_fn, extend_fn, collision_fn, goal_test=_never,
-        goal_probability=.2, max_iterations=RRT_ITERATIONS, max_time=INF):
+        goal_probability=.2, max_iterations=RRT_ITERATIONS, max_time=INF, allow_host=False):
     """:return: path [q', ..., q"] or None (rrt.py:49-85)."""
     require_plain_extend(extend_fn, 'rrt')
     if not callable(goal_sample):
@@ -126,6 +128,7 @@ def rrt(start, goal_sample, distance_fn, sample_fn, extend_fn, collision_fn, goa
         goal_sample = lambda: g
     if not (isinstance(distance_fn, GpuDistanceFn) and isinstance(extend_fn, GpuExtendFn)
             and isinstance(collision_fn, GpuCollisionFn)):
+        utils.require_device_primitives('rrt', allow_host)
         return _rrt_reference_order(start, goal_sample, distance_fn, sample_fn, extend_fn, collision_fn, goal_test,
                                     goal_probability, max_iterations, max_time)
     start_time = time.time()

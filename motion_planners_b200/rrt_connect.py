@@ -23,6 +23,8 @@ import random
 import time
 
 import numpy as np
+
+from . import utils
 import torch
 
 from . import ops
@@ -270,6 +272,8 @@ def rrt_connect(start, goal, distance_fn, sample_fn, extend_fn, collision_fn, ma
     require_plain_extend(extend_fn, 'rrt_connect')
     tree_frequency = kwargs.get('tree_frequency', 1)
     if not _accelerated(distance_fn, extend_fn, collision_fn) or tree_frequency != 1:
+        utils.require_device_primitives('rrt_connect' if tree_frequency == 1 else 'rrt_connect(tree_frequency != 1)',
+                                        kwargs.get('allow_host', False))
         return _rrt_connect_reference_order(start, goal, distance_fn, sample_fn, extend_fn, collision_fn,
                                             max_iterations, max_time, tree_frequency)
     start_time = time.time()

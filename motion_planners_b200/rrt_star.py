@@ -17,6 +17,8 @@ import time
 from random import random
 
 import numpy as np
+
+from . import utils
 import torch
 
 from . import ops
@@ -189,11 +191,12 @@ class _StepState(object):
 
 
 def rrt_star(start, goal, distance_fn, sample_fn, extend_fn, collision_fn, radius, max_time=INF, max_iterations=INF,
-             goal_probability=.2, informed=True, verbose=False):
+             goal_probability=.2, informed=True, verbose=False, allow_host=False):
     """:return: path [q', ..., q"] or None (rrt_star.py:86-146)."""
     require_plain_extend(extend_fn, 'rrt_star')
     if not (isinstance(distance_fn, GpuDistanceFn) and isinstance(extend_fn, GpuExtendFn)
             and isinstance(collision_fn, GpuCollisionFn)):
+        utils.require_device_primitives('rrt_star', allow_host)
         return _rrt_star_reference_order(start, goal, distance_fn, sample_fn, extend_fn, collision_fn, radius,
                                          max_time, max_iterations, goal_probability, informed)
     start = np.asarray(start, dtype=np.float64)

@@ -71,3 +71,19 @@ def as_config_array(configs, dim=None):
         return np.zeros((0, dim or 0))
     arr = np.ascontiguousarray(np.array([np.asarray(c, dtype=np.float64) for c in configs], dtype=np.float64))
     return arr.reshape(len(configs), -1)
+
+
+ALLOW_HOST_PLANNERS = False
+
+
+def require_device_primitives(who, allow_host=False):
+    """The planners of this package run their nearest-neighbour and collision work on the GPU; that needs the
+    batched primitives of motion_planners_b200.primitives (GpuDistanceFn / GpuExtendFn / GpuCollisionFn).  Handed
+    anything else they refuse -- there is no silent CPU path -- unless the caller opts into the plain host loop
+    (the reference's own statement order, useful to cross-check a custom callable) with allow_host=True or by
+    setting motion_planners_b200.utils.ALLOW_HOST_PLANNERS = True."""
+    if allow_host or ALLOW_HOST_PLANNERS:
+        return
+    raise TypeError("%s: distance_fn / extend_fn / collision_fn must be the batched primitives of "
+                    "motion_planners_b200.primitives (there is no CPU fallback); pass allow_host=True to run the "
+                    "host loop on arbitrary callables" % who)

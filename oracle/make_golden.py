@@ -592,7 +592,38 @@ def gen_lazy_prm_star():
               **_world_arrays(world))
 
 
-GENERATORS = {"knn": gen_knn, "extend": gen_extend, "collide": gen_collide, "edges": gen_edges, "dist": gen_dist,
+# --------------------------------------------------------------------------- BruteForceNeighbors
+def gen_brute_force():
+    """nearest.py:89-109 BruteForceNeighbors.query_neighbors (full distance_fn scan, stable sort, first k) with the
+    reference's two distance functions, and lazy_prm.Roadmap(weights=None, distance_fn=...) .add_samples
+    (lazy_prm.py:115-116,148-160), which is the caller that reaches it."""
+    from motion_planners.lazy_prm import Roadmap
+    from motion_planners.nearest import BruteForceNeighbors
+    from motion_planners.primitives import get_distance_fn as prim
+    from motion_planners.tkinter.samplers import get_distance_fn as samp, get_extend_fn
+    for D, N, M, k, seed in [(2, 400, 60, 6, 41), (7, 500, 50, 11, 42)]:
+        rs = np.random.RandomState(seed)
+        X = rs.uniform(size=(N, D))
+        X[40:60] = X[10:30]                                   # exact duplicates: ties go to the lower index
+        Q = np.concatenate([X[: M // 2], rs.uniform(size=(M - M // 2, D))])
+        w = rs.uniform(0.5, 2.0, size=D)
+        out = dict(samples=X, queries=Q, weights=w, k=np.int64(k))
+        for name, fn in (("primitives", prim(w)), ("samplers", samp(w))):
+            nn = BruteForceNeighbors(fn)
+            list(nn.add_data(list(X)))
+            idx = np.full((M, k), -1, np.int64)
+            dist = np.full((M, k), np.inf)
+            for r, q in enumerate(Q):
+                for j, (d, i, _) in enumerate(nn.query_neighbors(q, k=k)):
+                    idx[r, j], dist[r, j] = i, d
+            out["idx_" + name], out["dist_" + name] = idx, dist
+        rm = Roadmap(get_extend_fn(), weights=None, distance_fn=samp(w), max_degree=k - 1)
+        rm.add_samples(list(X))
+        out["roadmap_edges"] = _edge_array(rm.edges)
+        _save("brute_force_d%d" % D, **out)
+
+
+GENERATORS = {"brute_force": gen_brute_force, "knn": gen_knn, "extend": gen_extend, "collide": gen_collide, "edges": gen_edges, "dist": gen_dist,
               "lazy_prm": gen_lazy_prm, "prm": gen_prm, "rrt_connect": gen_rrt_connect, "rrt_star": gen_rrt_star,
               "birrt": gen_birrt, "circular": gen_circular,
               "lazy_prm_circular": gen_lazy_prm_circular, "rrt": gen_rrt,

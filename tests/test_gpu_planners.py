@@ -398,6 +398,8 @@ def test_rrt_matches_reference_runs(mp, golden, name):
             np.random.seed(seed)
             sample_fn = mp.primitives.get_sample_fn(env, obstacles=[])
             kw = {} if goal_test is None else {"goal_test": goal_test}
+            if plain:
+                kw["allow_host"] = True       # plain callables run the host loop only on request
             prims = (lambda a, b: dist(a, b), sample_fn, lambda a, b: ext(a, b), lambda c: col(c)) if plain \
                 else (dist, sample_fn, ext, col)
             path = rrt(g["starts"][q], goal, prims[0], prims[1], prims[2], prims[3], goal_probability=.2,
@@ -434,3 +436,52 @@ def test_lazy_prm_star_matches_reference_run(mp, golden, name):
         cost_fn = mp.primitives.get_distance_fn(w, p_norm=2)
         cost = sum(cost_fn(a, b) for a, b in zip(arr[:-1], arr[1:]))
         assert abs(cost - float(g["cost"])) <= 1e-9 * float(g["cost"])
+
+
+# ------------------------------------------------------------------ BruteForceNeighbors / Roadmap(weights=None)
+@pytest.mark.parametrize("D", [2, 7])
+def test_brute_force_neighbors_match_reference_run(golden, D):
+    """nearest.py:89-109 through the drop-in class: BruteForceNeighbors.query_neighbors with both accelerated
+    distance functions, and lazy_prm.Roadmap(weights=None, distance_fn=...) (lazy_prm.py:115-116), against a run
+    of the unmodified reference (oracle/make_golden.py gen_brute_force)."""
+    from motion_planners_b200 import primitives
+    from motion_planners_b200.lazy_prm import Roadmap
+    from motion_planners_b200.nearest import BruteForceNeighbors
+    g = golden("brute_force_d%d" % D)
+    X, Q, w, k = g["samples"], g["queries"], g["weights"], int(g["k"])
+    for name, fn in (("primitives", primitives.get_distance_fn(w, p_norm=2)), ("samplers", primitives.get_distance_fn(w))):
+        nn = BruteForceNeighbors(fn)
+        handed = list(nn.add_data(list(X)))
+        assert [i for i, _ in handed] == list(range(len(X)))
+        for r in range(0, len(Q), 7):                                  # the per-query call of the reference API
+            got = nn.query_neighbors(Q[r], k=k)
+            assert [i for _, i, _ in got] == list(g["idx_" + name][r])
+            assert [d for d, _, _ in got] == list(g["dist_" + name][r])
+            assert all(x is nn.data[i] for _, i, x in got)
+        idx, dist = nn.query_batch(list(Q), k)
+        assert (idx == g["idx_" + name]).all() and (dist == g["dist_" + name]).all()
+    rm = Roadmap(primitives.get_extend_fn(), weights=None, distance_fn=primitives.get_distance_fn(w), max_degree=k - 1)
+    rm.add_samples(list(X))
+    edges = np.array(sorted(rm.edges), np.int64).reshape(-1, 2)
+    assert (edges == g["roadmap_edges"]).all()
+
+
+def test_planners_refuse_plain_callables_unless_asked():
+    """No silent CPU path: handed primitives that are not the batched ones, the planners raise; allow_host=True runs
+    the reference's statement order on the host (and finds the same path as with the batched primitives)."""
+    import random as pyrandom
+    from motion_planners_b200 import primitives, workloads
+    from motion_planners_b200.rrt_connect import rrt_connect
+    world, start, goal = workloads.problem1_world()
+    col, ext, dfn = primitives.GpuCollisionFn(world), primitives.get_extend_fn(), primitives.get_distance_fn(np.ones(2))
+    env, obstacles = world.shapes()
+    plain_col = lambda q: bool(col(q))
+    with pytest.raises(TypeError):
+        rrt_connect(start, goal, dfn, primitives.get_sample_fn(env), ext, plain_col, max_iterations=5)
+    paths = []
+    for c, kw in ((col, {}), (plain_col, {"allow_host": True})):
+        pyrandom.seed(3)
+        np.random.seed(3)
+        paths.append(rrt_connect(start, goal, dfn, primitives.get_sample_fn(env), ext, c, max_iterations=50, **kw))
+    assert paths[0] is not None and len(paths[0]) == len(paths[1])
+    assert all((np.asarray(a) == np.asarray(b)).all() for a, b in zip(*paths))

@@ -116,3 +116,15 @@ def test_circular_knn_matches_reference(golden, name):
     nr = g["idx_r"].shape[0]
     idx_r, dist_r = oracle.knn_circular(X, X[:nr], k, circ, w, max_dist=float(g["radius"]))
     assert (idx_r == g["idx_r"]).all() and (dist_r == g["dist_r"]).all()
+
+
+@pytest.mark.parametrize("D", [2, 7])
+def test_brute_force_neighbors_golden(golden, D):
+    """nearest.py:89-109 BruteForceNeighbors with both reference distance functions: the oracle's metric kNN
+    (stable on the index) returns the reference's neighbours and distances, duplicates included."""
+    g = golden("brute_force_d%d" % D)
+    X, Q, w, k = g["samples"], g["queries"], g["weights"], int(g["k"])
+    for name, mode in (("primitives", oracle.METRIC_PRIMITIVES), ("samplers", oracle.METRIC_SAMPLERS)):
+        idx, dist = oracle.knn_metric(X, Q, k, w, mode)
+        assert (idx == g["idx_" + name]).all()
+        assert (dist == g["dist_" + name]).all()

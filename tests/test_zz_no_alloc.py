@@ -30,6 +30,14 @@ def test_static_scratch_knn_equals_workspace_knn_on_consecutive_calls():
     stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
     nullw = ctypes.POINTER(ctypes.c_double)()
     capacity = 4 << 20
+    # the claim in this file's name, asked of the driver itself: free device memory before and after the calls
+    rt = ctypes.CDLL("libcudart.so.12")
+    free_b, total_b = ctypes.c_size_t(), ctypes.c_size_t()
+
+    def free_bytes():
+        torch.cuda.synchronize()
+        assert rt.cudaMemGetInfo(ctypes.byref(free_b), ctypes.byref(total_b)) == 0
+        return free_b.value
 
     for N, M, D, k, seed in [(60000, 20000, 6, 11, 0), (3000, 3000, 7, 11, 1), (60000, 20000, 6, 11, 0)]:
         rs = np.random.RandomState(seed)
@@ -51,9 +59,15 @@ def test_static_scratch_knn_equals_workspace_knn_on_consecutive_calls():
         idx_b = torch.full((M, k), -7, dtype=torch.int64, device="cuda")
         dist_b = torch.full((M, k), -7.0, dtype=torch.float64, device="cuda")
         stats = torch.full((2,), -1, dtype=torch.int64, device="cuda")
+        # one untimed call first: the first call on a device resolves the array's address (documented set-up step)
         rc = lib.mpb_knn_f32filter_static(_vp(xs), N, _vp(qs), M, D, nullw, k, float("inf"), _vp(idx_b), _vp(dist_b),
                                           _vp(stats), stream)
         assert rc == 0, lib.mpb_last_error()
+        before = free_bytes()
+        rc = lib.mpb_knn_f32filter_static(_vp(xs), N, _vp(qs), M, D, nullw, k, float("inf"), _vp(idx_b), _vp(dist_b),
+                                          _vp(stats), stream)
+        assert rc == 0, lib.mpb_last_error()
+        assert free_bytes() == before                 # the call took nothing from the device allocator
         torch.cuda.synchronize()
         assert torch.equal(idx_a, idx_b)            # bit-exact, like every other parity test here
         assert torch.equal(dist_a, dist_b)
