@@ -35,9 +35,12 @@ import numpy as np  # noqa: E402
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the kernel, from the committed `ncu --set full`
 # captures under profiles/ (1 GPU, the workload's full size); None = not captured
 NCU = {
-    "knn_tc_kernel": {"traffic": None, "tensor_pipe_active_pct": None, "source": None},
-    "arm_edges_kernel": {"traffic": None, "fp64_pipe_active_pct": None, "source": None},
-    "edges_check_rows_kernel": {"traffic": None, "fp64_pipe_active_pct": None, "source": None},
+    "knn_tc_kernel": {"traffic": 567.259136e6 + 67.038464e6, "tensor_pipe_active_pct": 23.03,
+                      "source": "profiles/r2_ncu_full_knn_tc_raw.csv (c4, 1M x 7-DoF, 1 GPU)"},
+    "arm_edges_kernel": {"traffic": 210.380544e6 + 40.558592e6, "fp64_pipe_active_pct": 34.60,
+                         "source": "profiles/r2_ncu_full_arm_edges_raw.csv (c4, 11M directed edges, 1 GPU)"},
+    "edges_check_rows_kernel": {"traffic": 219.491840e6 + 40.684288e6, "fp64_pipe_active_pct": 23.99,
+                                "source": "profiles/r2_ncu_full_edges_rows_raw.csv (c4lite, 11M directed edges, 1 GPU)"},
 }
 
 METRIC = "PRM edges collision-checked/sec (kNN k=10 + vertex + edge checks per roadmap build step)"
@@ -481,7 +484,7 @@ def main():
                 "executed_tflops": executed / (ms * 1e-3) / 1e12,
                 "frac_executed": executed / (ms * 1e-3) / 1e12 / tf32_peak,
                 "ncu_tensor_pipe_active_pct": NCU["knn_tc_kernel"]["tensor_pipe_active_pct"],
-                "traffic": NCU["knn_tc_kernel"]["traffic"] if (world_size == 1 and r is m) else None,
+                "traffic": NCU["knn_tc_kernel"]["traffic"] if (world_size == 1 and n == 1000000) else None,
                 "ncu_source": NCU["knn_tc_kernel"]["source"],
             })
         else:
@@ -533,7 +536,8 @@ def main():
                         "exit skipped that much work, not that the pipe ran faster than its peak",
                 "bytes_per_edge": bytes_edge, "hbm": {"achieved_gbs": gbs, "peak_gbs": hbm_peak, "frac": frac_hbm},
                 "binding": "fp64 pipe / latency (hbm fraction %.4f)" % (frac_hbm or 0.0),
-                "ncu_fp64_pipe_active_pct": ncu.get("fp64_pipe_active_pct"), "traffic": ncu.get("traffic") if world_size == 1 else None,
+                "ncu_fp64_pipe_active_pct": ncu.get("fp64_pipe_active_pct"),
+                "traffic": ncu.get("traffic") if (world_size == 1 and n == 1000000) else None,
                 "ncu_source": ncu.get("source")}
 
     roofline_knn = knn_roofline(m)
@@ -574,10 +578,17 @@ def main():
                       "C oracle under OpenMP); kd-tree build %.2f s untimed" % (r["hi"], n, r["n_edges"],
                                                                                 r["tree_build_s"]),
         }
-        p = cpu_baseline.python_port_step(m["world"], m["X"], 0, 40, k)
-        line["cpu_baseline"]["python_port"] = {
-            "value": p["n_edges"] / p["seconds"], "unit": UNIT, "cores": 1,
-            "sample": "first 40 queries, %d edges, per-call Python structure of the reference" % p["n_edges"]}
+        # the per-call Python path: the unmodified reference itself where its checkout is reachable (the build
+        # container), else the port of its per-call structure -- the line says which one ran
+        p = cpu_baseline.reference_step(m["world"], m["X"], 0, 40, k)
+        which = "unmodified reference (imported from its checkout)"
+        if p is None:
+            p = cpu_baseline.python_port_step(m["world"], m["X"], 0, 40, k)
+            which = "python port of the reference's per-call structure (reference checkout not reachable on this box)"
+        line["cpu_baseline"]["python_per_call"] = {
+            "value": p["n_edges"] / p["seconds"], "unit": UNIT, "cores": 1, "ran": which,
+            "sample": "first 40 queries, %d edges; kd-tree over all samples built inside the timed region "
+                      "(nearest.py:54-61 rebuilds it on every add_data)" % p["n_edges"]}
 
     if not args.no_extra:
         for other in [w_ for w_ in ("c4lite", "c2") if w_ != args.workload]:

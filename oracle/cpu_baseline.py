@@ -106,5 +106,46 @@ def python_port_step(world, X, q_lo, q_hi, k):
     return dict(seconds=t2 - t0, knn_s=t1 - t0, edges_s=t2 - t1, n_queries=q_hi - q_lo, n_edges=n_edges)
 
 
+def reference_step(world, X, q_lo, q_hi, k):
+    """The same slice of work through the UNMODIFIED reference's own functions, imported from the reference
+    checkout (oracle/ref_loader.py): KDNeighbors.add_data + query_neighbors per sample (nearest.py:36-85, as
+    lazy_prm.py:155-157 calls it), get_extend_fn (tkinter/samplers.py:113-127) and, for configuration-space
+    worlds, get_collision_fn (tkinter/samplers.py:88-98); for the arm world the reference has no collision_fn and
+    takes the user's callable (_py_collision_arm).  Single-threaded, like the reference.  Returns None when the
+    checkout is not reachable (the GPU box): callers then report the python_port figure and say so."""
+    from . import ref_loader
+    if not ref_loader.available():
+        return None
+    ref_loader.load()
+    from motion_planners.nearest import KDNeighbors
+    from motion_planners.primitives import get_embed_fn
+    from motion_planners.tkinter.samplers import get_collision_fn, get_extend_fn
+    from motion_planners.tkinter.viewer import Box, Circle
+    from motion_planners.utils import default_selector
+    t0 = time.perf_counter()
+    nearest = KDNeighbors(embed_fn=get_embed_fn(np.ones(X.shape[1])))
+    list(nearest.add_data(list(X)))
+    nbrs = []
+    for v in range(q_lo, q_hi):
+        nbrs.append([i for _, i, _ in nearest.query_neighbors(X[v], k=k + 1) if i != v])
+    t1 = time.perf_counter()
+    if hasattr(world, "model"):
+        col = lambda q: _py_collision_arm(world, q)
+    else:
+        env = Box(world.env_lo.copy(), world.env_hi.copy())
+        obs = [Box(lo.copy(), hi.copy()) for lo, hi in zip(world.box_lo, world.box_hi)]
+        obs += [Circle(c.copy(), float(r)) for c, r in zip(world.sph_c, world.sph_r)]
+        col = get_collision_fn(env, obs)
+    ext = get_extend_fn()
+    n_edges = 0
+    for v, row in zip(range(q_lo, q_hi), nbrs):
+        col(X[v])
+        for j in row:
+            any(col(q) for q in default_selector(list(ext(X[v], X[j]))))    # lazy_prm.py:189-195 check_edge
+            n_edges += 1
+    t2 = time.perf_counter()
+    return dict(seconds=t2 - t0, knn_s=t1 - t0, edges_s=t2 - t1, n_queries=q_hi - q_lo, n_edges=n_edges)
+
+
 def cores():
     return oracle.use_all_cores()
