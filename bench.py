@@ -266,6 +266,50 @@ def measure_rrt_star(iters=20000):
             "kernel_launches": int(getattr(rrt_star, "last_launches", 0))}
 
 
+def measure_lazy_prm_c2(num=100000, degree=10):
+    """configs[1] through the drop-in signature: lazy_prm(start, goal, ..., roadmap=Roadmap(max_degree=10),
+    num_samples=100k) on the 6-DoF world, wall clock, with the split between the roadmap's construction (batched
+    kNN on the device + the reference-shaped Python edge sets), the goal-rooted shortest-path pass (device) and
+    the lazy search / path checks."""
+    import random as pyrandom
+    import torch
+    from motion_planners_b200 import lazy_prm as lp, primitives, workloads
+    world = workloads.c2_world()
+    env, obstacles = world.shapes()
+    col, ext = primitives.GpuCollisionFn(world), primitives.get_extend_fn()
+    w = np.ones(world.dim)
+    pyrandom.seed(0)
+    np.random.seed(0)
+    cfree = primitives.get_sample_fn(env, obstacles=obstacles)
+    sample_fn = primitives.get_sample_fn(env, obstacles=[])
+    start, goal = cfree(), cfree()
+    col.batch(np.zeros((1, world.dim)))                      # CUDA context and library up before the clock starts
+    torch.cuda.synchronize()
+    ts = time.perf_counter()
+    drawn = lp.sample_until(sample_fn, num)                  # the reference's per-call sample_fn, on the host
+    t0 = time.perf_counter()
+    rm = lp.Roadmap(ext, weights=w, cost_fn=primitives.get_distance_fn(w, p_norm=2), max_degree=degree)
+    rm.add_samples([start, goal] + drawn)
+    torch.cuda.synchronize()
+    t1 = time.perf_counter()
+    h = rm.cost_to_go(rm.index(goal), rm.cost_fn)
+    torch.cuda.synchronize()
+    t2 = time.perf_counter()
+    sol = lp.lazy_prm(start, goal, sample_fn, ext, col, roadmap=rm, num_samples=num, weights=w, verbose=False)
+    torch.cuda.synchronize()
+    t3 = time.perf_counter()
+    return {"description": "configs[1]: lazy_prm(roadmap=Roadmap(max_degree=%d), num_samples=%d), 6-DoF, 64 boxes, through the "
+                           "drop-in signature" % (degree, num),
+            "seconds_total": t3 - ts, "sampling_host_s": t0 - ts, "roadmap_build_s": t1 - t0,
+            "roadmap_build_note": "batched kNN on the device (a few ms) + the reference-shaped Python edge set and adjacency "
+                                  "dictionaries of lazy_prm.Roadmap (about 0.6 M undirected edges inserted one by one in the "
+                                  "reference's order, which check_roadmap's iteration order depends on)",
+            "cost_to_go_device_s": t2 - t1,
+            "lazy_prm_call_s": t3 - t2, "cost_to_go_on_device": h is not None, "solved": sol.path is not None,
+            "path_points": 0 if sol.path is None else len(sol.path), "edges": len(rm.edges) // 2,
+            "vertices_checked": len(sol.colliding_vertices), "edges_checked": len(sol.colliding_edges) // 2}
+
+
 def measure_prm_c1(num=2000, degree=10):
     """configs[0], the reference's own CPU-runnable case: prm() on the 2-D demo fixture (3 boxes + 1 disc), 2000
     collision-free samples, target degree 10, seed 0 (the same draws as tests/golden/prm_problem1_s0.npz).  The
@@ -604,6 +648,7 @@ def main():
         if rank == 0:
             line["extra_c5_rrt_star"] = measure_rrt_star()
             line["extra_c1_prm"] = measure_prm_c1()
+            line["extra_c2_lazy_prm"] = measure_lazy_prm_c2()
 
     if rank == 0:
         print(json.dumps(line))

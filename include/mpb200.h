@@ -323,6 +323,14 @@ int mpb_rrt_star_step(const mpb_world *world, double *table, int64_t n_nodes, in
                       double step, double eps, void *workspace, size_t workspace_bytes,
                       void *out_record, size_t record_bytes, void *stream);
 
+/* Edge costs of a neighbour matrix under one of the reference's distance procedures: out_cost[r, j] =
+ * distance_fn(samples[row_offset + r], samples[nbr[r, j]]) with the rounding of `metric` (MPB_METRIC_*), +inf for
+ * a missing neighbour.  lazy_prm.py:216-222 Roadmap.get_cost evaluates cost_fn per edge on demand; the graph
+ * search below wants them all, bit for bit what cost_fn returns.  out_cost dev [n_rows, row_len] f64. */
+int mpb_edge_costs(const double *samples, int64_t n_samples, int dim, const double *weights, int metric,
+                   const int64_t *nbr, int64_t n_rows, int row_len, int64_t row_offset, double *out_cost,
+                   void *stream);
+
 /* ---- shortest paths over a device-resident roadmap ------------------------------------------
  * The graph search either side of check_path (lazy_prm.py:41-58 dijkstra, :70-98 wastar_search) for the
  * roadmap the entry points above produce: nbr / nbr_dist dev [n_rows, row_len] (kNN output; row r = sample

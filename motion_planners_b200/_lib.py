@@ -75,6 +75,7 @@ SIGNATURES = {
                                       c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "mpb_scan_nearest_radius": (c_int, [c_vp, c_i64, c_int, c_vp, c_hostf64, c_int, c_dbl, c_vp, c_vp, c_vp, c_vp,
                                         c_vp]),
+    "mpb_edge_costs": (c_int, [c_vp, c_i64, c_int, c_hostf64, c_int, c_vp, c_i64, c_int, c_i64, c_vp, c_vp]),
     "mpb_roadmap_relax": (c_int, [c_vp, c_vp, c_vp, c_vp, c_i64, c_int, c_i64, c_vp, c_vp, c_int, c_vp]),
     "mpb_roadmap_parents": (c_int, [c_vp, c_vp, c_vp, c_vp, c_i64, c_int, c_i64, c_vp, c_i64, c_vp, c_vp]),
     "mpb_peak_fma_f32": (c_int, [c_int, c_int, c_int, c_vp, c_vp]),

@@ -60,7 +60,55 @@ __global__ void __launch_bounds__(256)
     if (b < INFINITY && __dadd_rn(b, wt) == a && u != source) atomicMin(reinterpret_cast<unsigned long long *>(parent + u), (unsigned long long)v);
 }
 
+// cost of every listed edge under one of the reference's distance procedures (mpb_common.cuh metric_dist)
+template <int D>
+__global__ void __launch_bounds__(256)
+    edge_costs_kernel(const double *__restrict__ x, const int64_t *__restrict__ nbr, int64_t n_rows, int kk,
+                      int64_t row_offset, Weights wt, int metric, double *__restrict__ out)
+{
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n_rows * kk) return;
+    const int64_t u = row_offset + e / kk, v = nbr[e];
+    if (v < 0) {
+        out[e] = INFINITY;
+        return;
+    }
+    double a[D], b[D];
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+        a[d] = x[u * D + d];
+        b[d] = x[v * D + d];
+    }
+    out[e] = metric_dist<D>(a, b, wt, metric);
+}
+
+template <int D>
+int launch_edge_costs(const double *x, const int64_t *nbr, int64_t n_rows, int kk, int64_t row_offset, const Weights &wt,
+                      int metric, double *out, cudaStream_t st)
+{
+    const int64_t total = n_rows * kk;
+    edge_costs_kernel<D><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(x, nbr, n_rows, kk, row_offset, wt, metric, out);
+    MPB_LAUNCH_CHECK();
+    return MPB_OK;
+}
+
 }   // namespace
+
+MPB_API int mpb_edge_costs(const double *samples, int64_t n_samples, int dim, const double *weights, int metric,
+                           const int64_t *nbr, int64_t n_rows, int row_len, int64_t row_offset, double *out_cost,
+                           void *stream)
+{
+    MPB_REQUIRE(dim >= 1 && dim <= MPB_MAX_DIM, "mpb_edge_costs: dim %d outside [1, %d]", dim, MPB_MAX_DIM);
+    MPB_REQUIRE(metric >= 0 && metric <= 2, "mpb_edge_costs: bad metric %d", metric);
+    MPB_REQUIRE(n_rows >= 0 && row_len >= 1 && row_offset >= 0 && row_offset + n_rows <= n_samples, "mpb_edge_costs: bad rows");
+    if (n_rows == 0) return MPB_OK;
+    MPB_REQUIRE(samples && nbr && out_cost, "mpb_edge_costs: NULL buffer");
+    const Weights wt = make_weights(weights, dim);
+#define CALL(DD) launch_edge_costs<DD>(samples, nbr, n_rows, row_len, row_offset, wt, metric, out_cost, (cudaStream_t)stream)
+    MPB_DISPATCH_DIM(dim, CALL)
+#undef CALL
+    return MPB_EINVAL;
+}
 
 MPB_API int mpb_roadmap_relax(const int64_t *nbr, const double *nbr_dist, const int32_t *edge_hit,
                               const uint8_t *vertex_hit, int64_t n_rows, int row_len, int64_t row_offset,

@@ -131,6 +131,10 @@ class Roadmap(object):
         # mirrors the list for the opposite direction, and the mirrored list is NOT the opposite extension:
         # it starts at ~v1 and stops one step short of v2), recorded when a verdict is computed in batch
         self._path_dir = {}
+        # the neighbour rows every add_samples batch produced: [(first new vertex, idx int64 [n_new, k])] -- every
+        # edge of the roadmap is listed in the row of the vertex that asked for it, which is all the device search
+        # needs (it relaxes both directions of every listed edge)
+        self._knn_blocks = []
 
     # -- views (lazy_prm.py:127-140)
     @property
@@ -172,16 +176,71 @@ class Roadmap(object):
         if isinstance(self.nearest, GpuNeighbors):
             idx, _ = self.nearest.query_batch(queries, k, distance_upper_bound=self.max_distance)
             rows = [[int(j) for j in row if j >= 0] for row in idx]
+            first = new[0][0]
+            if [v for v, _ in new] == list(range(first, first + len(new))):
+                self._knn_blocks.append((first, np.ascontiguousarray(idx, dtype=np.int64)))
+            else:
+                self._knn_blocks = None
         elif k <= ops.MAX_K and getattr(self.nearest.distance_fn, 'metric', None) is not None:
             idx, _ = self.nearest.query_batch(queries, k)      # the brute-force index ignores max_distance
             rows = [[int(j) for j in row if j >= 0] for row in idx]
         else:
             rows = [[i for _, i, _ in self.nearest.query_neighbors(x, k=k)] for x in queries]
+        edges, out = self.edges, self.outgoing_from_vertex       # add_edge (lazy_prm.py:141-147), inlined
         for (v1, _), row in zip(new, rows):
             for v2 in row:
                 if v1 != v2:
-                    new_edges.update(self.add_edge(v1, v2))
+                    pair = {(v1, v2), (v2, v1)}
+                    edges.update(pair)
+                    out[v1].add(v2)
+                    out[v2].add(v1)
+                    new_edges.update(pair)
         return new_edges
+
+    # -- the goal-rooted shortest-path pass of lazy_prm (lazy_prm.py:295-296) on the device
+    DEVICE_SEARCH_MIN = 2048         # vertices from which cost_to_go runs on the GPU
+
+    def cost_to_go(self, goal_vertex, cost_fn):
+        """dijkstra(goal, neighbors_fn, get_cost) as an array: h[v] = cost of the cheapest path v -> goal over the
+        edges not known to collide (inf: unreachable), or None when this roadmap cannot be searched on the device
+        (then the caller runs the host search).  The values are the host search's bit for bit: both compute the
+        fixed point d[v] = min_u fl(d[u] + c(u, v)) from d[goal] = 0 with the same edge costs (mpb_edge_costs
+        evaluates cost_fn's own rounding procedure), and fl(a + c) is monotone in a."""
+        n = len(self.samples)
+        if (n < self.DEVICE_SEARCH_MIN or not self._knn_blocks or not isinstance(self.nearest, GpuNeighbors)
+                or getattr(cost_fn, 'metric', None) is None or self.colliding_vertices or self.colliding_edges
+                or getattr(self.nearest, 'circular', None)):
+            return None
+        if sum(idx.shape[0] for _, idx in self._knn_blocks) != n:
+            return None
+        import ctypes
+        from . import _lib
+        lib = _lib.lib()
+        dev = self.nearest.device_samples
+        D = dev.shape[1]
+        st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+        p = lambda t: ctypes.c_void_p(t.data_ptr())
+        w = np.ascontiguousarray(np.asarray(cost_fn.weights, dtype=np.float64))
+        wp = w.ctypes.data_as(ctypes.POINTER(ctypes.c_double))
+        blocks = []
+        for first, idx in self._knn_blocks:
+            nbr = torch.from_numpy(idx).cuda()
+            cost = torch.empty(nbr.shape, dtype=torch.float64, device='cuda')
+            _lib.check(lib.mpb_edge_costs(p(dev), n, D, wp, int(cost_fn.metric), p(nbr), nbr.shape[0], nbr.shape[1], first,
+                                          p(cost), st), 'mpb_edge_costs')
+            free = torch.full(nbr.shape, -1, dtype=torch.int32, device='cuda')     # nothing is known to collide yet
+            blocks.append((first, nbr, cost, free))
+        dist = torch.full((n,), float('inf'), dtype=torch.float64, device='cuda')
+        dist[int(goal_vertex)] = 0.0
+        changed = torch.zeros(1, dtype=torch.int32, device='cuda')
+        for _ in range(4096):
+            changed.zero_()
+            for first, nbr, cost, free in blocks:
+                _lib.check(lib.mpb_roadmap_relax(p(nbr), p(cost), p(free), None, nbr.shape[0], nbr.shape[1], first, p(dist),
+                                                 p(changed), 8, st), 'mpb_roadmap_relax')
+            if int(changed.item()) == 0:
+                return dist.cpu().numpy()
+        raise RuntimeError('cost_to_go: distances still changing after 32768 sweeps')
 
     # -- queries on the caches (lazy_prm.py:161-172)
     def is_colliding(self, v1, v2):
@@ -403,8 +462,12 @@ def lazy_prm(start, goal, sample_fn, extend_fn, collision_fn, distance_fn=None, 
     if meta:
         weight_fn = lambda v1, v2: ORDINAL * int(not roadmap.is_safe(v1, v2)) + roadmap.get_cost(v1, v2)
 
-    visited = dijkstra(end_vertex, roadmap.neighbors_fn, weight_fn)
-    heuristic_fn = lambda v: visited[v].g if v in visited else INF
+    to_go = None if meta else roadmap.cost_to_go(end_vertex, cost_fn)      # on the device where it can be
+    if to_go is not None:
+        heuristic_fn = lambda v: float(to_go[v])
+    else:
+        visited = dijkstra(end_vertex, roadmap.neighbors_fn, weight_fn)
+        heuristic_fn = lambda v: visited[v].g if v in visited else INF
     path = None
     while elapsed_time(start_time) < max_time and path is None:
         lazy_path = wastar_search(start_vertex, end_vertex, neighbors_fn=roadmap.neighbors_fn, cost_fn=weight_fn,

@@ -485,3 +485,39 @@ def test_planners_refuse_plain_callables_unless_asked():
         paths.append(rrt_connect(start, goal, dfn, primitives.get_sample_fn(env), ext, c, max_iterations=50, **kw))
     assert paths[0] is not None and len(paths[0]) == len(paths[1])
     assert all((np.asarray(a) == np.asarray(b)).all() for a, b in zip(*paths))
+
+
+def test_lazy_prm_device_cost_to_go_equals_host_dijkstra(mp):
+    """lazy_prm's goal-rooted shortest-path pass (lazy_prm.py:295-296) on the device: the heuristic array is the
+    host dijkstra's, bit for bit (same fixed point, same edge costs), and the planner returns the same Solution
+    whichever of the two ran."""
+    import random
+    from motion_planners_b200 import workloads
+    lp, pr = mp.lazy_prm, mp.primitives
+    world = workloads.c2_world()
+    env, obstacles = world.shapes()
+    col, ext = pr.GpuCollisionFn(world), pr.get_extend_fn()
+    D = world.dim
+    w = np.ones(D)
+    sols, heur = [], []
+    for device in (True, False):
+        random.seed(11)
+        np.random.seed(11)
+        cfree = pr.get_sample_fn(env, obstacles=obstacles)
+        sample_fn = pr.get_sample_fn(env, obstacles=[])
+        start, goal = cfree(), cfree()
+        rm = lp.Roadmap(ext, weights=w, cost_fn=pr.get_distance_fn(w, p_norm=2), max_degree=10)
+        rm.DEVICE_SEARCH_MIN = 2048 if device else 10 ** 9
+        rm.add_samples([start, goal] + lp.sample_until(sample_fn, 6000))
+        goal_v = rm.index(goal)
+        h = rm.cost_to_go(goal_v, rm.cost_fn)
+        assert (h is not None) == device
+        if device:
+            visited = lp.dijkstra(goal_v, rm.neighbors_fn, rm.get_cost)
+            ref = np.array([visited[v].g if v in visited else np.inf for v in rm.vertices])
+            assert (h == ref).all()
+        sols.append(lp.lazy_prm(start, goal, sample_fn, ext, col, roadmap=rm, num_samples=6000, weights=w, verbose=False))
+    a, b = sols
+    assert (a.path is None) == (b.path is None) and a.path is not None
+    assert len(a.path) == len(b.path) and all((np.asarray(x) == np.asarray(y)).all() for x, y in zip(a.path, b.path))
+    assert a.colliding_vertices == b.colliding_vertices and a.colliding_edges == b.colliding_edges
