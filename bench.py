@@ -186,7 +186,7 @@ def run_reference_arm(args, rank):
 
 
 # ------------------------------------------------------------------------------- batched RRT extra
-def measure_rrt_batch(world_size, rank, dist, total_queries=4096, iters=100):
+def measure_rrt_batch(world_size, rank, dist, total_queries=65536, iters=200):
     """configs[2]: a batch of independent 7-DoF RRT-Connect queries split over the ranks with no
     communication; every query consumes its own pre-drawn random streams."""
     import random as pyrandom
@@ -308,6 +308,42 @@ def measure_lazy_prm_c2(num=100000, degree=10):
             "lazy_prm_call_s": t3 - t2, "cost_to_go_on_device": h is not None, "solved": sol.path is not None,
             "path_points": 0 if sol.path is None else len(sol.path), "edges": len(rm.edges) // 2,
             "vertices_checked": len(sol.colliding_vertices), "edges_checked": len(sol.colliding_edges) // 2}
+
+
+def measure_smoothing_c5(n_paths=10000, iters=100, rrt_iters=100):
+    """configs[4]'s second half: linear-shortcut smoothing (smoothing.py:51-144) of 10k RRT-Connect paths in the
+    3-D world, max_iterations=100 each, every path on its own seeded generators (the result of path i equals a
+    seeded smooth_path call on it).  The device does the waypoint and collision batches, the host the per-path
+    draws and splices."""
+    import random as pyrandom
+    import torch
+    from motion_planners_b200 import primitives, workloads
+    from motion_planners_b200.rrt_connect import rrt_connect_batch
+    from motion_planners_b200.smoothing import smooth_paths_batch
+    world = workloads.c5_world()
+    D = world.dim
+    col, ext = primitives.GpuCollisionFn(world), primitives.get_extend_fn()
+    dfn = primitives.get_distance_fn(np.ones(D))
+    rs = np.random.RandomState(777)
+    pool = rs.uniform(size=(8 * n_paths, D))
+    free = pool[~col.batch(pool).cpu().numpy()]
+    starts, goals = free[:n_paths], free[n_paths:2 * n_paths]
+    u = rs.uniform(size=(n_paths, rrt_iters))
+    tg = rs.uniform(size=(n_paths, rrt_iters, D))
+    t0 = time.perf_counter()
+    paths = rrt_connect_batch(starts, goals, dfn, ext, col, u, tg)
+    torch.cuda.synchronize()
+    t1 = time.perf_counter()
+    solved = [p for p in paths if p is not None]
+    out = smooth_paths_batch(solved, ext, col, dfn, seeds=list(range(len(solved))), max_iterations=iters)
+    torch.cuda.synchronize()
+    t2 = time.perf_counter()
+    before = sum(len(p) for p in solved)
+    after = sum(len(p) for p in out)
+    return {"description": "configs[4]: %d 3-D rrt_connect paths (one launch), then smooth_path(max_iterations=%d) on each, "
+                           "in lock step" % (n_paths, iters),
+            "paths": len(solved), "rrt_connect_batch_s": t1 - t0, "smoothing_s": t2 - t1,
+            "paths_smoothed_per_s": len(solved) / (t2 - t1), "waypoints_before": before, "waypoints_after": after}
 
 
 def measure_prm_c1(num=2000, degree=10):
@@ -649,6 +685,7 @@ def main():
             line["extra_c5_rrt_star"] = measure_rrt_star()
             line["extra_c1_prm"] = measure_prm_c1()
             line["extra_c2_lazy_prm"] = measure_lazy_prm_c2()
+            line["extra_c5_smoothing"] = measure_smoothing_c5()
 
     if rank == 0:
         print(json.dumps(line))
