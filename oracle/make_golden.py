@@ -623,7 +623,82 @@ def gen_brute_force():
         _save("brute_force_d%d" % D, **out)
 
 
-GENERATORS = {"brute_force": gen_brute_force, "knn": gen_knn, "extend": gen_extend, "collide": gen_collide, "edges": gen_edges, "dist": gen_dist,
+# --------------------------------------------------------------------------- MultiRRT / MultiBiRRT
+def gen_multi_rrt():
+    """multi_rrt.py:71-159 under fixed seeds.  The reference keys its node table by configuration, so its own
+    numpy-yielding extend_fn cannot be used (unhashable); the runs go through tuple-yielding wrappers of the
+    reference's primitives, which is the form in which the unmodified planner works."""
+    from motion_planners.multi_rrt import MultiBiRRT, MultiRRT
+    from motion_planners.tkinter.samplers import get_collision_fn, get_distance_fn, get_extend_fn, get_sample_fn
+    for name in ("problem1", "mixed3d"):
+        world = WORLDS[name]()
+        env, obs = _ref_world(world)
+        D = world.dim
+        col_np = get_collision_fn(env, obs)
+        ext_np = get_extend_fn()
+        dist = get_distance_fn(np.ones(D))
+        col = lambda q: col_np(np.array(q))
+        ext = lambda a, b: (tuple(float(x) for x in q) for q in ext_np(np.array(a), np.array(b)))
+        dfn = lambda a, b: dist(np.array(a), np.array(b))
+        out = {}
+        for kind, cls in (("rrt", MultiRRT), ("birrt", MultiBiRRT)):
+            seed = 50 + (0 if kind == "rrt" else 1)
+            random.seed(seed)
+            np.random.seed(seed)
+            cfree = get_sample_fn(env, obstacles=obs, use_halton=False)
+            sample_np = get_sample_fn(env, obstacles=[], use_halton=False)
+            sample = lambda: tuple(float(x) for x in sample_np())
+            start = tuple(float(x) for x in cfree())
+            goals = [tuple(float(x) for x in cfree()) for _ in range(6)]
+            tree = cls(start, dfn, sample, ext, col)
+            paths, sizes = [], []
+            for g in goals:
+                if kind == "rrt":
+                    path = tree.grow((lambda gg=g: gg), iterations=40)
+                else:
+                    path = tree.grow(g, iterations=40)
+                paths.append(None if path is None else np.array([n.config for n in path]))
+                sizes.append(len(tree))
+            out[kind + "_seed"] = np.int64(seed)
+            out[kind + "_start"] = np.array(start)
+            out[kind + "_goals"] = np.array(goals)
+            out[kind + "_sizes"] = np.array(sizes, np.int64)
+            out[kind + "_solved"] = np.array([p is not None for p in paths])
+            for i, pth in enumerate(paths):
+                out["%s_path%d" % (kind, i)] = pth if pth is not None else np.zeros((0, D))
+        _save("multi_rrt_%s" % name, **out, **_world_arrays(world))
+
+
+# --------------------------------------------------------------------------- curve collision
+def gen_curve_collision():
+    """trajectory/smooth.py:32-50 get_curve_collision_fn: distance_discretize_curve samples of spline curves and
+    the verdict any(map(collision_fn, default_selector(samples)))."""
+    from scipy.interpolate import CubicSpline
+    from motion_planners.tkinter.samplers import get_collision_fn
+    from motion_planners.trajectory.discretize import distance_discretize_curve
+    from motion_planners.trajectory.smooth import get_curve_collision_fn
+    world = WORLDS["mixed3d"]()
+    env, obs = _ref_world(world)
+    col = get_collision_fn(env, obs)
+    fn = get_curve_collision_fn(col)
+    rs = np.random.RandomState(60)
+    knots, verdicts, samples, counts, windows = [], [], [], [], []
+    for c in range(40):
+        pts = rs.uniform(0.05, 0.95, size=(4, world.dim))
+        curve = CubicSpline(np.arange(4.0), pts)
+        t0, t1 = (None, None) if c % 3 else (0.5, 2.5)
+        _, smp = distance_discretize_curve(curve, start_t=t0, end_t=t1)
+        smp = np.array(smp)
+        knots.append(pts)
+        windows.append([np.nan if t0 is None else t0, np.nan if t1 is None else t1])
+        verdicts.append(bool(fn(curve, t0, t1)))
+        samples.append(smp)
+        counts.append(len(smp))
+    _save("curve_collision_mixed3d", knots=np.array(knots), windows=np.array(windows), verdicts=np.array(verdicts),
+          samples=np.concatenate(samples), counts=np.array(counts, np.int64), **_world_arrays(world))
+
+
+GENERATORS = {"multi_rrt": gen_multi_rrt, "curve_collision": gen_curve_collision, "brute_force": gen_brute_force, "knn": gen_knn, "extend": gen_extend, "collide": gen_collide, "edges": gen_edges, "dist": gen_dist,
               "lazy_prm": gen_lazy_prm, "prm": gen_prm, "rrt_connect": gen_rrt_connect, "rrt_star": gen_rrt_star,
               "birrt": gen_birrt, "circular": gen_circular,
               "lazy_prm_circular": gen_lazy_prm_circular, "rrt": gen_rrt,

@@ -521,3 +521,54 @@ def test_lazy_prm_device_cost_to_go_equals_host_dijkstra(mp):
     assert (a.path is None) == (b.path is None) and a.path is not None
     assert len(a.path) == len(b.path) and all((np.asarray(x) == np.asarray(y)).all() for x, y in zip(a.path, b.path))
     assert a.colliding_vertices == b.colliding_vertices and a.colliding_edges == b.colliding_edges
+
+
+# ------------------------------------------------------------------ MultiRRT / MultiBiRRT, curve collision
+@pytest.mark.parametrize("name", ["problem1", "mixed3d"])
+def test_multi_rrt_matches_reference_runs(mp, golden, name):
+    """multi_rrt.py:71-159: a tree grown towards six goals in turn, under the reference run's seeds: the same paths
+    (configurations as tuples, the form in which the reference's planner works) and the same tree sizes."""
+    import random
+    from motion_planners_b200.multi_rrt import MultiBiRRT, MultiRRT
+    g = golden("multi_rrt_" + name)
+    world = _world(mp, g)
+    dist, ext, col = _tree_primitives(mp, world)
+    env, obstacles = world.shapes()
+    for kind, cls in (("rrt", MultiRRT), ("birrt", MultiBiRRT)):
+        seed = int(g[kind + "_seed"])
+        random.seed(seed)
+        np.random.seed(seed)
+        cfree = mp.primitives.get_sample_fn(env, obstacles=obstacles)
+        sample_fn = mp.primitives.get_sample_fn(env, obstacles=[])
+        start = tuple(float(x) for x in cfree())
+        goals = [tuple(float(x) for x in cfree()) for _ in range(6)]
+        assert start == tuple(g[kind + "_start"]) and np.array_equal(np.array(goals), g[kind + "_goals"])
+        tree = cls(start, dist, sample_fn, ext, col)
+        for i, goal in enumerate(goals):
+            path = tree.grow((lambda gg=goal: gg), iterations=40) if kind == "rrt" else tree.grow(goal, iterations=40)
+            assert (path is not None) == bool(g[kind + "_solved"][i]), (kind, i)
+            if path is not None:
+                arr = np.array([n.config for n in path])
+                ref = g["%s_path%d" % (kind, i)]
+                assert arr.shape == ref.shape and (arr == ref).all(), (kind, i)
+            assert len(tree) == int(g[kind + "_sizes"][i]), (kind, i)
+        # the Mapping interface of multi_rrt.py:29-38 and the two-point query of :40-59
+        assert start in tree and tree[start].parent is None
+        assert tree(start) == [start]
+
+
+def test_curve_collision_fn_matches_reference(mp, golden):
+    """trajectory/smooth.py:32-50: verdicts of the reference's curve_collision_fn on 40 spline curves, from the
+    samples its distance_discretize_curve took (stored), one launch per curve and one launch for all."""
+    from motion_planners_b200.trajectory import get_curve_collision_fn
+    g = golden("curve_collision_mixed3d")
+    world = _world(mp, g)
+    col = mp.primitives.GpuCollisionFn(world)
+    off = np.concatenate([[0], np.cumsum(g["counts"])])
+    lists = [g["samples"][off[i]:off[i + 1]] for i in range(len(g["counts"]))]
+    served = iter(lists)
+    fn = get_curve_collision_fn(col, lambda curve, start_t=None, end_t=None: (None, next(served)))
+    got = [fn(object(), None, None) for _ in lists]
+    assert got == [bool(v) for v in g["verdicts"]]
+    assert fn.batch(lists) == got
+    assert fn(None) is True
