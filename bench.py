@@ -236,7 +236,7 @@ def measure_rrt_batch(world_size, rank, dist, total_queries=65536, iters=200):
             "kernel_launches": int(state.launches)}
 
 
-def measure_rrt_star(iters=20000):
+def measure_rrt_star(iters=200000):
     """configs[4] as a rate: RRT* in the 3-D world (32 boxes + 8 spheres, radius 0.1); every rank runs its
     own replica (the tree is sequential), so this is a per-GPU figure."""
     import random as pyrandom
@@ -263,6 +263,7 @@ def measure_rrt_star(iters=20000):
     return {"description": "configs[4]: rrt_star, 3-D, 32 boxes + 8 spheres, radius 0.1, %d iterations "
                            "(one tree per GPU: replicas only)" % iters,
             "seconds": sec, "iterations_per_s": iters / sec, "solved": path is not None,
+            "nodes": int(getattr(rrt_star, "last_nodes", 0)),
             "kernel_launches": int(getattr(rrt_star, "last_launches", 0))}
 
 

@@ -323,6 +323,37 @@ int mpb_rrt_star_step(const mpb_world *world, double *table, int64_t n_nodes, in
                       double step, double eps, void *workspace, size_t workspace_bytes,
                       void *out_record, size_t record_bytes, void *stream);
 
+/* ---- RRT*: many iterations per launch ----------------------------------------------------------
+ * rrt_star.py:100-137 as executed on Python 3 (see mpb_rrt_star_step), with the tree, the costs and the parent
+ * links resident on the device and the whole loop inside ONE cooperative kernel: per iteration the goal-biased
+ * sample from the caller's pre-drawn streams, the informed-set rejection, nearest node, safe extension, new node,
+ * goal test and the choose-parent pass.  The caller pre-draws what the reference would draw one by one:
+ * u_draws dev [n_u] f64 = consecutive random.random() values; sample_draws dev [n_s, dim] f64 =
+ * consecutive sample_fn() configurations.  The kernel consumes them in the reference's order (a random() only
+ * while no solution exists and not at iteration 0; a configuration only when the goal was not chosen) and stops
+ * when max_iterations iterations have been counted (status MPB_RRTSTAR_DONE), a stream runs dry
+ * (MPB_RRTSTAR_NEED_DRAWS: call again with reset = 0 and fresh arrays that continue the streams; positions
+ * consumed so far come back through mpb_rrt_star_run_read), or the node arrays are full (MPB_RRTSTAR_FULL: grow
+ * them, copy, call again).  Node i: table[i] (configuration), cost[i], parent[i] (-1 for the root), and the
+ * recipe of the waypoints strictly between parent and node: the first path_cnt[i] waypoints of
+ * extend_fn(table[parent[i]], path_to[i]).  All arrays dev, capacity rows; state dev, 256-byte aligned,
+ * mpb_rrt_star_run_state_bytes() bytes, owned by the caller for the life of the tree.  reset = 1 starts a new
+ * tree at `start` (HOST [dim]); goal HOST [dim].  Synchronises the stream when reset = 1. */
+#define MPB_RRTSTAR_RUNNING 0
+#define MPB_RRTSTAR_DONE 1
+#define MPB_RRTSTAR_NEED_DRAWS 2
+#define MPB_RRTSTAR_FULL 3
+#define MPB_RRTSTAR_CAND_OVERFLOW 4
+size_t mpb_rrt_star_run_state_bytes(void);
+int mpb_rrt_star_run(const mpb_world *world, const double *start, const double *goal, double radius,
+                     const double *weights, int metric, double step, double eps, double goal_probability,
+                     int informed, int64_t max_iterations, double *table, double *cost, int32_t *parent,
+                     double *path_to, int32_t *path_cnt, int64_t capacity, const double *u_draws, int64_t n_u,
+                     const double *sample_draws, int64_t n_s, void *state, int reset, void *stream);
+/* out6 HOST [6] i64 = {n_nodes, iterations counted, random() draws consumed, configurations consumed, index of the
+ * goal node or -1, status}; out_goal_cost HOST.  Synchronises the stream. */
+int mpb_rrt_star_run_read(const void *state, int64_t *out6, double *out_goal_cost, void *stream);
+
 /* Edge costs of a neighbour matrix under one of the reference's distance procedures: out_cost[r, j] =
  * distance_fn(samples[row_offset + r], samples[nbr[r, j]]) with the rounding of `metric` (MPB_METRIC_*), +inf for
  * a missing neighbour.  lazy_prm.py:216-222 Roadmap.get_cost evaluates cost_fn per edge on demand; the graph

@@ -9,7 +9,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "lib")
 OBJ_DIR = os.path.join(LIB_DIR, "obj")
 LIB = os.path.join(LIB_DIR, "libmpb200.so")
-SOURCES = ["world.cu", "knn.cu", "trees.cu", "rrt.cu", "graph.cu", "peaks.cu", "circular.cu", "rrtstar.cu", "arm.cu"]
+SOURCES = ["world.cu", "knn.cu", "trees.cu", "rrt.cu", "graph.cu", "peaks.cu", "circular.cu", "rrtstar.cu", "arm.cu", "rrtstar_run.cu"]
 
 # -fmad=false: nothing is contracted behind our back; every fused operation in the kernels is an
 # explicit __fma_rn / __fmaf_rn (the fp32 filter loop, the sphere test, the peak benchmarks).

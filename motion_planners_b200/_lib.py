@@ -51,6 +51,10 @@ SIGNATURES = {
     "mpb_rrt_star_record_bytes": (c_sz, [c_i64]),
     "mpb_rrt_star_step": (c_int, [c_vp, c_vp, c_i64, c_i64, c_hostf64, c_dbl, c_hostf64, c_int, c_dbl, c_dbl, c_vp,
                                   c_sz, c_vp, c_sz, c_vp]),
+    "mpb_rrt_star_run_state_bytes": (c_sz, []),
+    "mpb_rrt_star_run": (c_int, [c_vp, c_hostf64, c_hostf64, c_dbl, c_hostf64, c_int, c_dbl, c_dbl, c_dbl, c_int, c_i64,
+                                 c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_i64, c_vp, c_i64, c_vp, c_int, c_vp]),
+    "mpb_rrt_star_run_read": (c_int, [c_vp, ctypes.POINTER(ctypes.c_int64), ctypes.POINTER(ctypes.c_double), c_vp]),
     "mpb_knn_filter_kind": (c_int, [c_i64, c_int, c_int]),
     "mpb_knn_tc_key_error": (c_int, [c_vp, c_i64, c_vp, c_i64, c_int, c_hostf64, c_vp, c_sz, c_vp, c_vp]),
     "mpb_knn_launch_count": (c_int, []),

@@ -216,4 +216,13 @@ def get_sample_fn(region, obstacles=[], only_cfree=True, use_halton=False):
                 continue
             return q
 
+    # what a caller needs to draw the same stream in bulk (rrt_star's device loop): n calls of a plain box sampler
+    # = np.random.uniform(size=(n, D)) mapped by the same convex combination
+    sample_fn.lower, sample_fn.upper = lower, upper
+    sample_fn.plain_box = (collision_fn is None) and not degenerate
+
+    def bulk(n):
+        w = np.random.uniform(size=(int(n), len(lower)))
+        return (1 - w) * np.array(lower) + w * np.array(upper)
+    sample_fn.bulk = bulk
     return sample_fn

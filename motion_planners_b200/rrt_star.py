@@ -190,8 +190,104 @@ class _StepState(object):
         return head, self.cands[:n_cand]
 
 
+def _rrt_star_device_loop(start, goal, distance_fn, sample_fn, extend_fn, collision_fn, radius, max_time, max_iterations,
+                          goal_probability, informed):
+    """The whole loop of rrt_star.py:100-137 inside one cooperative kernel (mpb_rrt_star_run): the host only
+    pre-draws the two random streams in the reference's order (random() and the box sampler, in bulk), grows the
+    node arrays when they fill up, and retraces the path at the end.  The global generators are left exactly where
+    the reference's loop would have left them (the unconsumed part of the last bulk draw is given back)."""
+    import ctypes
+    import random as pyrandom
+    from . import _lib
+    lib = _lib.lib()
+    D = len(start)
+    dev = 'cuda'
+    hp = lambda a: a.ctypes.data_as(ctypes.POINTER(ctypes.c_double))
+    p = lambda t: ctypes.c_void_p(t.data_ptr())
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    cap = 1 << 14
+    if max_iterations < INF:
+        cap = max(cap, int(max_iterations) + 2)
+
+    def alloc(c):
+        return (torch.empty((c, D), dtype=torch.float64, device=dev), torch.empty(c, dtype=torch.float64, device=dev),
+                torch.empty(c, dtype=torch.int32, device=dev), torch.empty((c, D), dtype=torch.float64, device=dev),
+                torch.empty(c, dtype=torch.int32, device=dev))
+    table, cost, parent, path_to, path_cnt = alloc(cap)
+    nbytes = lib.mpb_rrt_star_run_state_bytes()
+    state_buf = torch.zeros(nbytes + 256, dtype=torch.uint8, device=dev)
+    state = ctypes.c_void_p(state_buf.data_ptr() + (-state_buf.data_ptr()) % 256)
+    w = np.ascontiguousarray(np.asarray(distance_fn.weights, dtype=np.float64))
+    s_host, g_host = np.ascontiguousarray(start), np.ascontiguousarray(goal)
+    saved_py, saved_np = pyrandom.getstate(), np.random.get_state()
+    used_u = used_s = 0
+    left_u, left_s = [], np.zeros((0, D))
+    chunk, done, reset, launches = 4096, 0, 1, 0
+    out6 = (ctypes.c_int64 * 6)()
+    goal_cost = ctypes.c_double()
+    start_time = time.time()
+    n_nodes, goal_idx = 1, -1
+    while done < max_iterations and elapsed_time(start_time) < max_time:
+        u = left_u + [pyrandom.random() for _ in range(max(0, chunk - len(left_u)))]
+        smp = np.concatenate([left_s, sample_fn.bulk(max(0, chunk - len(left_s)))]) if len(left_s) < chunk else left_s
+        u_dev = torch.tensor(u, dtype=torch.float64, device=dev)
+        s_dev = torch.from_numpy(np.ascontiguousarray(smp)).to(dev)
+        limit = int(min(max_iterations, done + 8 * chunk))
+        rc = lib.mpb_rrt_star_run(collision_fn.obstacles._h, hp(s_host), hp(g_host), float(radius), hp(w),
+                                  int(distance_fn.metric), float(extend_fn.step_size), EPSILON, float(goal_probability),
+                                  int(bool(informed)), limit, p(table), p(cost), p(parent), p(path_to), p(path_cnt), cap,
+                                  p(u_dev), len(u), p(s_dev), len(smp), state, reset, st)
+        _lib.check(rc, 'mpb_rrt_star_run')
+        _lib.check(lib.mpb_rrt_star_run_read(state, out6, ctypes.byref(goal_cost), st), 'mpb_rrt_star_run_read')
+        launches += 1
+        reset = 0
+        n_nodes, done, u_pos, s_pos, goal_idx, status = [int(v) for v in out6]
+        used_u += u_pos
+        used_s += s_pos
+        left_u, left_s = u[u_pos:], smp[s_pos:]
+        if status == 4:
+            raise _lib.MpbError('rrt_star: more candidate parents in one iteration than the device loop holds')
+        if status == 3:                                   # node arrays full: double them
+            new = alloc(2 * cap)
+            for old, big in zip((table, cost, parent, path_to, path_cnt), new):
+                big[:cap] = old
+            table, cost, parent, path_to, path_cnt = new
+            cap *= 2
+        elif status == 2:
+            chunk = min(2 * chunk, 1 << 17)
+    # give back what was drawn ahead: the generators end where the reference's loop would leave them
+    pyrandom.setstate(saved_py)
+    for _ in range(used_u):
+        pyrandom.random()
+    np.random.set_state(saved_np)
+    if used_s:
+        sample_fn.bulk(used_s)
+    rrt_star.last_launches = launches
+    rrt_star.last_iterations = done
+    rrt_star.last_nodes = n_nodes
+    if goal_idx < 0:
+        return None
+    par = parent[:n_nodes].cpu().numpy()
+    chain = [goal_idx]
+    while par[chain[-1]] >= 0:
+        chain.append(int(par[chain[-1]]))
+    chain = chain[::-1]
+    sel = torch.tensor(chain, dtype=torch.int64, device=dev)
+    cfg = table[sel].cpu().numpy()
+    to = path_to[sel].cpu().numpy()
+    cnt = path_cnt[sel].cpu().numpy()
+    out = [cfg[0]]
+    if len(chain) > 1:
+        offsets, way = extend_fn.batch(cfg[:-1], to[1:])  # extend_fn(parent config, recipe target), all nodes at once
+        offsets, way = offsets.cpu().numpy(), way.cpu().numpy()
+        for i in range(1, len(chain)):
+            out.extend(list(way[offsets[i - 1]:offsets[i - 1] + int(cnt[i])]))
+            out.append(cfg[i])
+    return out
+
+
 def rrt_star(start, goal, distance_fn, sample_fn, extend_fn, collision_fn, radius, max_time=INF, max_iterations=INF,
-             goal_probability=.2, informed=True, verbose=False, allow_host=False):
+             goal_probability=.2, informed=True, verbose=False, allow_host=False, device_loop=True):
     """:return: path [q', ..., q"] or None (rrt_star.py:86-146)."""
     require_plain_extend(extend_fn, 'rrt_star')
     if not (isinstance(distance_fn, GpuDistanceFn) and isinstance(extend_fn, GpuExtendFn)
@@ -204,6 +300,9 @@ def rrt_star(start, goal, distance_fn, sample_fn, extend_fn, collision_fn, radiu
     D = len(start)
     if bool(collision_fn.batch(np.stack([start, goal])).any().item()):
         return None
+    if device_loop and not verbose and getattr(sample_fn, 'plain_box', False) and (max_iterations < INF or max_time < INF):
+        return _rrt_star_device_loop(start, goal, distance_fn, sample_fn, extend_fn, collision_fn, radius, max_time,
+                                     max_iterations, goal_probability, informed)
     obs = collision_fn.obstacles
     step = extend_fn.step_size
     state = _StepState(obs, D, 4096)

@@ -572,3 +572,35 @@ def test_curve_collision_fn_matches_reference(mp, golden):
     assert got == [bool(v) for v in g["verdicts"]]
     assert fn.batch(lists) == got
     assert fn(None) is True
+
+
+def test_rrt_star_device_loop_equals_stepwise(mp):
+    """The persistent-kernel loop (mpb_rrt_star_run) against the one-iteration-per-call path (mpb_rrt_star_step) on a
+    longer run than the goldens: same path, same number of nodes, and the global generators left in the same state
+    (the bulk draws ahead of the kernel are given back)."""
+    import random
+    from motion_planners_b200 import workloads
+    from motion_planners_b200.rrt_star import rrt_star
+    world = workloads.c5_world()
+    dist, ext, col = _tree_primitives(mp, world)
+    env, obstacles = world.shapes()
+    random.seed(0)
+    np.random.seed(0)
+    cfree = mp.primitives.get_sample_fn(env, obstacles=obstacles)
+    while True:
+        s, g = cfree(), cfree()
+        if np.linalg.norm(s - g) > 0.8:
+            break
+    got = []
+    for device_loop in (True, False):
+        random.seed(5)
+        np.random.seed(5)
+        sample_fn = mp.primitives.get_sample_fn(env, obstacles=[])
+        path = rrt_star(s, g, dist, sample_fn, ext, col, radius=0.1, max_iterations=3000, device_loop=device_loop)
+        if device_loop:
+            assert rrt_star.last_launches < 50          # a handful of kernel launches, not four per iteration
+        got.append((path, random.random(), float(np.random.uniform())))
+    (pa, ra, na), (pb, rb, nb) = got
+    assert pa is not None and pb is not None and len(pa) == len(pb)
+    assert all((np.asarray(x) == np.asarray(y)).all() for x, y in zip(pa, pb))
+    assert ra == rb and na == nb
