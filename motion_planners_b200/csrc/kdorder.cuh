@@ -26,6 +26,7 @@ struct KdPlan {
     int levels;           // sorts
     int ways[kKdMaxLevels];   // level l cuts every cell ways[l] ways along coordinate dim_order[l]
     int leaf_bits;        // bits needed for a cell id
+    int coord_bits;       // leading bits of the order-preserving fp32 image kept in a key
 };
 
 inline int ceil_log2_i64(int64_t v)
@@ -90,6 +91,12 @@ inline KdPlan kd_plan(int64_t n, int64_t min_leaves, int D, bool even)
         }
     }
     p.leaf_bits = ceil_log2_i64(p.leaves);
+    // a key = (cell << coord_bits) | coordinate bits: with at most 32 significant bits a level takes four radix
+    // passes instead of five; 16 coordinate bits (sign, exponent, 7 mantissa bits) still order a cell's points well
+    // enough for a split into a handful of parts, and ties keep their previous order (the sort is stable)
+    p.coord_bits = 32 - p.leaf_bits;
+    if (p.coord_bits > kKdCoordBits) p.coord_bits = kKdCoordBits;
+    if (p.coord_bits < 16) p.coord_bits = 16;
     return p;
 }
 
@@ -150,7 +157,7 @@ __global__ void __launch_bounds__(256) kd_rows_kernel(const uint32_t *__restrict
     if (r < rows) out[r] = (int64_t)perm[pos0 + r];
 }
 
-// keys of one level: (first leaf of the point's current cell) << 24 | leading bits of its centred coordinate
+// keys of one level: (first leaf of the point's current cell) << coord_bits | leading bits of its centred coordinate
 template <int D>
 __global__ void __launch_bounds__(256)
     kd_key_kernel(const double *__restrict__ x, Weights wt, const KnnHeader *__restrict__ h, KdPlan p, int level,
@@ -168,7 +175,7 @@ __global__ void __launch_bounds__(256)
         if (dd == d) w = wt.w[dd];
     const float f = (float)d_sub(d_mul(w, x[(int64_t)j * D + d]), h->center[d]);
     const uint64_t cell = (uint64_t)kd_cell_start(p, kd_leaf_of(pos, p.n, p.leaves), level);
-    keys[pos] = (cell << kKdCoordBits) | (uint64_t)(ord_f32(f) >> (32 - kKdCoordBits));
+    keys[pos] = (cell << p.coord_bits) | (uint64_t)(ord_f32(f) >> (32 - p.coord_bits));
     vals[pos] = j;
 }
 
@@ -360,7 +367,7 @@ int kd_order(const double *x, int64_t n, const Weights &wt, const KnnHeader *h, 
         MPB_LAUNCH_CHECK();
         if (launches) *launches += 1;
         cur ^= 1;
-        const int bits = kKdCoordBits + (l == 0 ? 0 : plan.leaf_bits);
+        const int bits = plan.coord_bits + (l == 0 ? 0 : plan.leaf_bits);
         cur = rs_sort(s, cur, n, bits, st, launches);
         MPB_LAUNCH_CHECK();
     }
