@@ -49,6 +49,12 @@ constexpr int kTcQueries = 128;                // queries per CTA = MMA M = TMEM
 #ifndef MPB_TC_WAIT_HINT
 #define MPB_TC_WAIT_HINT 4000    // ns an epilogue warp may stay suspended inside one mbarrier.try_wait
 #endif
+#ifndef MPB_TC_MERGER_SLEEP
+#define MPB_TC_MERGER_SLEEP 0     // ns the threshold merger pauses between lane quarters
+#endif
+#ifndef MPB_TC_REFRESH_EVERY
+#define MPB_TC_REFRESH_EVERY 0    // 1: every epilogue thread re-reads its query's published threshold at every tile
+#endif
 #ifndef MPB_TC_BULK_MIN
 #define MPB_TC_BULK_MIN 5         // flagged lanes of a chunk from which the whole warp takes the sorting-network path
 #endif
@@ -887,6 +893,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
                     const float u = union16(qt);
                     float *dst = &sthr[qt * 32 + lane];
                     if (u < *(volatile float *)dst) *(volatile float *)dst = u;
+                    if (MPB_TC_MERGER_SLEEP) __nanosleep(MPB_TC_MERGER_SLEEP);
                 }
             }
         } else if (warp == kTcEpiWarps) {
@@ -966,6 +973,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
                 asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&tempty[b]);
+                if (MPB_TC_REFRESH_EVERY) thr = fminf(thr, *(volatile float *)&sthr[q]);
                 if constexpr (DIAG) {
                     measure(va, t * kTcTile + c0 * 32);
                     measure(vb, t * kTcTile + (c0 + 1) * 32);
