@@ -197,7 +197,10 @@ def get_sample_fn(region, obstacles=[], only_cfree=True, use_halton=False):
     lower = np.asarray(region.lower, dtype=np.float64)
     upper = np.asarray(region.upper, dtype=np.float64)
     collision_fn = get_collision_fn(region, obstacles) if (only_cfree and len(obstacles)) else None
-    env_only = get_collision_fn(region, []) if (only_cfree and not len(obstacles)) else None
+    # without obstacles the reference's rejection test is the closed environment test alone (samplers.py:92):
+    # two comparisons per coordinate, done here on the host instead of one kernel launch per drawn sample
+    env_only = (lambda q: not (np.less_equal(lower, q).all() and np.less_equal(q, upper).all())) \
+        if (only_cfree and not len(obstacles)) else None
     degenerate = bool(np.equal(lower, upper).all())
     state = {'used': False}
 
