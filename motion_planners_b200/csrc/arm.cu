@@ -7,8 +7,8 @@
 // waypoint recurrence of tkinter/samplers.py:113-127 in joint space.  The model itself (chain, spheres, the
 // fixed-polynomial sincos) is defined in oracle/arm_oracle.c, which this file follows operation for operation.
 //
-// One thread per directed edge (persistent grid); the workspace boxes, and a 16^3 grid that lists for every cell
-// the boxes a sphere centred there could touch, are staged in shared memory once per block.  The chain is walked
+// The workspace boxes are staged in shared memory once per block; a 32^3 grid over the workspace lists for every
+// cell the boxes a sphere centred there could touch (global memory, read through L1 / L2).  The chain is walked
 // joint by joint and the spheres of a joint are tested as soon as its frame is known, so a colliding waypoint
 // usually costs a fraction of the forward kinematics.
 #include <math.h>

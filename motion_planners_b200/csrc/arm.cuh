@@ -7,7 +7,16 @@
 
 constexpr int kArmMaxJoints = MPB_ARM_MAX_JOINTS;
 constexpr int kArmMaxSpheres = MPB_ARM_MAX_SPHERES;
-constexpr int kArmGrid = 16;                       // cells per workspace axis of the box grid
+#ifndef MPB_ARM_GRID
+#define MPB_ARM_GRID 32
+#endif
+#ifndef MPB_ARM_GRID_GLOBAL
+#define MPB_ARM_GRID_GLOBAL 1      // 1: the grid's lists stay in global memory (L1 / L2) instead of shared memory
+// measured on the 1M-sample build (tools/ab_arm.py), edge phase: 16^3 in shared memory 12.9 ms, 24^3 in shared memory
+// 11.7, 32^3 in global memory 10.7, 48^3 in global memory 10.8: shorter lists (0.9 boxes per cell against 1.55) matter
+// more than where the lists live
+#endif
+constexpr int kArmGrid = MPB_ARM_GRID;             // cells per workspace axis of the box grid
 
 // kernel-parameter view of an arm world (about 1.6 KB, read through the constant cache)
 struct ArmDev {
@@ -36,6 +45,7 @@ struct ArmSmem {
 inline size_t arm_smem_bytes(const ArmDev &A)
 {
     size_t b = (size_t)A.n_box * 3 * sizeof(double2);
+    if (MPB_ARM_GRID_GLOBAL) return b;
     b += ((size_t)(kArmGrid * kArmGrid * kArmGrid + 1) * sizeof(int) + 15) & ~(size_t)15;
     b += ((size_t)A.n_items * sizeof(unsigned short) + 15) & ~(size_t)15;
     return b;
@@ -48,6 +58,11 @@ __device__ __forceinline__ ArmSmem arm_stage(const ArmDev &A, unsigned char *sm)
     const size_t cs_bytes = ((size_t)(kArmGrid * kArmGrid * kArmGrid + 1) * sizeof(int) + 15) & ~(size_t)15;
     unsigned short *items = reinterpret_cast<unsigned short *>(reinterpret_cast<unsigned char *>(cs) + cs_bytes);
     for (int i = threadIdx.x; i < A.n_box * 3; i += blockDim.x) boxes[i] = make_double2(A.boxes[2 * i], A.boxes[2 * i + 1]);
+    if (MPB_ARM_GRID_GLOBAL) {
+        __syncthreads();
+        ArmSmem g = {boxes, A.cell_start, A.cell_items};
+        return g;
+    }
     for (int i = threadIdx.x; i <= kArmGrid * kArmGrid * kArmGrid; i += blockDim.x) cs[i] = A.cell_start[i];
     for (int i = threadIdx.x; i < A.n_items; i += blockDim.x) items[i] = A.cell_items[i];
     __syncthreads();
