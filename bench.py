@@ -37,11 +37,9 @@ import numpy as np  # noqa: E402
 NCU = {
     "knn_tc_kernel": {"traffic": 569.560064e6 + 68.432384e6, "tensor_pipe_active_pct": 23.03,
                       "source": "profiles/r2_ncu_full_knn_tc_raw.csv (c4, 1M x 7-DoF, 1 GPU)"},
-    # the arm's edge phase is two kernels: first waypoints of all edges (3.65 ms), then the survivors' walk (9.18 ms)
-    "arm_edges_first_kernel + arm_edges_rest_kernel": {
-        "traffic": 264.438784e6 + 56.862464e6 + 264.583424e6 + 34.416896e6, "fp64_pipe_active_pct": 47.8,
-        "source": "profiles/r2_ncu_full_arm_edges_first_raw.csv + r2_ncu_full_arm_edges_rest_raw.csv (c4, 11M directed "
-                  "edges, 1 GPU; fp64 pipe 51.9 % / 46.2 % active, time-weighted)"},
+    "arm_edges_refill_kernel": {
+        "traffic": None, "fp64_pipe_active_pct": None,
+        "source": "profiles/r2_ncu_full_arm_edges_refill_raw.csv (c4, 11M directed edges, 1 GPU)"},
     "edges_check_rows_kernel": {"traffic": 219.491840e6 + 40.684288e6, "fp64_pipe_active_pct": 23.99,
                                 "source": "profiles/r2_ncu_full_edges_rows_raw.csv (c4lite, 11M directed edges, 1 GPU)"},
 }
@@ -592,7 +590,7 @@ def main():
             S, B, J = world.n_sph, world.n_box, world.model.n_joints
             fk = 68 * J + 12 * S                                      # chain (sincos, frame turn, link) + sphere centres
             test_all = 17 * S * B                                     # clamp / subtract / fused square-add per axis + compare
-            kernel = "arm_edges_first_kernel + arm_edges_rest_kernel"
+            kernel = "arm_edges_refill_kernel"
             model = ("per waypoint: %d (recurrence) + %d (forward kinematics of %d joints, %d sphere centres) + %d "
                      "(%d spheres x %d boxes x 17, un-culled; the kernel tests only the boxes listed for the sphere's grid "
                      "cell and stops at the first hit)" % (3 * D, fk, J, S, test_all, S, B))

@@ -23,8 +23,12 @@
 struct mpb_arm_host {
     ArmDev dev;
     void *blob;
-    cudaMemPool_t pool;   // stream-ordered scratch of the two-pass edge walk; keeps its pages between calls
+    cudaMemPool_t pool;   // stream-ordered scratch (the edge walk's work cursor); keeps its pages between calls
 };
+
+#ifndef MPB_ARM_REFILL_CHUNK
+#define MPB_ARM_REFILL_CHUNK 128
+#endif
 
 namespace {
 
@@ -58,8 +62,8 @@ __global__ void __launch_bounds__(256) arm_fk_kernel(ArmDev A, const double *__r
 // Edges: explicit endpoints (Bp != NULL), index pairs (src/dst), or the rows of a neighbour matrix (kk > 0: edge e
 // runs from sample row_offset + e / kk to sample dst[e]).  Modes and skip_last as mpb_edges_check.
 //
-// (Used directly for mode LAST and small batches; modes ANY / FIRST on large batches go through
-// arm_edges_first_kernel + arm_edges_rest_kernel below, see launch_arm_edges.)
+// (Used for mode LAST and small batches; modes ANY / FIRST on large batches go through arm_edges_refill_kernel
+// below, see launch_arm_edges.)
 // Work is scheduled per LANE and per JOINT.  Edges differ wildly in cost -- most colliding ones end at their first
 // waypoints, often at the first joints, free ones walk ten waypoints of seven joints and sixteen spheres -- and
 // with one thread per edge 3.5 of a warp's 32 lanes were busy on average (ncu, profiles/r2_summary.md).  Here a
@@ -72,14 +76,10 @@ __global__ void __launch_bounds__(256)
     arm_edges_kernel(ArmDev A, const double *__restrict__ Ap, const double *__restrict__ Bp,
                      const int64_t *__restrict__ src, const int64_t *__restrict__ dst, int kk, int64_t row_offset,
                      int64_t E, double step, int mode, int skip_last, int32_t *__restrict__ out_hit,
-                     int32_t *__restrict__ out_n, const int32_t *__restrict__ list,
-                     const unsigned long long *__restrict__ list_count)
+                     int32_t *__restrict__ out_n)
 {
     extern __shared__ __align__(16) unsigned char sm[];
     __shared__ ArmTables T;
-    // list != NULL: the edges to walk are list[0 .. *list_count), each already found free at its first waypoint
-    // (arm_edges_first_kernel), so the walk starts at the second one
-    if (list) E = (int64_t)*list_count;
     arm_fill_tables(A, &T);
     const ArmSmem S = arm_stage(A, sm);                 // ends with __syncthreads()
     const int lane = threadIdx.x & 31;
@@ -110,7 +110,7 @@ __global__ void __launch_bounds__(256)
             const int64_t mine = cursor + __popc(need & lt);
             cursor = cursor + __popc(need) < stop ? cursor + __popc(need) : (cursor > stop ? cursor : stop);
             if (!active && mine < stop) {
-                e = list ? (int64_t)list[mine] : mine;
+                e = mine;
                 int64_t ia = e, ib = e;
                 const double *pb = Bp;
                 if (!Bp) {
@@ -132,10 +132,6 @@ __global__ void __launch_bounds__(256)
                     i = 0;
                     ji = 0;
                     best = -1;
-                    if (list) {
-                        waypoint_step<NJ>(q, b, n, 0);          // past the first waypoint
-                        i = 1;
-                    }
                     if (lim > i) {
                         active = true;
                     } else {
@@ -190,106 +186,93 @@ __global__ void __launch_bounds__(256)
     }
 }
 
-// First waypoint of every edge, one thread per edge: most colliding roadmap edges collide right there (their source
-// configuration does), and what is left for the walk above is a homogeneous set -- edges that are free at the
-// start, most of them free to the end -- on which its lanes stay busy.  Survivors are appended to `list`.
+// Modes ANY and FIRST on large batches: one thread per edge at a time, with lanes that refill.  A lane whose edge
+// has ended (collision, or its last waypoint) takes the next edge of its warp's share at once instead of idling
+// until the longest edge of the warp is done; a trip of the warp's loop is one waypoint for every lane (whole
+// chain, joints unrolled: the configuration stays in registers, unlike arm_edges_kernel's joint-granular trips).
+// Warps draw chunks of kChunk consecutive edges from a shared cursor (work_cursor, zero at launch); without one
+// (NULL) a warp's share is every `warps`-th chunk, which leaves a tail: 9.0 against 8.6 ms on the 1M-sample build,
+// whatever the chunk size from 32 to 256.
 template <int NJ>
 __global__ void __launch_bounds__(256)
-    arm_edges_first_kernel(ArmDev A, const double *__restrict__ Ap, const double *__restrict__ Bp,
-                           const int64_t *__restrict__ src, const int64_t *__restrict__ dst, int kk, int64_t row_offset,
-                           int64_t E, double step, int skip_last, int32_t *__restrict__ out_hit,
-                           int32_t *__restrict__ out_n, int32_t *__restrict__ list, unsigned long long *__restrict__ list_count)
+    arm_edges_refill_kernel(ArmDev A, const double *__restrict__ Ap, const double *__restrict__ Bp,
+                            const int64_t *__restrict__ src, const int64_t *__restrict__ dst, int kk, int64_t row_offset,
+                            int64_t E, double step, int skip_last, int32_t *__restrict__ out_hit,
+                            int32_t *__restrict__ out_n, unsigned long long *__restrict__ work_cursor)
 {
     extern __shared__ __align__(16) unsigned char sm[];
     const ArmSmem S = arm_stage(A, sm);
     const int lane = threadIdx.x & 31;
-    const int64_t total = ((E + 31) / 32) * 32;          // whole warps stay together for the vote
-    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
-        bool survivor = false;
-        if (e < E) {
-            int64_t ia = e, ib = e;
-            const double *pb = Bp;
-            if (!Bp) {
-                ia = kk > 0 ? (src ? src[e / kk] : row_offset + e / kk) : src[e];
-                ib = dst[e];
-                pb = Ap;
-            }
-            if (ia < 0 || ib < 0) {
-                out_hit[e] = -1;
-                if (out_n) out_n[e] = 0;
-            } else {
-                double q[NJ], b[NJ];
-#pragma unroll
-                for (int d = 0; d < NJ; ++d) {
-                    q[d] = Ap[ia * NJ + d];
-                    b[d] = pb[ib * NJ + d];
-                }
-                const int n = waypoint_count<NJ>(q, b, step);
-                const int lim = n - (skip_last ? 1 : 0);
-                if (out_n) out_n[e] = n;
-                if (lim <= 0) {
-                    out_hit[e] = -1;
+    const unsigned lt = (1u << lane) - 1u;
+    constexpr int64_t kChunk = MPB_ARM_REFILL_CHUNK;
+    const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    int64_t chunk = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    int64_t cursor = work_cursor ? 0 : chunk * kChunk;
+    int64_t stop = work_cursor ? 0 : (cursor + kChunk < E ? cursor + kChunk : E);
+    if (work_cursor && E == 0) return;
+    bool active = false;
+    int64_t e = 0;
+    double q[NJ], b[NJ];
+    int n = 0, lim = 0, i = 0;
+    for (;;) {
+        const unsigned need = __ballot_sync(0xffffffffu, !active);
+        if (need) {
+            if (cursor >= stop && cursor < E) {          // on to this warp's next chunk
+                if (work_cursor) {
+                    unsigned long long base = 0;
+                    if (lane == 0) base = atomicAdd(work_cursor, (unsigned long long)kChunk);
+                    base = __shfl_sync(0xffffffffu, base, 0);
+                    cursor = (int64_t)base < E ? (int64_t)base : E;
                 } else {
-                    waypoint_step<NJ>(q, b, n, 0);
-                    if (arm_collides<NJ>(A, S, q, nullptr)) {
-                        out_hit[e] = 0;
-                    } else if (lim == 1) {
-                        out_hit[e] = -1;
-                    } else {
-                        survivor = true;
+                    chunk += warps;
+                    cursor = chunk * kChunk < E ? chunk * kChunk : E;
+                }
+                stop = cursor + kChunk < E ? cursor + kChunk : E;
+            }
+            const int64_t mine = cursor + __popc(need & lt);
+            if (!active && mine < stop) {
+                e = mine;
+                int64_t ia = e, ib = e;
+                const double *pb = Bp;
+                if (!Bp) {
+                    ia = kk > 0 ? (src ? src[e / kk] : row_offset + e / kk) : src[e];
+                    ib = dst[e];
+                    pb = Ap;
+                }
+                if (ia < 0 || ib < 0) {
+                    out_hit[e] = -1;
+                    if (out_n) out_n[e] = 0;
+                } else {
+#pragma unroll
+                    for (int d = 0; d < NJ; ++d) {
+                        q[d] = Ap[ia * NJ + d];
+                        b[d] = pb[ib * NJ + d];
                     }
+                    n = waypoint_count<NJ>(q, b, step);
+                    lim = n - (skip_last ? 1 : 0);
+                    if (out_n) out_n[e] = n;
+                    i = 0;
+                    active = lim > 0;
+                    if (!active) out_hit[e] = -1;
                 }
             }
-        }
-        const unsigned m = __ballot_sync(0xffffffffu, survivor);
-        if (m) {
-            unsigned long long base = 0;
-            if (lane == __ffs(m) - 1) base = atomicAdd(list_count, (unsigned long long)__popc(m));
-            base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
-            if (survivor) list[base + __popc(m & ((1u << lane) - 1u))] = (int32_t)e;
-        }
-    }
-}
-
-// The survivors' walk, one thread per edge from the second waypoint on: the edges that reach it are free at their
-// start and mostly free to the end, so the threads of a warp do nearly the same work.
-template <int NJ>
-__global__ void __launch_bounds__(256)
-    arm_edges_rest_kernel(ArmDev A, const double *__restrict__ Ap, const double *__restrict__ Bp,
-                          const int64_t *__restrict__ src, const int64_t *__restrict__ dst, int kk, int64_t row_offset,
-                          double step, int skip_last, int32_t *__restrict__ out_hit, const int32_t *__restrict__ list,
-                          const unsigned long long *__restrict__ list_count)
-{
-    extern __shared__ __align__(16) unsigned char sm[];
-    const ArmSmem S = arm_stage(A, sm);
-    const int64_t n_list = (int64_t)*list_count;
-    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n_list; t += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t e = list[t];
-        int64_t ia = e, ib = e;
-        const double *pb = Bp;
-        if (!Bp) {
-            ia = kk > 0 ? (src ? src[e / kk] : row_offset + e / kk) : src[e];
-            ib = dst[e];
-            pb = Ap;
-        }
-        double q[NJ], b[NJ];
-#pragma unroll
-        for (int d = 0; d < NJ; ++d) {
-            q[d] = Ap[ia * NJ + d];
-            b[d] = pb[ib * NJ + d];
-        }
-        const int n = waypoint_count<NJ>(q, b, step);
-        const int lim = n - (skip_last ? 1 : 0);
-        waypoint_step<NJ>(q, b, n, 0);
-        int best = -1;
-        for (int i = 1; i < lim; ++i) {
-            waypoint_step<NJ>(q, b, n, i);
-            if (arm_collides<NJ>(A, S, q, nullptr)) {
-                best = i;
-                break;
+            cursor = cursor + __popc(need) < stop ? cursor + __popc(need) : stop;
+            if (__ballot_sync(0xffffffffu, active) == 0) {
+                if (cursor >= E) break;
+                continue;
             }
         }
-        out_hit[e] = best;
+        if (active) {
+            waypoint_step<NJ>(q, b, n, i);              // samplers.py:113-127: q is the running waypoint
+            const bool hit = arm_collides<NJ>(A, S, q, nullptr);
+            if (hit) {
+                out_hit[e] = i;
+                active = false;
+            } else if (++i >= lim) {
+                out_hit[e] = -1;
+                active = false;
+            }
+        }
     }
 }
 
@@ -350,48 +333,33 @@ int launch_arm_edges(const ArmDev &A, const double *Ap, const double *Bp, const 
     int64_t blocks = (E + 255) / 256;
     const int64_t cap = (int64_t)sm_count_arm() * per_sm;
     if (blocks > cap) blocks = cap;
-    // Modes ANY and FIRST with enough edges to matter: the first waypoints in one pass, the survivors' walk in
-    // another (the list of survivors is stream-ordered scratch from the world's own memory pool: no
-    // synchronisation, and the pool's release threshold keeps the pages mapped across synchronisations -- from the
-    // device's default pool every build after a stream synchronize paid 4 to 6 ms to map 40 MB again).
-    // Mode LAST has to look at every waypoint of every edge anyway.
-    if (mode != MPB_EDGE_LAST && E >= 65536 && E < 2147483647LL && pool != nullptr) {
+    // Edge phase of the 1M-sample build (10M edges, modes ANY / FIRST): the joint-granular kernel 21.2 ms; first
+    // waypoints in one pass and the survivors, one thread per edge, in another 10.7; the same with refilling lanes
+    // in the second pass 8.8; refilling lanes from the first waypoint on, in one pass, 8.6.  The work cursor is 256
+    // stream-ordered bytes from the world's own pool (its release threshold keeps them mapped: from the device's
+    // default pool, which gives its pages back at every synchronisation, the earlier 40 MB survivor list cost each
+    // build 4 to 6 ms); without it the kernel falls back to fixed shares.
+    // Mode LAST has to look at every waypoint of every edge, and small batches do not fill the refill kernel's grid.
+    if (mode != MPB_EDGE_LAST && E >= 65536) {
+        MPB_CUDA_CHECK(cudaFuncSetAttribute(arm_edges_refill_kernel<NJ>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)smem));
+        int per_sm2 = 1;
+        MPB_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm2, arm_edges_refill_kernel<NJ>, 256, smem));
         void *scratch = nullptr;
-        const size_t bytes = 256 + (size_t)E * sizeof(int32_t);
-        if (cudaMallocFromPoolAsync(&scratch, bytes, pool, st) == cudaSuccess) {
-            unsigned long long *count = reinterpret_cast<unsigned long long *>(scratch);
-            int32_t *list = reinterpret_cast<int32_t *>(reinterpret_cast<char *>(scratch) + 256);
-            MPB_CUDA_CHECK(cudaMemsetAsync(count, 0, sizeof(unsigned long long), st));
-            MPB_CUDA_CHECK(cudaFuncSetAttribute(arm_edges_first_kernel<NJ>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                (int)smem));
-            int per_sm1 = 1;
-            MPB_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm1, arm_edges_first_kernel<NJ>, 256, smem));
-            int64_t blocks1 = (E + 255) / 256;
-            const int64_t cap1 = (int64_t)sm_count_arm() * (per_sm1 < 1 ? 1 : per_sm1);
-            if (blocks1 > cap1) blocks1 = cap1;
-            arm_edges_first_kernel<NJ><<<(unsigned)blocks1, 256, smem, st>>>(A, Ap, Bp, src, dst, kk, row_offset, E, step,
-                                                                           skip_last, out_hit, out_n, list, count);
-            MPB_LAUNCH_CHECK();
-            // the walk of the survivors: one thread per edge (9.2 ms at 1M samples) beats the lane-scheduled kernel
-            // (14.5 ms) on this homogeneous set; MPB200_ARM_REST=0 selects the latter for comparison
-            static const int rest_mode = [] { const char *e = getenv("MPB200_ARM_REST"); return e ? atoi(e) : 1; }();
-            if (rest_mode == 1) {
-                MPB_CUDA_CHECK(cudaFuncSetAttribute(arm_edges_rest_kernel<NJ>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                    (int)smem));
-                arm_edges_rest_kernel<NJ><<<(unsigned)cap1, 256, smem, st>>>(A, Ap, Bp, src, dst, kk, row_offset, step,
-                                                                            skip_last, out_hit, list, count);
-            } else {
-                arm_edges_kernel<NJ><<<(unsigned)cap, 256, smem, st>>>(A, Ap, Bp, src, dst, kk, row_offset, E, step, mode,
-                                                                      skip_last, out_hit, out_n, list, count);
-            }
-            MPB_LAUNCH_CHECK();
-            MPB_CUDA_CHECK(cudaFreeAsync(scratch, st));
-            return MPB_OK;
+        if (!pool || cudaMallocFromPoolAsync(&scratch, 256, pool, st) != cudaSuccess) {
+            (void)cudaGetLastError();
+            scratch = nullptr;
         }
-        (void)cudaGetLastError();       // no pool memory: the single-pass walk needs none
+        if (scratch) MPB_CUDA_CHECK(cudaMemsetAsync(scratch, 0, sizeof(unsigned long long), st));
+        arm_edges_refill_kernel<NJ><<<(unsigned)(sm_count_arm() * (per_sm2 < 1 ? 1 : per_sm2)), 256, smem, st>>>(
+            A, Ap, Bp, src, dst, kk, row_offset, E, step, skip_last, out_hit, out_n,
+            reinterpret_cast<unsigned long long *>(scratch));
+        MPB_LAUNCH_CHECK();
+        if (scratch) MPB_CUDA_CHECK(cudaFreeAsync(scratch, st));
+        return MPB_OK;
     }
     arm_edges_kernel<NJ><<<(unsigned)blocks, 256, smem, st>>>(A, Ap, Bp, src, dst, kk, row_offset, E, step, mode,
-                                                             skip_last, out_hit, out_n, nullptr, nullptr);
+                                                             skip_last, out_hit, out_n);
     MPB_LAUNCH_CHECK();
     return MPB_OK;
 }
@@ -578,7 +546,7 @@ MPB_API int mpb_arm_world_create(const mpb_arm_model *m, const double *box_lo, c
     w->blob = nullptr;
     w->arm = arm;
     cudaGetDevice(&w->device);
-    // a pool of this world's own (without one, edge checks walk in a single pass)
+    // a pool of this world's own (without one the edge walk uses fixed shares)
     cudaMemPoolProps props;
     memset(&props, 0, sizeof(props));
     props.allocType = cudaMemAllocationTypePinned;
