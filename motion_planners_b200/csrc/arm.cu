@@ -29,6 +29,15 @@ struct mpb_arm_host {
 #ifndef MPB_ARM_REFILL_CHUNK
 #define MPB_ARM_REFILL_CHUNK 128
 #endif
+// block shape of the refill kernel, measured on the 1M-sample build (edge phase): 256 threads, 2 blocks per SM (95
+// registers) 8.5 ms; 128 x 5 (93 registers, 20 warps per SM) 7.7; 256 x 3 (80 registers, 16 B spilled) 7.7; 128 x 8
+// (64 registers, 88 B spilled) 7.7; 64 x 12 8.1 -- the kernel waits on fp64 latency, more warps hide more of it
+#ifndef MPB_ARM_REFILL_THREADS
+#define MPB_ARM_REFILL_THREADS 128
+#endif
+#ifndef MPB_ARM_REFILL_MINB
+#define MPB_ARM_REFILL_MINB 5
+#endif
 
 namespace {
 
@@ -194,7 +203,7 @@ __global__ void __launch_bounds__(256)
 // (NULL) a warp's share is every `warps`-th chunk, which leaves a tail: 9.0 against 8.6 ms on the 1M-sample build,
 // whatever the chunk size from 32 to 256.
 template <int NJ>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(MPB_ARM_REFILL_THREADS, MPB_ARM_REFILL_MINB)
     arm_edges_refill_kernel(ArmDev A, const double *__restrict__ Ap, const double *__restrict__ Bp,
                             const int64_t *__restrict__ src, const int64_t *__restrict__ dst, int kk, int64_t row_offset,
                             int64_t E, double step, int skip_last, int32_t *__restrict__ out_hit,
@@ -344,14 +353,15 @@ int launch_arm_edges(const ArmDev &A, const double *Ap, const double *Bp, const 
         MPB_CUDA_CHECK(cudaFuncSetAttribute(arm_edges_refill_kernel<NJ>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                             (int)smem));
         int per_sm2 = 1;
-        MPB_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm2, arm_edges_refill_kernel<NJ>, 256, smem));
+        MPB_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm2, arm_edges_refill_kernel<NJ>,
+                                                                     MPB_ARM_REFILL_THREADS, smem));
         void *scratch = nullptr;
         if (!pool || cudaMallocFromPoolAsync(&scratch, 256, pool, st) != cudaSuccess) {
             (void)cudaGetLastError();
             scratch = nullptr;
         }
         if (scratch) MPB_CUDA_CHECK(cudaMemsetAsync(scratch, 0, sizeof(unsigned long long), st));
-        arm_edges_refill_kernel<NJ><<<(unsigned)(sm_count_arm() * (per_sm2 < 1 ? 1 : per_sm2)), 256, smem, st>>>(
+        arm_edges_refill_kernel<NJ><<<(unsigned)(sm_count_arm() * (per_sm2 < 1 ? 1 : per_sm2)), MPB_ARM_REFILL_THREADS, smem, st>>>(
             A, Ap, Bp, src, dst, kk, row_offset, E, step, skip_last, out_hit, out_n,
             reinterpret_cast<unsigned long long *>(scratch));
         MPB_LAUNCH_CHECK();

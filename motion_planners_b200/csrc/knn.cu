@@ -122,6 +122,9 @@ __global__ void __launch_bounds__(256) knn_minmax_kernel(const double *__restric
             hi[d] = fmax(hi[d], e);
         }
     }
+    // warp, then block, then one atomic per block and bound (one per warp had 130k atomics queue on 14 addresses:
+    // 100 us of a 1.2 ms prepare)
+    __shared__ double s_lo[8][D], s_hi[8][D];
 #pragma unroll
     for (int d = 0; d < D; ++d) {
 #pragma unroll
@@ -130,9 +133,20 @@ __global__ void __launch_bounds__(256) knn_minmax_kernel(const double *__restric
             hi[d] = fmax(hi[d], __shfl_xor_sync(FULL_MASK, hi[d], o));
         }
         if ((threadIdx.x & 31) == 0) {
-            atomicMin(&h->mm[d], enc_f64(lo[d]));
-            atomicMax(&h->mm[MPB_MAX_DIM + d], enc_f64(hi[d]));
+            s_lo[threadIdx.x >> 5][d] = lo[d];
+            s_hi[threadIdx.x >> 5][d] = hi[d];
         }
+    }
+    __syncthreads();
+    if (threadIdx.x < D) {
+        const int d = threadIdx.x;
+        double l = s_lo[0][d], u = s_hi[0][d];
+        for (int w = 1; w < 8; ++w) {
+            l = fmin(l, s_lo[w][d]);
+            u = fmax(u, s_hi[w][d]);
+        }
+        atomicMin(&h->mm[d], enc_f64(l));
+        atomicMax(&h->mm[MPB_MAX_DIM + d], enc_f64(u));
     }
 }
 
@@ -758,7 +772,7 @@ int launch_prepare(const double *x, int64_t N, const Weights &wt, void *ws, bool
     MPB_LAUNCH_CHECK();
     if (N > 0) {
         int64_t blocks = (N + 255) / 256;
-        if (blocks > (int64_t)sm_count() * 8) blocks = (int64_t)sm_count() * 8;
+        if (blocks > (int64_t)sm_count() * 4) blocks = (int64_t)sm_count() * 4;
         knn_minmax_kernel<D><<<(unsigned)blocks, 256, 0, st>>>(x, N, wt, h);
         MPB_LAUNCH_CHECK();
     }
