@@ -76,7 +76,11 @@ int mpb_points_check(const mpb_world *world, const double *q, int64_t n, uint8_t
  * The returned handle is an mpb_world: mpb_points_check, mpb_edges_check, mpb_edges_check_pairs and
  * mpb_edges_check_knn take it (configurations have n_joints coordinates); the entry points that are stated for
  * configuration-space obstacles only (circular joints, the resident-tree planners) refuse it.
- * box_lo/box_hi: HOST [n_box, 3] raw bounds; env_lo/env_hi: HOST [n_joints]. */
+ * box_lo/box_hi: HOST [n_box, 3] raw bounds; env_lo/env_hi: HOST [n_joints].
+ * Memory: the world owns a CUDA memory pool; an edge check of 65 536 edges or more (modes ANY / FIRST) takes 256
+ * stream-ordered bytes from it for the duration of its kernel (cudaMallocFromPoolAsync / cudaFreeAsync on the
+ * caller's stream: no synchronisation, nothing from the device's default pool), and runs without them when the
+ * pool cannot give any. */
 #define MPB_ARM_MAX_JOINTS 8
 #define MPB_ARM_MAX_SPHERES 32
 typedef struct mpb_arm_model {

@@ -9,9 +9,12 @@
 // (:118), one new node (:121), the goal test (:124), and the choose-parent pass over the nodes strictly closer
 // than `radius` in index order (:128-137).
 //
-// The grid is one block per SM; the node scans are split over the blocks, the short serial parts (the sample, the
-// extension, the parent choice) are done redundantly by every block or by block 0, and three grid-wide barriers
-// separate the phases of an iteration.  mpb_rrt_star_step (rrtstar.cu) does the same work one iteration per call
+// The grid is one block per SM; the node scans are split over the blocks, and the short serial parts (the sample,
+// the extension, the parent choice, the loop's scalars) are done redundantly by EVERY block on its own registers,
+// so that only two grid-wide barriers are left per iteration: after the per-block partials of the nearest scan
+// and after the per-block best candidate parents.  (With block 0 doing the sample and the parent choice alone,
+// behind a third barrier, an iteration took 23.4 us, 45 % of it waiting at barriers.)  Block 0 writes the new
+// node; the other blocks see it in memory after the next barrier and, until then, carry it in registers.  mpb_rrt_star_step (rrtstar.cu) does the same work one iteration per call
 // and stays as the cross-check.
 #include <cooperative_groups.h>
 #include <math.h>
@@ -41,7 +44,6 @@ constexpr int kRunThreads = 256;
 constexpr int kRunMaxBlocks = 160;
 constexpr int kRunWayChunk = 128;        // waypoints of an extension staged in shared memory at a time (<= kRunThreads)
 constexpr int kRunLocalCand = 256;       // candidates one block may list per iteration
-constexpr int kRunMaxCand = 4096;        // candidates that pass the cost test in one iteration (else: status)
 
 struct RunPartial {
     double d;
@@ -58,14 +60,10 @@ struct RunState {
     long long n_nodes, iteration, u_pos, s_pos;
     int goal_idx, status, pad0, pad1;
     double goal_cost;
-    // per-iteration slots, double-buffered by the parity of the kernel's local trip counter
-    double s[2][MPB_MAX_DIM];
-    int do_goal[2], accepted[2];
-    int n_cand[2];
-    int pad2[2];
-    RunPartial partial[kRunMaxBlocks];
+    // per-iteration slots, double-buffered by the parity of the kernel's local trip counter (a block that is still
+    // reading trip t's slots cannot meet a block already writing trip t + 2's: a barrier of trip t + 1 lies between)
+    RunPartial partial[2][kRunMaxBlocks];  // per block: its nearest node
     RunCand best_cand[2][kRunMaxBlocks];   // per block: its accepted candidate with the smallest cost + d (idx = -1: none)
-    RunCand cand[2][kRunMaxCand];
     long long t_phase[8];   // MPB_RRTSTAR_TIMING builds: nanoseconds block 0 spent per phase, and rejected samples
 };
 
@@ -109,87 +107,83 @@ __global__ void __launch_bounds__(kRunThreads) rrt_star_run_kernel(RunArgs A)
 #ifdef MPB_RRTSTAR_TIMING
     long long t_last = gtime();
 #endif
+    // the loop's scalars, in every thread of every block (block 0 writes them back when the launch ends)
+    long long n_nodes = S->n_nodes, iteration = S->iteration, u_pos = S->u_pos, s_pos = S->s_pos;
+    int goal_idx = S->goal_idx, status = 0;
+    double goal_cost = S->goal_cost;
+    bool have_new = false;              // the previous trip appended a node that is not yet visible in memory
+    double newest[D];
+#pragma unroll
+    for (int d = 0; d < D; ++d) newest[d] = 0.;
     for (unsigned trip = 0;; ++trip) {
         const int pb = trip & 1;
-        // ---- A (block 0, one thread): the next accepted sample, or the reason to stop
-        if (blockIdx.x == 0 && tid == 0) {
-            int accepted = 0;
-            for (;;) {
-                if (S->iteration >= A.max_iterations) {
-                    S->status = MPB_RRTSTAR_DONE;
-                    break;
-                }
-                if (S->n_nodes + 1 >= A.cap) {
-                    S->status = MPB_RRTSTAR_FULL;
-                    break;
-                }
-                // do_goal = goal_n is None and (iteration == 0 or random() < goal_probability)
-                bool do_goal = false;
-                long long u_next = S->u_pos;
-                if (S->goal_idx < 0) {
-                    if (S->iteration == 0) {
-                        do_goal = true;
-                    } else {
-                        if (u_next >= A.n_u) {
-                            S->status = MPB_RRTSTAR_NEED_DRAWS;
-                            break;
-                        }
-                        do_goal = A.u[u_next++] < A.goal_probability;
-                    }
-                }
-                double s[D];
-                if (do_goal) {
-#pragma unroll
-                    for (int d = 0; d < D; ++d) s[d] = A.goal[d];
-                } else {
-                    if (S->s_pos >= A.n_s) {
-                        S->status = MPB_RRTSTAR_NEED_DRAWS;     // the random() draw of this trip is not consumed
-                        break;
-                    }
-#pragma unroll
-                    for (int d = 0; d < D; ++d) s[d] = A.samples[S->s_pos * D + d];
-                    S->s_pos += 1;
-                }
-                S->u_pos = u_next;
-                if (A.informed && S->goal_idx >= 0) {
-                    double a[D], g[D];
-#pragma unroll
-                    for (int d = 0; d < D; ++d) {
-                        a[d] = A.start[d];
-                        g[d] = A.goal[d];
-                    }
-                    if (d_add(metric_dist<D>(a, s, A.wt, A.metric), metric_dist<D>(s, g, A.wt, A.metric)) >= S->goal_cost)
-                    {
-#ifdef MPB_RRTSTAR_TIMING
-                        S->t_phase[7] += 1;
-#endif
-                        continue;                               // rrt_star.py:108-110: not an iteration
-                    }
-                }
-                S->iteration += 1;
-#pragma unroll
-                for (int d = 0; d < D; ++d) S->s[pb][d] = s[d];
-                S->do_goal[pb] = do_goal ? 1 : 0;
-                S->n_cand[pb] = 0;
-                accepted = 1;
+        // ---- A (every block, redundantly): the next accepted sample, or the reason to stop
+        bool accepted = false, do_goal = false;
+        double s[D];
+        for (;;) {
+            if (iteration >= A.max_iterations) {
+                status = MPB_RRTSTAR_DONE;
                 break;
             }
-            S->accepted[pb] = accepted;
+            if (n_nodes + 1 >= A.cap) {
+                status = MPB_RRTSTAR_FULL;
+                break;
+            }
+            // do_goal = goal_n is None and (iteration == 0 or random() < goal_probability)
+            do_goal = false;
+            long long u_next = u_pos;
+            if (goal_idx < 0) {
+                if (iteration == 0) {
+                    do_goal = true;
+                } else {
+                    if (u_next >= A.n_u) {
+                        status = MPB_RRTSTAR_NEED_DRAWS;
+                        break;
+                    }
+                    do_goal = A.u[u_next++] < A.goal_probability;
+                }
+            }
+            if (do_goal) {
+#pragma unroll
+                for (int d = 0; d < D; ++d) s[d] = A.goal[d];
+            } else {
+                if (s_pos >= A.n_s) {
+                    status = MPB_RRTSTAR_NEED_DRAWS;         // the random() draw of this trip is not consumed
+                    break;
+                }
+#pragma unroll
+                for (int d = 0; d < D; ++d) s[d] = A.samples[s_pos * D + d];
+                s_pos += 1;
+            }
+            u_pos = u_next;
+            if (A.informed && goal_idx >= 0) {
+                double a[D], g[D];
+#pragma unroll
+                for (int d = 0; d < D; ++d) {
+                    a[d] = A.start[d];
+                    g[d] = A.goal[d];
+                }
+                if (d_add(metric_dist<D>(a, s, A.wt, A.metric), metric_dist<D>(s, g, A.wt, A.metric)) >= goal_cost) {
+#ifdef MPB_RRTSTAR_TIMING
+                    if (blockIdx.x == 0 && tid == 0) S->t_phase[7] += 1;
+#endif
+                    continue;                                   // rrt_star.py:108-110: not an iteration
+                }
+            }
+            iteration += 1;
+            accepted = true;
+            break;
         }
         RT_MARK(0)
-        grid.sync();
-        RT_MARK(1)
-        if (!S->accepted[pb]) break;
-        const long long n = S->n_nodes;
-        double s[D];
-#pragma unroll
-        for (int d = 0; d < D; ++d) s[d] = S->s[pb][d];
+        if (!accepted) break;
+        const long long n = n_nodes;
 
         // ---- B: first arg-min of distance_fn(node, s): per-block partials
         {
             double best = INFINITY;
             int bi = 0x7fffffff;
-            for (long long j = (long long)blockIdx.x * kRunThreads + tid; j < n; j += (long long)gridDim.x * kRunThreads) {
+            const long long n_vis = have_new ? n - 1 : n;       // node n - 1 may not have reached memory yet
+            for (long long j = (long long)blockIdx.x * kRunThreads + tid; j < n_vis; j += (long long)gridDim.x * kRunThreads) {
                 double a[D];
 #pragma unroll
                 for (int d = 0; d < D; ++d) a[d] = A.table[j * D + d];
@@ -197,6 +191,13 @@ __global__ void __launch_bounds__(kRunThreads) rrt_star_run_kernel(RunArgs A)
                 if (dd < best) {
                     best = dd;
                     bi = (int)j;
+                }
+            }
+            if (have_new && blockIdx.x == 0 && tid == 0) {      // the highest index: it only wins a strictly smaller distance
+                const double dd = metric_dist<D>(newest, s, A.wt, A.metric);
+                if (dd < best) {
+                    best = dd;
+                    bi = (int)(n - 1);
                 }
             }
 #pragma unroll
@@ -219,8 +220,8 @@ __global__ void __launch_bounds__(kRunThreads) rrt_star_run_kernel(RunArgs A)
                         best = sd[w];
                         bi = si[w];
                     }
-                S->partial[blockIdx.x].d = best;
-                S->partial[blockIdx.x].i = bi;
+                S->partial[pb][blockIdx.x].d = best;
+                S->partial[pb][blockIdx.x].i = bi;
             }
         }
         RT_MARK(2)
@@ -231,8 +232,8 @@ __global__ void __launch_bounds__(kRunThreads) rrt_star_run_kernel(RunArgs A)
         double best = INFINITY;
         int nearest = 0x7fffffff;
         for (int p = tid; p < (int)gridDim.x; p += kRunThreads) {      // one partial per thread, then a block reduction
-            const double pd = S->partial[p].d;
-            const int pi = S->partial[p].i;
+            const double pd = S->partial[pb][p].d;
+            const int pi = S->partial[pb][p].i;
             if (pd < best || (pd == best && pi < nearest)) {
                 best = pd;
                 nearest = pi;
@@ -277,7 +278,9 @@ __global__ void __launch_bounds__(kRunThreads) rrt_star_run_kernel(RunArgs A)
             __syncthreads();
             if (tid < D) {
                 double q = (base == 0) ? A.table[(long long)nearest * D + tid] : wp[(kRunWayChunk - 1) * D + tid];
-                const double b = S->s[pb][tid];
+                double b = s[0];
+#pragma unroll
+                for (int d = 1; d < D; ++d) b = (d == tid) ? s[d] : b;
                 for (int i = 0; i < m; ++i) {
                     q = d_add(d_mul(cinv[i], d_sub(b, q)), q);
                     wp[i * D + tid] = q;
@@ -312,7 +315,10 @@ __global__ void __launch_bounds__(kRunThreads) rrt_star_run_kernel(RunArgs A)
                 break;
             }
         }
-        if (safe == 0) continue;                            // every block takes the same branch
+        if (safe == 0) {                                    // every block takes the same branch
+            have_new = false;
+            continue;
+        }
         const double d_near_new = metric_dist<D>(a, nw, A.wt, A.metric);
         const double cost0 = d_add(A.cost[nearest], d_near_new);          // OptimalNode.__init__: parent.cost + d
         RT_MARK(3)
@@ -410,11 +416,11 @@ __global__ void __launch_bounds__(kRunThreads) rrt_star_run_kernel(RunArgs A)
         grid.sync();
         RT_MARK(1)
 
-        // ---- E (block 0): the parent choice, the new node, the goal test.
+        // ---- E (every block, redundantly): the parent choice and the goal test; block 0 writes the new node.
         // "for n in neighbors (index order): if (n.cost + d) < new.cost and the edge is free: rewire" ends at the
         // accepted candidate with the smallest n.cost + d, the lowest index among equals (a later equal value is
         // not strictly smaller), provided that beats the cost through the nearest node: an arg-min.
-        if (blockIdx.x == 0) {
+        {
             double bv = INFINITY;
             int bidx = 0x7fffffff, bc = -1;
             for (int c = tid; c < (int)gridDim.x; c += kRunThreads) {
@@ -428,39 +434,38 @@ __global__ void __launch_bounds__(kRunThreads) rrt_star_run_kernel(RunArgs A)
             }
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) {
-                const double ov = __shfl_down_sync(0xffffffffu, bv, o);
-                const int oi = __shfl_down_sync(0xffffffffu, bidx, o);
-                const int oc = __shfl_down_sync(0xffffffffu, bc, o);
+                const double ov = __shfl_xor_sync(0xffffffffu, bv, o);
+                const int oi = __shfl_xor_sync(0xffffffffu, bidx, o);
+                const int oc = __shfl_xor_sync(0xffffffffu, bc, o);
                 if (ov < bv || (ov == bv && oi < bidx)) {
                     bv = ov;
                     bidx = oi;
                     bc = oc;
                 }
             }
-            __shared__ double ev[kRunThreads / 32];
-            __shared__ int ei[kRunThreads / 32], ec[kRunThreads / 32];
             if (lane == 0) {
-                ev[warp] = bv;
-                ei[warp] = bidx;
-                ec[warp] = bc;
+                sd[warp] = bv;
+                si[warp] = bidx;
+                ss[warp] = bc;
             }
             __syncthreads();
-            if (tid == 0) {
-                for (int w = 1; w < kRunThreads / 32; ++w)
-                    if (ev[w] < bv || (ev[w] == bv && ei[w] < bidx)) {
-                        bv = ev[w];
-                        bidx = ei[w];
-                        bc = ec[w];
-                    }
-                double cur = cost0;
-                int par = nearest, cnt = safe - 1;
-                bool to_sample = true;
-                if (bc >= 0 && bv < cost0) {
-                    cur = bv;
-                    par = bidx;
-                    cnt = S->best_cand[pb][bc].safe - 1;
-                    to_sample = false;
+            for (int w = 0; w < kRunThreads / 32; ++w)
+                if (sd[w] < bv || (sd[w] == bv && si[w] < bidx)) {
+                    bv = sd[w];
+                    bidx = si[w];
+                    bc = ss[w];
                 }
+            __syncthreads();                                            // sd / si / ss are reused by the next trip
+            double cur = cost0;
+            int par = nearest, cnt = safe - 1;
+            bool to_sample = true;
+            if (bc >= 0 && bv < cost0) {
+                cur = bv;
+                par = bidx;
+                cnt = S->best_cand[pb][bc].safe - 1;
+                to_sample = false;
+            }
+            if (blockIdx.x == 0 && tid == 0) {
 #pragma unroll
                 for (int d = 0; d < D; ++d) {
                     A.table[n * D + d] = nw[d];
@@ -469,22 +474,33 @@ __global__ void __launch_bounds__(kRunThreads) rrt_star_run_kernel(RunArgs A)
                 A.cost[n] = cur;
                 A.parent[n] = par;
                 A.path_cnt[n] = cnt;
-                if (S->do_goal[pb]) {
-                    double g[D];
-#pragma unroll
-                    for (int d = 0; d < D; ++d) g[d] = A.goal[d];
-                    if (metric_dist<D>(nw, g, A.wt, A.metric) < A.eps) {       // rrt_star.py:124-126
-                        S->goal_idx = (int)n;
-                        S->goal_cost = cur;
-                    }
-                }
-                S->n_nodes = n + 1;
-                __threadfence();
             }
-            __syncthreads();
+            if (do_goal) {
+                double g[D];
+#pragma unroll
+                for (int d = 0; d < D; ++d) g[d] = A.goal[d];
+                if (metric_dist<D>(nw, g, A.wt, A.metric) < A.eps) {           // rrt_star.py:124-126
+                    goal_idx = (int)n;
+                    goal_cost = cur;
+                }
+            }
+            n_nodes = n + 1;
+            have_new = true;
+#pragma unroll
+            for (int d = 0; d < D; ++d) newest[d] = nw[d];
         }
         RT_MARK(5)
-        // block 0's thread 0 goes straight on to phase A of the next trip; the barrier after A publishes both
+    }
+    // the launch ends: block 0 leaves the loop's scalars for the next launch and the host (a candidate overflow
+    // reported by some block during the run stays)
+    if (blockIdx.x == 0 && tid == 0) {
+        S->n_nodes = n_nodes;
+        S->iteration = iteration;
+        S->u_pos = u_pos;
+        S->s_pos = s_pos;
+        S->goal_idx = goal_idx;
+        S->goal_cost = goal_cost;
+        if (S->status != MPB_RRTSTAR_CAND_OVERFLOW) S->status = status;
     }
 }
 
@@ -588,7 +604,7 @@ MPB_API int mpb_rrt_star_run_read(const void *state, int64_t *out6, double *out_
 {
     MPB_REQUIRE(state && out6 && out_goal_cost, "mpb_rrt_star_run_read: NULL buffer");
     RunState head;
-    MPB_CUDA_CHECK(cudaMemcpyAsync(&head, state, offsetof(RunState, s), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    MPB_CUDA_CHECK(cudaMemcpyAsync(&head, state, offsetof(RunState, partial), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     MPB_CUDA_CHECK(cudaStreamSynchronize((cudaStream_t)stream));
     out6[0] = head.n_nodes;
     out6[1] = head.iteration;

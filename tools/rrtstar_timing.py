@@ -26,8 +26,8 @@ st = keep["state"]
 off = (-st.data_ptr()) % 256
 raw = st[off:].cpu().numpy()
 tail = raw[: (len(raw) // 8) * 8].view(np.int64)
-struct_words = tail[207192 // 8: 207192 // 8 + 8]     # offsetof(RunState, t_phase)
-names = ["A sample", "grid.sync waits", "B nearest scan", "C extension", "D radius scan + candidate edges", "E parent choice", "-", "rejected samples"]
+struct_words = tail[12856 // 8: 12856 // 8 + 8]     # offsetof(RunState, t_phase)
+names = ["A sample (every block)", "grid.sync waits", "B nearest scan", "C extension", "D radius scan + candidate edges", "E parent choice (every block)", "-", "rejected samples"]
 tot = sum(int(v) for v in struct_words[:6])
 for nm, v in zip(names, struct_words):
     print("%-34s %12d  %5.1f%%" % (nm, int(v), 100.0 * int(v) / tot if nm != "rejected samples" else 0))
