@@ -453,7 +453,13 @@ def main():
         clocks = sampler.stop()
         rm.profile = False
         t = torch.tensor([total_ms], device="cuda", dtype=torch.float64)
+        per_rank = None
         if world_size > 1:
+            mine = torch.tensor([total_ms / steps] + [phase.get(a, 0.0) / steps for a in ("packed", "knn", "vertices", "edges")],
+                                device="cuda", dtype=torch.float64)
+            every = torch.empty((world_size, mine.numel()), device="cuda", dtype=torch.float64)
+            dist.all_gather_into_tensor(every, mine)
+            per_rank = [[round(v, 3) for v in row] for row in every.cpu().tolist()]
             dist.all_reduce(t, op=dist.ReduceOp.MAX)                # max over ranks
         total_ms = float(t.item())
         edges_local = torch.tensor([rm.n_edges_checked()], device="cuda", dtype=torch.int64)
@@ -480,7 +486,7 @@ def main():
                "phase_ms": {a: b / steps for a, b in phase.items()}, "clocks": clocks, "launches": rm.launches,
                "fallback_queries": int(fb.item()), "n_local": hi - lo, "wall_s": wall_s,
                "tiles_visited": int(tiles_visited.item()), "mean_waypoints": float(wp.mean().item()),
-               "edge_hit_frac": hit_frac, "free_vertex_frac": free_vertices}
+               "edge_hit_frac": hit_frac, "free_vertex_frac": free_vertices, "per_rank": per_rank}
 
         if with_e2e:
             pinned = torch.from_numpy(np.ascontiguousarray(X[lo:hi])).pin_memory()
@@ -643,6 +649,7 @@ def main():
                    "sharding": "samples sharded over ranks, one NCCL all-gather per step, edges stay sharded",
                    "l2": "flushed between timed steps (256 MiB write, untimed); inputs are smaller than L2"},
         "phases_ms": m["phase_ms"],
+        "per_rank_ms": {"columns": ["step", "packed", "knn", "vertices", "edges"], "rows": m["per_rank"]} if m["per_rank"] else None,
         "kernel_rates": {"knn_queries_per_s": m["n_local"] * world_size / (knn_ms * 1e-3),
                          "edges_per_s": m["edges"] / (m["phase_ms"].get("edges", float("nan")) * 1e-3)},
         "fallback_queries": m["fallback_queries"],

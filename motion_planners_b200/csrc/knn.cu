@@ -154,10 +154,24 @@ __global__ void knn_set_stat_kernel(int64_t *stats, int64_t v) { stats[0] = v; }
 
 // Where the answer of query q goes: row q, or -- when the queries are a slice of the samples' spatial order
 // (mpb_knn_search_part) -- the query's position in that order, counted from the slice's first position.
+// kdorder.cuh (included further down)
+__host__ __device__ inline int64_t kd_leaf_start(int64_t j, int64_t n, int64_t L);
+__host__ __device__ inline int64_t kd_leaf_of(int64_t pos, int64_t n, int64_t L);
+
 struct RowMap {
-    const int32_t *inv;     // sample index -> position in the spatial order (NULL: row = q)
-    int64_t pos0;
-    __device__ __forceinline__ int64_t row(int64_t q) const { return inv ? (int64_t)inv[q] - pos0 : q; }
+    const int32_t *inv;        // sample index -> position in the spatial order (NULL: row = q)
+    int64_t pos0;              // rowstart == NULL: the rows are the positions from pos0 on
+    const int32_t *rowstart;   // a dealt share (kd_share_leaf): first row of each of its blocks
+    int parts;
+    int64_t n, leaves;
+    __device__ __forceinline__ int64_t row(int64_t q) const
+    {
+        if (!inv) return q;
+        const int64_t pos = inv[q];
+        if (!rowstart) return pos - pos0;
+        const int64_t l = kd_leaf_of(pos, n, leaves);
+        return (int64_t)rowstart[l / parts] + pos - kd_leaf_start(l, n, leaves);
+    }
 };
 
 __global__ void knn_finalize_kernel(KnnHeader *h, int D)
@@ -881,26 +895,30 @@ int launch_search(const double *x, int64_t N, const double *qs, int64_t M, const
             const int *qorder = slot_idx;                  // the sample set queried against itself: block = half tile
             int64_t blocks = 2 * L.tc_tiles;
             int64_t own_block0 = 0;
-            RowMap rows = RowMap{nullptr, 0};
+            int own_part = 0, own_parts = 1;
+            RowMap rows = RowMap{nullptr, 0, nullptr, 1, 0, 0};
             const bool own = (qs == x && M == N);
             if (part >= 0) {
-                // the queries are the samples of leaves [leaf_begin, leaf_end) of the spatial order: the same blocks a
-                // whole-set search has, a share of them; answers go to rows counted from the slice's first position
+                // the queries are the samples of share `part` of the leaves (kd_share_leaf): the same blocks a
+                // whole-set search has, a share of them; block i's answers go to rows rowstart[i] onwards.  The two
+                // small tables live in the sort scratch, which a search of the set against itself does not use.
                 const KdPlan plan = tc_sample_plan(N, D);
-                const int64_t leaf_begin = plan.leaves * part / parts, leaf_end = plan.leaves * (part + 1) / parts;
-                const int64_t pos0 = kd_leaf_start(leaf_begin, N, plan.leaves);
-                const int64_t n_rows = kd_leaf_start(leaf_end, N, plan.leaves) - pos0;
-                qorder = slot_idx + leaf_begin * kTcQueries;
-                blocks = leaf_end - leaf_begin;
-                own_block0 = leaf_begin;
-                rows = RowMap{reinterpret_cast<const int32_t *>(base + L.inv_off), pos0};
-                if (out_rows && n_rows > 0) {
-                    kd_rows_kernel<<<(unsigned)((n_rows + 255) / 256), 256, 0, st>>>(
-                        reinterpret_cast<const uint32_t *>(base + L.perm_off), pos0, n_rows, out_rows);
-                    MPB_LAUNCH_CHECK();
-                    g_last_launches += 1;
-                }
+                blocks = kd_share_blocks(plan.leaves, part, parts);
                 if (blocks == 0) return MPB_OK;
+                int *share_q = reinterpret_cast<int *>(base + L.sort_off);
+                int32_t *rowstart = reinterpret_cast<int32_t *>(base + L.sort_off) + blocks * kTcQueries;
+                kd_share_rowstart_kernel<<<1, 1024, 0, st>>>(N, plan.leaves, part, parts, blocks, rowstart);
+                MPB_LAUNCH_CHECK();
+                kd_share_slots_kernel<<<(unsigned)blocks, 128, 0, st>>>(
+                    slot_idx, reinterpret_cast<const uint32_t *>(base + L.perm_off), N, plan.leaves, part, parts, rowstart,
+                    share_q, out_rows);
+                MPB_LAUNCH_CHECK();
+                g_last_launches += 2;
+                qorder = share_q;
+                own_block0 = 0;
+                own_part = part;
+                own_parts = parts;
+                rows = RowMap{reinterpret_cast<const int32_t *>(base + L.inv_off), 0, rowstart, parts, N, plan.leaves};
             } else if (!own) {
                 own_block0 = -1;
                 // any other query set gets its own k-d order, one leaf of at most 128 queries per block
@@ -919,7 +937,7 @@ int launch_search(const double *x, int64_t N, const double *qs, int64_t M, const
             MPB_CUDA_CHECK(cudaFuncSetAttribute(knn_tc_kernel<D, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                 (int)TcSmem::BYTES));
             knn_tc_kernel<D, false><<<(unsigned)blocks, kTcThreads, TcSmem::BYTES, st>>>(
-                qs, qorder, wt, tiles, (int)L.tc_tiles, boxes, L.box_stride, h, surv, sthr, nullptr, nullptr, nullptr, own_block0);
+                qs, qorder, wt, tiles, (int)L.tc_tiles, boxes, L.box_stride, h, surv, sthr, nullptr, nullptr, nullptr, own_block0, own_part, own_parts);
             MPB_LAUNCH_CHECK();
             const int64_t n_slots = blocks * kTcQueries;
             const int64_t rthreads = n_slots * 32;
@@ -966,7 +984,7 @@ int launch_tc_diag(const double *x, int64_t N, const double *qs, int64_t M, cons
         knn_tc_kernel<D, true><<<(unsigned)blocks, kTcThreads, TcSmem::BYTES, st>>>(
             qs, qo, wt, reinterpret_cast<const unsigned char *>(base + L.tc_off), (int)L.tc_tiles,
             reinterpret_cast<const float *>(base + L.box_off), L.box_stride, h, nullptr, nullptr, x,
-            reinterpret_cast<const int *>(base + L.slot_off), out, -1);
+            reinterpret_cast<const int *>(base + L.slot_off), out, -1, 0, 1);
         MPB_LAUNCH_CHECK();
         return MPB_OK;
     } else {
@@ -1103,8 +1121,13 @@ MPB_API int64_t mpb_knn_part_rows(int64_t n_samples, int dim, int part, int part
     if (dim < 1 || dim > kTcMaxDim || n_samples <= 0 || parts < 1 || part < 0 || part >= parts) return -1;
     if (!use_tc(n_samples, dim)) return -1;
     const KdPlan plan = tc_sample_plan(n_samples, dim);
-    const int64_t b = plan.leaves * part / parts, e = plan.leaves * (part + 1) / parts;
-    return kd_leaf_start(e, n_samples, plan.leaves) - kd_leaf_start(b, n_samples, plan.leaves);
+    int64_t rows = 0;
+    const int64_t blocks = kd_share_blocks(plan.leaves, part, parts);
+    for (int64_t i = 0; i < blocks; ++i) {
+        const int64_t l = kd_share_leaf(i, part, parts);
+        rows += kd_leaf_start(l + 1, n_samples, plan.leaves) - kd_leaf_start(l, n_samples, plan.leaves);
+    }
+    return rows;
 }
 
 MPB_API int mpb_knn_search_part(const double *samples, int64_t n_samples, int dim, const double *weights, int k,

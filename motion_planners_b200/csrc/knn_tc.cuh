@@ -388,7 +388,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
                   const unsigned char *__restrict__ tiles, int n_tiles, const float *__restrict__ tile_box,
                   int box_stride, const KnnHeader *__restrict__ h, int *__restrict__ surv_idx,
                   float *__restrict__ surv_thr, const double *__restrict__ x, const int *__restrict__ slot_idx,
-                  unsigned long long *__restrict__ diag, int64_t own_block0)
+                  unsigned long long *__restrict__ diag, int64_t own_block0, int own_part, int own_parts)
 {
     extern __shared__ __align__(1024) unsigned char smem[];
     unsigned char *sA = smem + TcSmem::A_OFF;
@@ -500,12 +500,13 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     };
 
     // ---- round 0: the nearest tile alone (ties: lowest index); it gives every query of the block a first
-    // threshold.  own_block0 >= 0: the queries are samples in their own leaf order, block b is leaf own_block0 + b,
-    // one half of tile (own_block0 + b) / 2.
+    // threshold.  own_block0 >= 0: the queries are samples in their own leaf order, block b is leaf b of share
+    // own_part of own_parts (kd_share_leaf; 0 of 1 = every leaf), one half of tile leaf / 2.
     if (own_block0 >= 0) {
         if (tid == 0) {
-            ctl->home = (int)((own_block0 + blockIdx.x) >> 1);
-            list[0] = key_of(0.f, (int)((own_block0 + blockIdx.x) >> 1));
+            const int64_t leaf = own_block0 + kd_share_leaf((int64_t)blockIdx.x, own_part, own_parts);
+            ctl->home = (int)(leaf >> 1);
+            list[0] = key_of(0.f, (int)(leaf >> 1));
             ctl->list_n = 1;
         }
         __syncthreads();
