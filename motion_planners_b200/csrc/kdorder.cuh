@@ -216,11 +216,12 @@ __global__ void __launch_bounds__(128) kd_share_slots_kernel(const int *__restri
     }
 }
 
-// keys of one level: (first leaf of the point's current cell) << coord_bits | leading bits of its centred coordinate
+// keys of one level: (number of the point's current cell) << coord_bits | leading bits of its centred coordinate
 template <int D>
 __global__ void __launch_bounds__(256)
     kd_key_kernel(const double *__restrict__ x, Weights wt, const KnnHeader *__restrict__ h, KdPlan p, int level,
-                  const uint32_t *__restrict__ perm_in, uint64_t *__restrict__ keys, uint32_t *__restrict__ vals)
+                  int64_t leaves_per_cell, const uint32_t *__restrict__ perm_in, uint64_t *__restrict__ keys,
+                  uint32_t *__restrict__ vals)
 {
     const int64_t pos = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (pos >= p.n) return;
@@ -233,7 +234,7 @@ __global__ void __launch_bounds__(256)
     for (int dd = 1; dd < D; ++dd)
         if (dd == d) w = wt.w[dd];
     const float f = (float)d_sub(d_mul(w, x[(int64_t)j * D + d]), h->center[d]);
-    const uint64_t cell = (uint64_t)kd_cell_start(p, kd_leaf_of(pos, p.n, p.leaves), level);
+    const uint64_t cell = (uint64_t)(kd_cell_start(p, kd_leaf_of(pos, p.n, p.leaves), level) / leaves_per_cell);
     keys[pos] = (cell << p.coord_bits) | (uint64_t)(ord_f32(f) >> (32 - p.coord_bits));
     vals[pos] = j;
 }
@@ -472,7 +473,7 @@ int kd_order(const double *x, int64_t n, const Weights &wt, const KnnHeader *h, 
     if (plan.levels == 0) {
         // a single leaf: the identity order (written through the same kernel for uniformity)
         KdPlan p1 = plan;
-        kd_key_kernel<D><<<blocks, 256, 0, st>>>(x, wt, h, p1, 0, nullptr, s.keys[0], s.vals[0]);
+        kd_key_kernel<D><<<blocks, 256, 0, st>>>(x, wt, h, p1, 0, p1.leaves, nullptr, s.keys[0], s.vals[0]);
         MPB_LAUNCH_CHECK();
         if (launches) *launches += 1;
         *perm_out = s.vals[0];
@@ -497,11 +498,13 @@ int kd_order(const double *x, int64_t n, const Weights &wt, const KnnHeader *h, 
             cur ^= 1;
         } else {
             // the keys are written into the buffer the sort will read; the values ride along
-            kd_key_kernel<D><<<blocks, 256, 0, st>>>(x, wt, h, plan, l, perm_in, s.keys[cur ^ 1], s.vals[cur ^ 1]);
+            kd_key_kernel<D><<<blocks, 256, 0, st>>>(x, wt, h, plan, l, leaves_per_cell, perm_in, s.keys[cur ^ 1],
+                                                     s.vals[cur ^ 1]);
             MPB_LAUNCH_CHECK();
             if (launches) *launches += 1;
             cur ^= 1;
-            const int bits = plan.coord_bits + (l == 0 ? 0 : plan.leaf_bits);
+            // the cell number takes log2(cells) bits, not the leaf number's: one radix pass fewer on the upper levels
+            const int bits = plan.coord_bits + ceil_log2_i64(cells);
             cur = rs_sort(s, cur, n, bits, st, launches);
             MPB_LAUNCH_CHECK();
         }
