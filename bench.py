@@ -502,15 +502,8 @@ def main():
                 e2e_s = (time.perf_counter() - t0) / steps
             else:
                 def e2e_step():
-                    dev = pinned.cuda(non_blocking=True)
-                    rm2.build(dev, gathered=rm2.gather_samples_equal(dev, gathered_buf) if equal else None)
-                    outs = (rm2.nbr_idx.to(torch.int32), rm2.vertex_hit, rm2.edge_hit)
-                    if not hasattr(rm2, "_host_out"):
-                        rm2._host_out = tuple(torch.empty(o.shape, dtype=o.dtype).pin_memory() for o in outs)
-                    for hbuf, o in zip(rm2._host_out, outs):
-                        hbuf.copy_(o, non_blocking=True)
-                    torch.cuda.current_stream().synchronize()
-                    return rm2._host_out
+                    return rm2.build_from_host(
+                        pinned, gather=(lambda d: rm2.gather_samples_equal(d, gathered_buf)) if equal else None)
                 for _ in range(2):
                     e2e_step()
                 barrier()

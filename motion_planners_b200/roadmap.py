@@ -157,6 +157,8 @@ class DeviceRoadmap(object):
                                out_dist=self.nbr_dist)
         launches += _lib.lib().mpb_knn_launch_count() - count0
         mark("knn")
+        if getattr(self, "_after_knn", None) is not None:
+            self._after_knn()
 
         if check:
             self.vertex_hit = self.obstacles.points_check(queries)
@@ -198,21 +200,47 @@ class DeviceRoadmap(object):
         have = [n for n in order if n in self.events]
         return {b: self.events[a].elapsed_time(self.events[b]) for a, b in zip(have[:-1], have[1:])}
 
-    def build_from_host(self, pinned_samples):
+    def build_from_host(self, pinned_samples, gather=None):
         """End-to-end call with HOST buffers: a pinned float64 [N, D] CPU tensor in; neighbour matrix (int32),
         vertex flags and edge flags back on the host.  Host->device and device->host copies are part of
-        the call; this is what bench.py times as `e2e`."""
+        the call; this is what bench.py times as `e2e`.  `gather` (multi-GPU): called with this rank's device shard,
+        returns the all-gathered sample set for build()."""
         dev = pinned_samples.cuda(non_blocking=True)
-        self.build(dev)
-        # sample indices are below 2^31 (the C ABI refuses larger sets): the neighbour matrix crosses PCIe as int32
-        outs = (self.nbr_idx.to(torch.int32), self.vertex_hit, self.edge_hit)
+        side = getattr(self, "_side_stream", None)
+        if side is None:
+            side = self._side_stream = torch.cuda.Stream()
+        sent = {}
+
+        def after_knn():
+            # the neighbour matrix goes home on a second stream while the collision checks run.  Sample indices are
+            # below 2^31 (the C ABI refuses larger sets): it crosses PCIe as int32
+            host = getattr(self, "_host_nbr", None)
+            if host is None or host.shape != self.nbr_idx.shape:
+                host = self._host_nbr = torch.empty(self.nbr_idx.shape, dtype=torch.int32).pin_memory()
+            done = torch.cuda.Event()
+            done.record()
+            side.wait_event(done)
+            with torch.cuda.stream(side):
+                sent["nbr32"] = self.nbr_idx.to(torch.int32)
+                host.copy_(sent["nbr32"], non_blocking=True)
+
+        self._after_knn = after_knn
+        try:
+            if gather is not None:
+                self.build(dev, gathered=gather(dev))
+            else:
+                self.build(dev)
+        finally:
+            self._after_knn = None
+        outs = (self.vertex_hit, self.edge_hit)
         host = getattr(self, "_host_out", None)
         if host is None or any(h.shape != o.shape for h, o in zip(host, outs)):
             host = self._host_out = tuple(torch.empty(o.shape, dtype=o.dtype).pin_memory() for o in outs)
         for h, o in zip(host, outs):
-            h.copy_(o, non_blocking=True)          # pinned destination: three back-to-back DMA transfers
+            h.copy_(o, non_blocking=True)          # pinned destinations
         torch.cuda.current_stream().synchronize()
-        return host
+        side.synchronize()
+        return (self._host_nbr,) + host
 
     # -- shortest path over the built roadmap (lazy_prm.py:41-98: dijkstra / wastar_search, on the device)
     def shortest_path(self, source, target=None, max_rounds=4096):

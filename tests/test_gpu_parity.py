@@ -380,3 +380,23 @@ def test_roadmap_shortest_path_matches_host_dijkstra(ops):
         cost += g[a, b]
     assert abs(cost - d[dst]) <= 1e-9 * d[dst]
     assert both.sum() > N // 2
+
+
+def test_roadmap_build_from_host_returns_what_build_leaves_on_the_device(ops):
+    """The host-buffer call (bench.py's e2e): pinned samples in; neighbour matrix (int32, copied on a second stream
+    while the collision checks run), vertex and edge flags back in pinned buffers -- equal to the device-resident
+    results of the same build, on two calls in a row (the second reuses the host buffers)."""
+    import torch
+    from motion_planners_b200 import workloads
+    from motion_planners_b200.roadmap import DeviceRoadmap
+    w = workloads.boxes_world(6, 64, 0.2, 0.6, seed=0)
+    X = workloads.uniform_samples(30000, 6, seed=4)
+    ref = DeviceRoadmap(w, k=10).build(dev(X))
+    pinned = torch.from_numpy(X).pin_memory()
+    rm = DeviceRoadmap(w, k=10)
+    for _ in range(2):
+        nbr, vhit, ehit = rm.build_from_host(pinned)
+        assert nbr.dtype == torch.int32 and not nbr.is_cuda
+        assert (nbr.numpy() == host(ref.nbr_idx)).all()
+        assert (vhit.numpy() == host(ref.vertex_hit)).all()
+        assert (ehit.numpy() == host(ref.edge_hit)).all()
