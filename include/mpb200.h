@@ -409,8 +409,8 @@ int mpb_knn_tc_key_error(const double *samples, int64_t n_samples, const double 
 
 /* The spatial order of a prepared sample set: out_order dev [n_samples] i32 = the sample indices in the leaf order
  * of the balanced k-d partition mpb_knn_prepare built for the tensor-core scan (consecutive entries are close in
- * space).  A multi-GPU caller gives every rank a contiguous slice of this order as its queries, so that each
- * rank's query blocks are as compact as a single GPU's (roadmap.py).  MPB_EINVAL when the set is not served by
+ * space).  mpb_knn_search_part forms a rank's query blocks from whole leaves of this order, so that each rank's
+ * blocks are as compact as a single GPU's (roadmap.py).  MPB_EINVAL when the set is not served by
  * the tensor-core scan (mpb_knn_filter_kind), which builds no order.  No counterpart in the reference (scipy's
  * cKDTree keeps its tree to itself, nearest.py:59-61). */
 int mpb_knn_sample_order(const void *workspace, size_t workspace_bytes, int64_t n_samples, int dim,
@@ -419,8 +419,10 @@ int mpb_knn_sample_order(const void *workspace, size_t workspace_bytes, int64_t 
 /* mpb_knn_search for one share of the sample set queried against itself -- the multi-GPU form of
  * lazy_prm.py:148-160 add_samples (every sample asks for its neighbours among all samples): after the all-gather
  * every rank holds all samples, prepares the same workspace, and answers part `part` of `parts` of the queries.
- * The parts are contiguous slices of the set's spatial order (whole k-d leaves), so every rank's 128-query blocks
- * are exactly the blocks a single-GPU search forms, a share of them, and prune as well.
+ * A part is a share of the set's k-d leaves (whole leaves, dealt in rotation: leaf parts * a + b belongs to part
+ * (a + b) mod parts), so every rank's 128-query blocks are exactly the blocks a single-GPU search forms, a share
+ * of them from all over the sampled region, and prune as well.  Rows: the part's leaves in ascending order, the
+ * samples of a leaf in the order of mpb_knn_sample_order.
  * out_rows dev [rows] i64 (may be NULL): the sample index of every row; out_idx dev [rows, k], out_dist dev
  * [rows, k] (may be NULL); rows = mpb_knn_part_rows(n_samples, dim, part, parts) (host arithmetic; -1 when the
  * tensor-core scan does not serve the set: use mpb_knn_search on an index shard then).  The union of all parts'
