@@ -13,7 +13,8 @@
  *    `stream`; nothing synchronises the device unless stated.
  *  - "dev" pointers are device pointers on the CURRENT device, "host" pointers are
  *    host pointers.  The caller owns every buffer; the library allocates nothing
- *    except inside mpb_world_create.
+ *    except inside mpb_world_create / mpb_arm_world_create (and, for an arm world, 256
+ *    stream-ordered bytes per large edge check from a pool that world owns: see there).
  *  - Configurations are row-major [n, D] IEEE binary64, contiguous, D <= MPB_MAX_DIM.
  *  - Return value: 0 on success, a negative MPB_E* code otherwise; mpb_last_error()
  *    returns a thread-local message.  Nothing throws, nothing aborts.
