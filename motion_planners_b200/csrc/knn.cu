@@ -643,16 +643,21 @@ static thread_local int g_last_launches = 0;
 // ------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------
-// Which filter serves a search.  The tensor-core scan (knn_tc.cuh) costs the same for every dimension up to 7
-// (its operand is always 24 columns wide) and has a heavier insertion path than the FFMA2 kernel, so it wins where
-// the scan is long and the dimension high.  Measured on B200, k = 11, tensor-core vs FFMA2 kernel: 7-DoF 1M samples
-// 140 vs 245 ms, 300k 20.7 vs 28.4, 200k 11.7 vs 13.8, 150k 7.5 vs 8.0, 100k 5.0 vs 4.1; 6-DoF 100k 4.9 vs 3.8;
-// the FFMA2 kernel at 1M samples takes 158 / 180 / 206 / 226 ms at 3 / 4 / 5 / 6 dimensions.  Default: from
-// kTcAutoMin[dim] samples on.  MPB200_KNN_TC=0 switches the tensor-core scan off, MPB200_KNN_TC=1 forces it for
+// Which filter serves a search.  The tensor-core scan (knn_tc.cuh) reads only the tiles near a query block, the
+// FFMA2 kernel scans every pair; the scan's prepare (k-d order, operand tiles) costs 0.2 to 0.7 ms against 0.04.
+// Measured on B200, uniform samples, k = 11, set against itself, prepare + search, tensor-core scan vs FFMA2
+// kernel (tools/tc_policy_sweep.py, profiles/r2_tc_policy_sweep.txt): 7-DoF 20k 0.61 vs 0.52 ms, 50k 1.02 vs 1.46,
+// 100k 1.77 vs 4.09, 1M 14.6 vs 244; 6-DoF 20k 0.54 vs 0.51, 50k 0.89 vs 1.38, 100k 1.53 vs 3.85, 1M 10.8 vs 226;
+// 5-DoF 20k 0.47 vs 0.49, 50k 0.69 vs 1.30, 1M 8.9 vs 207; 4-DoF 20k 0.35 vs 0.47, 100k 0.79 vs 3.32, 1M 24.7 vs
+// 180.  In 2 and 3 dimensions large sets are so dense (neighbours 1e-3 apart in a unit box) that the TF32
+// certificate cannot separate the k-th from the next key and queries fall through to the exact kernel (3-D: 33 of
+// 200k, 23k of 1M; 2-D: all of 1M): those stay with the FFMA2 kernel.  (Round 1's boundaries, 160k to 500k, were
+// measured before the scan pruned tiles.)  Default: from kTcAutoMin[dim] samples on.  MPB200_KNN_TC=0 switches
+// the tensor-core scan off, MPB200_KNN_TC=1 forces it for
 // every set it can serve (dimension <= 7, at least MPB200_KNN_TC_MIN samples, default 8192); both are read once,
 // when the library is first used.
 constexpr int64_t kTcNever = INT64_MAX;
-constexpr int64_t kTcAutoMin[kTcMaxDim + 1] = {kTcNever, kTcNever, kTcNever, kTcNever, 500000, 300000, 180000, 160000};
+constexpr int64_t kTcAutoMin[kTcMaxDim + 1] = {kTcNever, kTcNever, kTcNever, kTcNever, 16384, 24576, 32768, 32768};
 
 struct TcPolicy {
     int mode;            // 0 off, 1 forced, 2 automatic

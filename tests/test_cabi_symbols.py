@@ -70,9 +70,10 @@ def test_knn_filter_kind_policy_is_a_pure_host_query():
     lib = _lib.lib()
     kind = lambda n, d, k: lib.mpb_knn_filter_kind(ctypes.c_int64(n), d, k)
     FP32, TENSOR, EXACT = 0, 1, 2
-    assert kind(1000000, 7, 11) == TENSOR and kind(180000, 6, 11) == TENSOR and kind(160000, 7, 11) == TENSOR
-    assert kind(159999, 7, 11) == FP32 and kind(100000, 6, 11) == FP32
-    assert kind(1000000, 5, 11) == TENSOR and kind(299999, 5, 11) == FP32 and kind(499999, 4, 11) == FP32
+    assert kind(1000000, 7, 11) == TENSOR and kind(100000, 6, 11) == TENSOR and kind(32768, 7, 11) == TENSOR
+    assert kind(32767, 7, 11) == FP32 and kind(32767, 6, 11) == FP32
+    assert kind(24576, 5, 11) == TENSOR and kind(24575, 5, 11) == FP32
+    assert kind(16384, 4, 11) == TENSOR and kind(16383, 4, 11) == FP32
     assert kind(1000000, 3, 11) == FP32 and kind(1000000, 8, 11) == FP32
     assert kind(1000000, 7, 13) == FP32          # 32-entry lists: packed-fp32 kernel
     assert kind(1000000, 7, 29) == EXACT and kind(1000, 2, 32) == EXACT

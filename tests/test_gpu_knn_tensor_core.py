@@ -91,3 +91,36 @@ def test_tensor_core_filter_matches_oracle():
     out = subprocess.run([sys.executable, "-c", CHILD % ROOT], env=env, capture_output=True, text=True, timeout=900)
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
     assert "TC_OK" in out.stdout
+
+
+FP32_CHILD = r"""
+import sys, numpy as np, torch
+sys.path.insert(0, %r)
+import oracle
+from motion_planners_b200 import _lib, ops
+oracle.use_all_cores()
+lib = _lib.lib()
+host = lambda t: t.cpu().numpy()
+for N, M, D, k, seed in [(60000, 2000, 6, 11, 0), (40000, 1500, 7, 11, 1), (50000, 1000, 4, 12, 2)]:
+    assert lib.mpb_knn_filter_kind(N, D, k) == 0, (N, D, k)
+    rs = np.random.RandomState(seed)
+    X = rs.uniform(size=(N, D))
+    Q = np.concatenate([X[: M // 2], rs.uniform(-0.1, 1.1, size=(M - M // 2, D))])
+    w = rs.uniform(0.5, 2.0, size=D)
+    x, q = torch.from_numpy(X).cuda(), torch.from_numpy(Q).cuda()
+    idx, dist = ops.KnnIndex(x, w).search(q, k, float("inf"))
+    o_idx, o_dist = oracle.knn(X, Q, k, w)
+    assert (host(idx) == o_idx).all() and (host(dist) == o_dist).all(), (N, D)
+print("FP32_OK")
+"""
+
+
+def test_packed_fp32_filter_still_serves_mid_sized_sets_when_asked():
+    """With MPB200_KNN_TC=0 the FFMA2 filter takes the sets the tensor-core scan serves by default (it remains the
+    path of 2-D / 3-D sets, of more than 7 dimensions and of 12 < k <= 28): same answers as the oracle."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    env = dict(os.environ, MPB200_KNN_TC="0")
+    out = subprocess.run([sys.executable, "-c", FP32_CHILD % ROOT], env=env, capture_output=True, text=True, timeout=900)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+    assert "FP32_OK" in out.stdout

@@ -29,7 +29,6 @@ def test_static_scratch_knn_equals_workspace_knn_on_consecutive_calls():
     lib = _lib.lib()
     stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
     nullw = ctypes.POINTER(ctypes.c_double)()
-    capacity = 4 << 20
     # the claim in this file's name, asked of the driver itself: free device memory before and after the calls
     rt = ctypes.CDLL("libcudart.so.12")
     free_b, total_b = ctypes.c_size_t(), ctypes.c_size_t()
@@ -43,8 +42,9 @@ def test_static_scratch_knn_equals_workspace_knn_on_consecutive_calls():
         rs = np.random.RandomState(seed)
         xs = torch.from_numpy(rs.uniform(size=(N, D))).cuda()
         qs = torch.from_numpy(np.concatenate([xs[:M // 2].cpu().numpy(), rs.uniform(size=(M - M // 2, D))])).cuda()
+        # (the caller-owned workspace of the 60000-sample set is the tensor-core scan's, larger than the built-in
+        # array: the static entry point keeps to the packed-fp32 filter and sizes its scratch for that)
         need = lib.mpb_knn_workspace_bytes(N, M, D)
-        assert need <= capacity
 
         # existing entry point, caller-owned workspace
         ws = torch.empty(need + 256, dtype=torch.uint8, device="cuda")
