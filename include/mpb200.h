@@ -387,7 +387,7 @@ int mpb_roadmap_parents(const int64_t *nbr, const double *nbr_dist, const int32_
 /* Which filter mpb_knn_search / mpb_knn_f32filter run for a sample set of this size and dimension at this k
  * (for reporting; results are identical): the packed-fp32 FFMA2 scan, the tensor-core scan (tcgen05.mma
  * kind::tf32 on operands split into two TF32 parts, accumulator in tensor memory), or the exact fp64 scan alone.
- * The tensor-core scan is chosen for k <= 12 and sets of at least 160 000 / 180 000 / 300 000 / 500 000 samples in
+ * The tensor-core scan is chosen for k <= 12 and sets of at least 32 768 / 32 768 / 24 576 / 16 384 samples in
  * 7 / 6 / 5 / 4 dimensions (where it was measured faster);
  * MPB200_KNN_TC=0 / =1 in the environment (read once) switches it off / forces it wherever it applies. */
 #define MPB_KNN_KIND_FP32 0

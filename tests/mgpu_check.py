@@ -25,7 +25,8 @@ def main():
     ok = True
     # small sets (rows = the rank's own index shard), sets the tensor-core scan serves (rows = a slice of the
     # spatial order), ragged shard sizes, and the arm world of configs[3]
-    cases = [(20000, 6, workloads.c2_world()), (20003, 7, workloads.c3_world()), (200001, 7, workloads.c4lite_world()),
+    cases = [(20000, 6, workloads.c2_world()), (20003, 7, workloads.c3_world()), (50001, 6, workloads.c2_world()),
+             (200001, 7, workloads.c4lite_world()),
              (170000, 7, workloads.c4_world())]
     if os.environ.get("MPB_MGPU_FULL"):
         cases.append((1000000, 7, workloads.c4lite_world()))
