@@ -235,8 +235,10 @@ int mpb_knn_f32filter(const double *samples, int64_t n_samples, const double *qu
  * scratch is a fixed array of MPB_KNN_STATIC_BYTES inside the library, resident on every GPU that
  * loads it until the process exits; inputs and outputs are still the caller's.  No counterpart in
  * the reference (it has no device memory to manage).
- *  - Sizes whose scratch need (mpb_knn_workspace_bytes) exceeds MPB_KNN_STATIC_BYTES are refused
- *    with MPB_ENOMEM and a message; 4 MiB covers e.g. 100k samples x 100k queries at dim <= 7.
+ *  - This entry point always runs the packed-fp32 filter (never the tensor-core scan), and its scratch
+ *    need is that filter's alone (smaller than mpb_knn_workspace_bytes for sets the tensor-core scan
+ *    serves).  Sizes whose need exceeds MPB_KNN_STATIC_BYTES are refused with MPB_ENOMEM and a
+ *    message; 4 MiB covers e.g. 100k samples x 100k queries at dim <= 7.
  *  - The first call on each device looks up the array's device address; make that call before
  *    starting any stream capture on that device.
  *  - The call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine).
