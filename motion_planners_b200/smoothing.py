@@ -149,22 +149,33 @@ def smooth_paths_batch(paths, extend_fn, collision_fn, distance_fn, seeds, max_i
         cost_fn = distance_fn
     n = len(paths)
     way = [waypoints_from_path(p) if p else p for p in paths]
-    cost = [compute_path_cost(w, cost_fn=cost_fn) if w else INF for w in way]
+    same_fn = cost_fn is distance_fn
+    # per path: cost_fn of every segment, in order (compute_path_cost is their sequential sum from the left, which
+    # the candidate test below re-does with three new terms in the middle instead of calling cost_fn on every
+    # segment again), and distance_fn of every segment (the draw's weights)
+    segc = [[cost_fn(w[a], w[a + 1]) for a in range(len(w) - 1)] if w else None for w in way]
+    cost = [sum(c) if c is not None else INF for c in segc]
     rpy = [pyrandom.Random(int(s)) for s in seeds]
     rnp = [np.random.RandomState(int(s)) for s in seeds]
     weights = [None] * n                     # cached segment lengths, recomputed when a path changes
+    cdf = [None] * n                         # ... and the cumulative distribution RandomState.choice builds from them
     obs = collision_fn.obstacles
     for _ in range(int(max_iterations)):
-        # 1. per path: draw the two segments (host; identical generator calls to smooth_path)
+        # 1. per path: draw the two segments (host; the generator calls of smooth_path: choice(p=...) of the legacy
+        # RandomState is cdf = p.cumsum(); cdf /= cdf[-1]; cdf.searchsorted(random_sample(size), side='right'))
         drawn = []
         for i in range(n):
             w = way[i]
             if not w or len(w) <= 2:
                 continue
-            if weights[i] is None:
-                weights[i] = [distance_fn(w[a], w[a + 1]) for a in range(len(w) - 1)]
-            prob = np.array(weights[i]) / sum(weights[i])
-            s1, s2 = rnp[i].choice(list(range(len(w) - 1)), size=2, replace=True, p=prob)
+            if cdf[i] is None:
+                if weights[i] is None:
+                    weights[i] = segc[i] if same_fn else [distance_fn(w[a], w[a + 1]) for a in range(len(w) - 1)]
+                prob = np.array(weights[i]) / sum(weights[i])
+                c = prob.cumsum()
+                c /= c[-1]
+                cdf[i] = c
+            s1, s2 = cdf[i].searchsorted(rnp[i].random_sample(2), side='right')
             if s1 == s2:
                 continue
             if s2 < s1:
@@ -181,18 +192,24 @@ def smooth_paths_batch(paths, extend_fn, collision_fn, distance_fn, seeds, max_i
         off, pts = off.cpu().numpy(), pts.cpu().numpy()
         cand = []
         for j, (i, s1, s2) in enumerate(drawn):
-            seg_a = pts[off[2 * j]:off[2 * j + 1] - 1]            # list(extend_fn(...))[:-1]
-            seg_b = pts[off[2 * j + 1]:off[2 * j + 2] - 1]
-            if len(seg_a) == 0 or len(seg_b) == 0:
+            a0, a1 = int(off[2 * j]), int(off[2 * j + 1]) - 1       # list(extend_fn(...))[:-1]
+            b0, b1 = int(off[2 * j + 1]), int(off[2 * j + 2]) - 1
+            if a1 <= a0 or b1 <= b0:
                 continue
-            p1 = rpy[i].choice(list(seg_a))
-            p2 = rpy[i].choice(list(seg_b))
-            w = way[i]
-            new_w = w[:s1 + 1] + [p1, p2] + w[s2 + 1:]
-            new_cost = compute_path_cost(new_w, cost_fn=cost_fn)
+            p1 = pts[a0 + rpy[i].choice(range(a1 - a0))]              # random.choice(seq) = seq[_randbelow(len(seq))]
+            p2 = pts[b0 + rpy[i].choice(range(b1 - b0))]
+            w, sc = way[i], segc[i]
+            three = [cost_fn(w[s1], p1), cost_fn(p1, p2), cost_fn(p2, w[s2 + 1])]
+            new_cost = 0
+            for a in range(s1):
+                new_cost = new_cost + sc[a]
+            for c in three:
+                new_cost = new_cost + c
+            for a in range(s2 + 1, len(sc)):
+                new_cost = new_cost + sc[a]
             if new_cost >= cost[i] or (cost[i] - new_cost) / cost[i] <= 0.0:
                 continue
-            cand.append((i, p1, p2, new_w, new_cost))
+            cand.append((i, p1, p2, s1, s2, three, new_cost))
         if not cand:
             continue
         # 3. verdicts of all bridges: both end points, then the edge between them without its last waypoint
@@ -202,9 +219,12 @@ def smooth_paths_batch(paths, extend_fn, collision_fn, distance_fn, seeds, max_i
         hit, _ = obs.edges_check_pairs(a, b, mode=ops.EDGE_ANY, skip_last=True, step=extend_fn.step_size,
                                        want_counts=False)
         bad = (bad | (hit >= 0)).cpu().numpy()
-        for ok, (i, p1, p2, new_w, new_cost) in zip(~bad, cand):
+        for ok, (i, p1, p2, s1, s2, three, new_cost) in zip(~bad, cand):
             if ok:
-                way[i], cost[i], weights[i] = new_w, new_cost, None
+                w = way[i]
+                way[i] = w[:s1 + 1] + [p1, p2] + w[s2 + 1:]
+                segc[i] = segc[i][:s1] + three + segc[i][s2 + 1:]
+                cost[i], weights[i], cdf[i] = new_cost, None, None
     # 4. final re-discretisation of every path, one launch
     out = [None] * n
     idx = [i for i in range(n) if way[i]]
