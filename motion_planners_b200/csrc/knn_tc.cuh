@@ -1111,7 +1111,10 @@ __global__ void __launch_bounds__(256)
     int rank[NU];
 #pragma unroll
     for (int u = 0; u < NU; ++u) rank[u] = 0;
-    for (int o = 0; o < 32; ++o) {
+    // Lanes past the last survivor hold (inf, -1): they come before an entry only if that entry's own key is inf
+    // (then they all do), so the loop stops at the survivors and such an entry gets them added at once.
+    constexpr int kLive = (kTcSurvivors < 32) ? kTcSurvivors : 32;
+    for (int o = 0; o < kLive; ++o) {
 #pragma unroll
         for (int w = 0; w < NU; ++w) {
             const double So = __shfl_sync(FULL_MASK, S[w], o);
@@ -1119,6 +1122,9 @@ __global__ void __launch_bounds__(256)
 #pragma unroll
             for (int u = 0; u < NU; ++u) rank[u] += ((So < S[u]) || (So == S[u] && io < ci[u])) ? 1 : 0;
         }
+    }
+    if (NU == 1 && kLive < 32) {
+        if (ci[0] >= 0 && S[0] == INFINITY) rank[0] += 32 - kLive;
     }
     // k-th smallest exact key among the survivors (inf when fewer than k exist)
     double Sk = INFINITY;
