@@ -945,7 +945,7 @@ int launch_search(const double *x, int64_t N, const double *qs, int64_t M, const
                 qs, qorder, wt, tiles, (int)L.tc_tiles, boxes, L.box_stride, h, surv, sthr, nullptr, nullptr, nullptr, own_block0, own_part, own_parts);
             MPB_LAUNCH_CHECK();
             const int64_t n_slots = blocks * kTcQueries;
-            const int64_t rthreads = n_slots * 32;
+            const int64_t rthreads = n_slots * (kTcSurvivors <= 16 ? 16 : 32);      // a half warp per query slot
             knn_tc_rerank_kernel<D><<<(unsigned)((rthreads + 255) / 256), 256, 0, st>>>(
                 x, N, qs, M, wt, k, r2, h, qorder, n_slots, slot_idx, surv, sthr, fb, rows, out_idx, out_dist);
             MPB_LAUNCH_CHECK();

@@ -1081,11 +1081,18 @@ __global__ void __launch_bounds__(256)
                          int64_t *__restrict__ out_idx, double *__restrict__ out_dist)
 {
     constexpr int NU = (kTcSurvivors + 31) / 32;   // survivors per lane
+    // a query is served by a group of G lanes: the whole warp, or -- with 16 survivors -- half of it, two queries
+    // per warp (0.92 -> about 0.6 ms at 1M queries: most of the kernel is per-warp bookkeeping, not the 16 distances)
+    constexpr int G = (kTcSurvivors <= 16) ? 16 : 32;
     const int lane = threadIdx.x & 31;
-    const int64_t slot = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (slot >= n_slots) return;                // whole warps leave together
-    const int64_t q = qorder[slot];
-    if (q < 0 || q >= M) return;                // an unused slot of a query block
+    const int gl = lane & (G - 1), gbase = lane & ~(G - 1);
+    const unsigned gmask = (G == 32) ? FULL_MASK : (0xffffu << gbase);
+    const int64_t slot = (((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * (32 / G) + lane / G;
+    if (slot - lane / G >= n_slots) return;     // whole warps leave together (n_slots is a multiple of 128)
+    const int64_t q_raw = slot < n_slots ? (int64_t)qorder[slot] : -1;
+    const bool live = q_raw >= 0 && q_raw < M;  // not an unused slot of a query block
+    if (!__any_sync(FULL_MASK, live)) return;
+    const int64_t q = live ? q_raw : 0;
     double eq[D];
     double nq2 = 0.;
 #pragma unroll
@@ -1098,7 +1105,7 @@ __global__ void __launch_bounds__(256)
     double S[NU];
 #pragma unroll
     for (int u = 0; u < NU; ++u) {
-        ci[u] = (u * 32 + lane < kTcSurvivors) ? surv_idx[slot * kTcSurvivors + u * 32 + lane] : -1;
+        ci[u] = (live && u * 32 + gl < kTcSurvivors) ? surv_idx[slot * kTcSurvivors + u * 32 + gl] : -1;
         if (ci[u] >= 0) ci[u] = slot_idx[ci[u]];   // tile slot -> sample index (-1: a padding slot)
         S[u] = INFINITY;
         if (ci[u] >= 0) {
@@ -1117,8 +1124,8 @@ __global__ void __launch_bounds__(256)
     for (int o = 0; o < kLive; ++o) {
 #pragma unroll
         for (int w = 0; w < NU; ++w) {
-            const double So = __shfl_sync(FULL_MASK, S[w], o);
-            const int io = __shfl_sync(FULL_MASK, ci[w], o);
+            const double So = __shfl_sync(FULL_MASK, S[w], gbase + o);
+            const int io = __shfl_sync(FULL_MASK, ci[w], gbase + o);
 #pragma unroll
             for (int u = 0; u < NU; ++u) rank[u] += ((So < S[u]) || (So == S[u] && io < ci[u])) ? 1 : 0;
         }
@@ -1130,13 +1137,13 @@ __global__ void __launch_bounds__(256)
     double Sk = INFINITY;
 #pragma unroll
     for (int u = 0; u < NU; ++u) {
-        const unsigned mk = __ballot_sync(FULL_MASK, ci[u] >= 0 && rank[u] == k - 1);
+        const unsigned mk = __ballot_sync(FULL_MASK, ci[u] >= 0 && rank[u] == k - 1) & gmask;
         const double cand = __shfl_sync(FULL_MASK, S[u], mk ? (__ffs(mk) - 1) : 0);
         if (mk) Sk = cand;
     }
     int nvalid = 0;
 #pragma unroll
-    for (int u = 0; u < NU; ++u) nvalid += __popc(__ballot_sync(FULL_MASK, ci[u] >= 0));
+    for (int u = 0; u < NU; ++u) nvalid += __popc(__ballot_sync(FULL_MASK, ci[u] >= 0) & gmask);
     float T32 = INFINITY;
 #pragma unroll
     for (int p = 0; p < kTcLists; ++p) {
@@ -1165,6 +1172,7 @@ __global__ void __launch_bounds__(256)
         }
         ok = (Sk < bound) || (r2 <= bound);
     }
+    if (!live) return;                          // (no warp-wide operation below this line)
     if (ok) {
         const int64_t row = rows.row(q);
 #pragma unroll
@@ -1175,11 +1183,11 @@ __global__ void __launch_bounds__(256)
                 if (out_dist) out_dist[row * k + rank[u]] = keep ? __dsqrt_rn(S[u]) : INFINITY;
             }
         }
-        if (lane < k && lane >= nvalid) {
-            out_idx[row * k + lane] = -1;
-            if (out_dist) out_dist[row * k + lane] = INFINITY;
+        if (gl < k && gl >= nvalid) {
+            out_idx[row * k + gl] = -1;
+            if (out_dist) out_dist[row * k + gl] = INFINITY;
         }
-    } else if (lane == 0) {
+    } else if (gl == 0) {
         const int pos = atomicAdd(&h->fb_count, 1);
         fb_list[pos] = (int)q;
     }
