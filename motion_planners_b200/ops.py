@@ -309,7 +309,7 @@ class KnnIndex(object):
 
     def search_part(self, part, parts, k, max_dist=math.inf, stats=None):
         """Share `part` of `parts` of the set's own kNN graph (mpb_knn_search_part): -> (row_ids [rows] int64 =
-        sample index per row, idx [rows, k], dist [rows, k]); the parts are slices of the spatial order."""
+        sample index per row, idx [rows, k], dist [rows, k]); the parts are shares of the k-d leaves, dealt in rotation."""
         rows = self.part_rows(part, parts)
         if rows < 0:
             raise _lib.MpbError("this sample set has no spatial order (the tensor-core scan does not serve it)")

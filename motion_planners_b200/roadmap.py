@@ -14,9 +14,10 @@ passes over tensors that stay in HBM:
 Samples are sharded across ranks; one all-gather (NCCL over NVLink) builds the global sample
 set, every rank answers its share of the queries against it and checks the directed edges that
 leave those samples.  Which rows a rank owns (`row_ids`): its own index shard for small sets;
-for sets the tensor-core scan serves, a contiguous slice of the set's spatial (k-d leaf) order,
-so that the 128-query blocks of every rank are as compact in space as a single GPU's and the
-scan prunes as well at 8 GPUs as at 1.  The union of the ranks' rows is identical for every
+for sets the tensor-core scan serves, a share of the set's k-d leaves (whole leaves, dealt to the
+ranks in rotation), so that the 128-query blocks of every rank are as compact in space as a single
+GPU's, the scan prunes as well at 8 GPUs as at 1, and every rank gets leaves from all over the
+sampled region.  The union of the ranks' rows is identical for every
 world size (`gather_global` assembles it in sample order).
 """
 import math
@@ -136,7 +137,7 @@ class DeviceRoadmap(object):
         if getattr(self, "stats", None) is None:
             self.stats = torch.zeros(2, dtype=torch.int64, device=samples.device)
         if spatial:
-            # this rank's rows: a contiguous slice of the set's spatial order (every rank computes the same order), i.e.
+            # this rank's rows: a share of the leaves of the set's k-d order (every rank computes the same order), i.e.
             # a share of the very query blocks a single-GPU build forms
             self._index.prepare(N)
             mark("packed")

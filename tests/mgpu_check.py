@@ -23,7 +23,7 @@ def main():
     torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
     dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ["LOCAL_RANK"])))
     ok = True
-    # small sets (rows = the rank's own index shard), sets the tensor-core scan serves (rows = a slice of the
+    # small sets (rows = the rank's own index shard), sets the tensor-core scan serves (rows = a share of the leaves of the
     # spatial order), ragged shard sizes, and the arm world of configs[3]
     cases = [(20000, 6, workloads.c2_world()), (20003, 7, workloads.c3_world()), (50001, 6, workloads.c2_world()),
              (200001, 7, workloads.c4lite_world()),

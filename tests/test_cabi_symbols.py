@@ -78,3 +78,23 @@ def test_knn_filter_kind_policy_is_a_pure_host_query():
     assert kind(1000000, 7, 13) == FP32          # 32-entry lists: packed-fp32 kernel
     assert kind(1000000, 7, 29) == EXACT and kind(1000, 2, 32) == EXACT
     assert kind(1000, 0, 3) < 0 and kind(1000, 3, 0) < 0 and kind(1000, 3, 33) < 0
+
+
+def test_knn_part_rows_partition_the_set():
+    """mpb_knn_part_rows is host arithmetic: the shares of the k-d leaves that mpb_knn_search_part deals to the ranks
+    cover every sample exactly once and differ by no more than a leaf or two."""
+    import ctypes
+    import os
+    if os.environ.get("MPB200_KNN_TC") is not None:
+        import pytest
+        pytest.skip("the policy is overridden through the environment")
+    from motion_planners_b200 import _lib
+    lib = _lib.lib()
+    rows = lambda n, d, r, g: int(lib.mpb_knn_part_rows(ctypes.c_int64(n), d, r, g))
+    for n, d in [(1000000, 7), (200001, 7), (50001, 6), (100000, 6), (32768, 7), (777777, 5)]:
+        for g in (1, 2, 3, 4, 8):
+            sizes = [rows(n, d, r, g) for r in range(g)]
+            assert sum(sizes) == n and min(sizes) > 0, (n, d, g, sizes)
+            assert max(sizes) - min(sizes) <= 2 * 128, (n, d, g, sizes)
+    assert rows(20000, 6, 0, 2) == -1 and rows(1000000, 3, 0, 2) == -1      # sets the tensor-core scan does not serve
+    assert rows(1000000, 7, 2, 2) == -1 and rows(1000000, 7, -1, 2) == -1
