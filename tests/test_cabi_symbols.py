@@ -82,7 +82,7 @@ def test_knn_filter_kind_policy_is_a_pure_host_query():
 
 def test_knn_part_rows_partition_the_set():
     """mpb_knn_part_rows is host arithmetic: the shares of the k-d leaves that mpb_knn_search_part deals to the ranks
-    cover every sample exactly once and differ by no more than a leaf or two."""
+    cover every sample exactly once and are equal to within one per cent (leaves hold 122 or 123 samples at 1M)."""
     import ctypes
     import os
     if os.environ.get("MPB200_KNN_TC") is not None:
@@ -95,6 +95,6 @@ def test_knn_part_rows_partition_the_set():
         for g in (1, 2, 3, 4, 8):
             sizes = [rows(n, d, r, g) for r in range(g)]
             assert sum(sizes) == n and min(sizes) > 0, (n, d, g, sizes)
-            assert max(sizes) - min(sizes) <= 2 * 128, (n, d, g, sizes)
+            assert max(sizes) - min(sizes) <= max(2 * 128, n // g // 100), (n, d, g, sizes)
     assert rows(20000, 6, 0, 2) == -1 and rows(1000000, 3, 0, 2) == -1      # sets the tensor-core scan does not serve
     assert rows(1000000, 7, 2, 2) == -1 and rows(1000000, 7, -1, 2) == -1
