@@ -538,10 +538,11 @@ def main():
     from motion_planners_b200 import _lib as _mplib
 
     def knn_roofline(r):
-        """kNN scan.  SURVEY 8d: algorithmic work = 3*D flop per (query, sample) pair, all pairs."""
+        """kNN scan, ONE launch = one rank's queries against the whole set.  SURVEY 8d: algorithmic work = 3*D flop per
+        (query, sample) pair, all pairs of the launch."""
         n, D, k, n_local = r["n"], r["D"], r["k"], r["n_local"]
         ms = r["phase_ms"].get("knn", float("nan"))
-        pairs = float(n_local) * world_size * n
+        pairs = float(n_local) * n
         alg = 3.0 * D * pairs
         kind = _mplib.lib().mpb_knn_filter_kind(int(n), int(D), int(k) + 1)
         out = {"kernel": {0: "knn_filter_kernel", 1: "knn_tc_kernel", 2: "knn_exact_kernel"}[kind],
@@ -552,7 +553,7 @@ def main():
             # (every fp32 value enters as two TF32 parts: 24 operand columns).  The scan skips the tiles whose
             # bounding box is provably too far from a query block, so executed << algorithmic and
             # frac (algorithmic / peak) can exceed 1; frac_executed is what the tensor pipe actually did.
-            executed = float(r["tiles_visited"]) * 128 * 256 * 48
+            executed = float(r["tiles_visited"]) / world_size * 128 * 256 * 48      # tiles_visited is summed over ranks
             out.update({
                 "bound": "tensor", "achieved": alg / (ms * 1e-3) / 1e12, "peak": tf32_peak, "unit": "TFLOP/s",
                 "frac": alg / (ms * 1e-3) / 1e12 / tf32_peak,
@@ -560,7 +561,7 @@ def main():
                                 "was measured at a %s MHz median SM clock under power capping, this kernel runs at the clock in "
                                 "`clocks`" % peaks_file.get("clocks_under_load", {}).get("sm_mhz_median", "?")) if bf16_peak
                 else "fallback: nominal dense TF32, 1130 TFLOP/s",
-                "executed_flops_per_pair_visited": 48, "tiles_read": r["tiles_visited"],
+                "executed_flops_per_pair_visited": 48, "tiles_read": r["tiles_visited"] / world_size,
                 "tiles_read_per_query_block": r["tiles_visited"] / max(1.0, n_local * world_size / 128.0),
                 "tiles_total": (n + 255) // 256, "pairs_visited_frac": executed / 48.0 / pairs,
                 "executed_tflops": executed / (ms * 1e-3) / 1e12,
@@ -583,7 +584,7 @@ def main():
         n, D, k = r["n"], r["D"], r["k"]
         world = r["world"]
         ms = r["phase_ms"].get("edges", float("nan"))
-        rows_edges = float(r["n_local"]) * world_size * (k + 1)       # edges the kernel walks (self-edges included)
+        rows_edges = float(r["n_local"]) * (k + 1)       # edges ONE launch walks (this rank's rows, self-edges included)
         wp = r["mean_waypoints"]
         arm = hasattr(world, "model")
         if arm:
